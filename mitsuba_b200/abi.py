@@ -1,0 +1,104 @@
+"""ctypes mirror of include/mtsb200.h (the C ABI of the B200 `path` hot path).
+
+Only layout definitions live here -- no compute.  Both the product binding
+(`mitsuba_b200.lib`) and the test-only oracle binding (`oracle/`) describe scenes
+with these structures so that they consume byte-identical inputs.
+"""
+import ctypes as C
+
+import numpy as np
+
+ABI_VERSION = 1
+
+OK, ERR_INVALID, ERR_NO_DEVICE, ERR_CUDA, ERR_CANCELLED, ERR_IO, ERR_PARSE = range(7)
+BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_ROUGHDIELECTRIC, BSDF_NULL = range(4)
+DISTR_BECKMANN, DISTR_GGX = 0, 1
+MAT_TWOSIDED, MAT_SAMPLE_VISIBLE = 1, 2
+EMITTER_AREA, EMITTER_POINT, EMITTER_CONSTANT = 0, 1, 2
+RFILTER_GAUSSIAN, RFILTER_BOX = 0, 1
+TRACE_CLOSEST, TRACE_ANY = 0, 1
+NO_HIT = 0xFFFFFFFF
+RENDER_KEEP_FILM = 1
+
+
+class Material(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("flags", C.c_uint32), ("distribution", C.c_uint32), ("back", C.c_int32),
+                ("alpha_u", C.c_float), ("alpha_v", C.c_float), ("eta", C.c_float), ("_pad0", C.c_float),
+                ("reflectance", C.c_float * 3), ("transmittance", C.c_float * 3),
+                ("cond_eta", C.c_float * 3), ("cond_k", C.c_float * 3)]
+
+
+class Shape(C.Structure):
+    _fields_ = [("first_vertex", C.c_uint32), ("n_vertices", C.c_uint32), ("first_tri", C.c_uint32),
+                ("n_tris", C.c_uint32), ("material", C.c_int32), ("emitter", C.c_int32),
+                ("has_normals", C.c_uint32), ("has_texcoords", C.c_uint32)]
+
+
+class Emitter(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("shape", C.c_int32), ("radiance", C.c_float * 3),
+                ("position", C.c_float * 3), ("sampling_weight", C.c_float), ("_pad", C.c_float * 3)]
+
+
+class Sensor(C.Structure):
+    _fields_ = [("to_world", C.c_float * 16), ("fov_x_deg", C.c_float), ("near_clip", C.c_float),
+                ("far_clip", C.c_float), ("film_width", C.c_int32), ("film_height", C.c_int32),
+                ("crop_x", C.c_int32), ("crop_y", C.c_int32), ("crop_width", C.c_int32), ("crop_height", C.c_int32),
+                ("rfilter", C.c_uint32), ("rfilter_radius", C.c_float), ("rfilter_stddev", C.c_float)]
+
+
+class Integrator(C.Structure):
+    _fields_ = [("max_depth", C.c_int32), ("rr_depth", C.c_int32), ("strict_normals", C.c_int32),
+                ("hide_emitters", C.c_int32), ("sample_count", C.c_int32), ("_pad", C.c_uint32)]
+
+
+class SceneDesc(C.Structure):
+    _fields_ = [("abi_version", C.c_uint32), ("n_shapes", C.c_uint32), ("n_materials", C.c_uint32),
+                ("n_emitters", C.c_uint32), ("n_vertices", C.c_uint64), ("n_tris", C.c_uint64),
+                ("shapes", C.POINTER(Shape)), ("materials", C.POINTER(Material)), ("emitters", C.POINTER(Emitter)),
+                ("positions", C.POINTER(C.c_float)), ("normals", C.POINTER(C.c_float)),
+                ("texcoords", C.POINTER(C.c_float)), ("indices", C.POINTER(C.c_uint32)),
+                ("sensor", Sensor), ("integrator", Integrator)]
+
+
+class RenderParams(C.Structure):
+    _fields_ = [("spp", C.c_int32), ("spp_offset", C.c_int32), ("seed", C.c_uint64),
+                ("tile_index", C.c_int32), ("tile_count", C.c_int32), ("spp_per_pass", C.c_int32),
+                ("flags", C.c_uint32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("samples", C.c_uint64), ("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
+                ("shade_events", C.c_uint64), ("path_length_sum", C.c_uint64), ("kernel_launches", C.c_uint64),
+                ("bad_samples", C.c_uint64), ("ms_total", C.c_float), ("ms_trace_closest", C.c_float),
+                ("ms_trace_any", C.c_float), ("ms_shade", C.c_float), ("ms_raygen", C.c_float),
+                ("ms_splat", C.c_float), ("ms_h2d", C.c_float), ("ms_d2h", C.c_float), ("n_passes", C.c_uint32)]
+
+
+class SceneInfo(C.Structure):
+    _fields_ = [("n_tris", C.c_uint64), ("n_bvh_nodes", C.c_uint64), ("bvh_bytes", C.c_uint64),
+                ("tri_bytes", C.c_uint64), ("aabb_min", C.c_float * 3), ("aabb_max", C.c_float * 3),
+                ("build_ms", C.c_float), ("n_emitters", C.c_uint32)]
+
+
+# numpy views of the array-of-struct records that cross the ABI
+RAY_DTYPE = np.dtype([("o", np.float32, 3), ("mint", np.float32), ("d", np.float32, 3), ("maxt", np.float32)])
+HIT_DTYPE = np.dtype([("prim", np.uint32), ("u", np.float32), ("v", np.float32), ("t", np.float32)])
+BSDF_QUERY_DTYPE = np.dtype([("wi", np.float32, 3), ("wo", np.float32, 3), ("u", np.float32, 3)])
+BSDF_RESULT_DTYPE = np.dtype([("eval", np.float32, 3), ("pdf", np.float32), ("weight", np.float32, 3),
+                              ("spdf", np.float32), ("swo", np.float32, 3), ("seta", np.float32)])
+DIRECT_QUERY_DTYPE = np.dtype([("ref", np.float32, 3), ("ref_n", np.float32, 3), ("u", np.float32, 2)])
+DIRECT_RESULT_DTYPE = np.dtype([("value", np.float32, 3), ("pdf", np.float32), ("d", np.float32, 3),
+                                ("dist", np.float32), ("p", np.float32, 3), ("emitter", np.int32),
+                                ("n", np.float32, 3), ("measure", np.int32)])
+assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 16
+assert BSDF_QUERY_DTYPE.itemsize == 36 and BSDF_RESULT_DTYPE.itemsize == 48
+assert DIRECT_QUERY_DTYPE.itemsize == 32 and DIRECT_RESULT_DTYPE.itemsize == 64
+assert C.sizeof(Material) == 80 and C.sizeof(Shape) == 32 and C.sizeof(Emitter) == 48
+
+
+def ptr(arr, ctype):
+    """ctypes pointer to a C-contiguous numpy array (or NULL)."""
+    if arr is None:
+        return C.cast(None, C.POINTER(ctype))
+    assert arr.flags["C_CONTIGUOUS"]
+    return arr.ctypes.data_as(C.POINTER(ctype))

@@ -1,0 +1,258 @@
+"""Host-side flat scene description (the POD that crosses the C ABI).
+
+`SceneBuilder` plays the role of `Scene::addChild` + `Scene::initialize` flattening
+(reference: src/librender/scene.cpp:322-384, 558-592): shapes are appended as
+triangle meshes with a BSDF record and an optional area emitter, and `desc()` emits
+the `MtsbSceneDesc` with concatenated vertex / index buffers (global primitive id =
+shape offset + local triangle index, src/librender/skdtree.cpp:68-70).
+"""
+import ctypes as C
+import math
+
+import numpy as np
+
+from . import abi
+
+
+def _f3(v):
+    a = np.asarray(v, dtype=np.float32).reshape(-1)
+    if a.size == 1:
+        a = np.repeat(a, 3)
+    return (C.c_float * 3)(*[float(x) for x in a[:3]])
+
+
+def diffuse(reflectance=0.5, twosided=False):
+    """`diffuse` BSDF record (src/bsdfs/diffuse.cpp:82-84; reflectance clamped by
+    ensureEnergyConservation, src/librender/bsdf.cpp:96-113)."""
+    r = np.asarray(reflectance, dtype=np.float32).reshape(-1)
+    if r.size == 1:
+        r = np.repeat(r, 3)
+    mx = float(r.max())
+    if mx > 1.0:
+        r = r * np.float32(0.99 * (1.0 / mx))
+    m = abi.Material()
+    m.type = abi.BSDF_DIFFUSE
+    m.flags = abi.MAT_TWOSIDED if twosided else 0
+    m.back = -1
+    m.alpha_u = m.alpha_v = 0.1
+    m.eta = 1.0
+    m.reflectance = _f3(r)
+    m.transmittance = _f3(1.0)
+    m.cond_eta = _f3(0.0)
+    m.cond_k = _f3(1.0)
+    return m
+
+
+def _microfacet(m, distribution, alpha, alpha_u, alpha_v, sample_visible):
+    if alpha_u is None:
+        alpha_u = alpha_v = alpha
+    m.distribution = {"beckmann": abi.DISTR_BECKMANN, "ggx": abi.DISTR_GGX}[distribution]
+    m.alpha_u = max(float(alpha_u), 1e-4)      # microfacet.h:135-136
+    m.alpha_v = max(float(alpha_v), 1e-4)
+    if sample_visible:
+        m.flags |= abi.MAT_SAMPLE_VISIBLE
+
+
+def roughconductor(eta, k, alpha=0.1, distribution="beckmann", specular_reflectance=1.0, ext_eta=1.000277,
+                   sample_visible=True, twosided=False, alpha_u=None, alpha_v=None):
+    """`roughconductor` record (src/bsdfs/roughconductor.cpp:168-201): eta, k are divided by extEta."""
+    m = abi.Material()
+    m.type = abi.BSDF_ROUGHCONDUCTOR
+    m.flags = abi.MAT_TWOSIDED if twosided else 0
+    m.back = -1
+    _microfacet(m, distribution, alpha, alpha_u, alpha_v, sample_visible)
+    e = np.asarray(eta, dtype=np.float32).reshape(-1)
+    kk = np.asarray(k, dtype=np.float32).reshape(-1)
+    if e.size == 1:
+        e = np.repeat(e, 3)
+    if kk.size == 1:
+        kk = np.repeat(kk, 3)
+    m.cond_eta = _f3(e / np.float32(ext_eta))
+    m.cond_k = _f3(kk / np.float32(ext_eta))
+    m.reflectance = _f3(specular_reflectance)
+    m.transmittance = _f3(1.0)
+    m.eta = 1.0
+    return m
+
+
+def roughdielectric(int_ior=1.5046, ext_ior=1.000277, alpha=0.1, distribution="beckmann", specular_reflectance=1.0,
+                    specular_transmittance=1.0, sample_visible=True, alpha_u=None, alpha_v=None):
+    """`roughdielectric` record (src/bsdfs/roughdielectric.cpp:183-211)."""
+    m = abi.Material()
+    m.type = abi.BSDF_ROUGHDIELECTRIC
+    m.flags = 0
+    m.back = -1
+    _microfacet(m, distribution, alpha, alpha_u, alpha_v, sample_visible)
+    m.eta = float(np.float32(int_ior) / np.float32(ext_ior))
+    m.reflectance = _f3(specular_reflectance)
+    m.transmittance = _f3(specular_transmittance)
+    m.cond_eta = _f3(0.0)
+    m.cond_k = _f3(1.0)
+    return m
+
+
+def look_at(origin, target, up):
+    """Transform::lookAt (src/libcore/transform.cpp:191-214): row-major camera-to-world."""
+    p = np.asarray(origin, dtype=np.float64)
+    t = np.asarray(target, dtype=np.float64)
+    u = np.asarray(up, dtype=np.float64)
+    d = (t - p) / np.linalg.norm(t - p)
+    left = np.cross(u, d)
+    left /= np.linalg.norm(left)
+    new_up = np.cross(d, left)
+    m = np.eye(4)
+    m[:3, 0], m[:3, 1], m[:3, 2], m[:3, 3] = left, new_up, d, p
+    return m.astype(np.float32)
+
+
+class SceneBuilder:
+    def __init__(self):
+        self.materials = []
+        self.shapes = []          # dicts
+        self.emitters = []
+        self._pos, self._nrm, self._uv, self._idx = [], [], [], []
+        self._nv = 0
+        self._nt = 0
+        self.sensor = abi.Sensor()
+        self.integrator = abi.Integrator()
+        self.set_integrator()
+        self.set_sensor(look_at([0, 0, -5], [0, 0, 0], [0, 1, 0]), 45.0, 64, 64)
+        self._keep = None
+
+    # -- plugin-like setters ------------------------------------------------
+    def set_integrator(self, max_depth=-1, rr_depth=5, strict_normals=False, hide_emitters=False, sample_count=4):
+        """`path` integrator + `independent` sampler properties
+        (src/librender/integrator.cpp:252-287, src/samplers/independent.cpp:57)."""
+        ig = self.integrator
+        ig.max_depth, ig.rr_depth = int(max_depth), int(rr_depth)
+        ig.strict_normals, ig.hide_emitters = int(strict_normals), int(hide_emitters)
+        ig.sample_count = int(sample_count)
+
+    def set_sensor(self, to_world, fov, width, height, fov_axis="x", near_clip=1e-2, far_clip=1e4,
+                   rfilter="gaussian", stddev=0.5, box_radius=0.5, crop=None):
+        """`perspective` sensor + `hdrfilm` + reconstruction filter
+        (src/librender/sensor.cpp:225-309, src/librender/film.cpp:28-54, src/rfilters/{gaussian,box}.cpp)."""
+        s = self.sensor
+        tw = np.asarray(to_world, dtype=np.float32).reshape(16)
+        s.to_world = (C.c_float * 16)(*[float(x) for x in tw])
+        aspect = width / float(height)
+        if fov_axis == "smaller":
+            fov_axis = "y" if aspect > 1 else "x"
+        elif fov_axis == "larger":
+            fov_axis = "x" if aspect > 1 else "y"
+        if fov_axis == "x":
+            xfov = fov
+        elif fov_axis == "y":
+            xfov = math.degrees(2 * math.atan(math.tan(0.5 * math.radians(fov)) * aspect))
+        else:
+            raise ValueError("fovAxis must be x, y, smaller or larger")
+        s.fov_x_deg = xfov
+        s.near_clip, s.far_clip = near_clip, far_clip
+        s.film_width, s.film_height = int(width), int(height)
+        if crop is None:
+            crop = (0, 0, width, height)
+        s.crop_x, s.crop_y, s.crop_width, s.crop_height = [int(c) for c in crop]
+        if rfilter == "gaussian":
+            s.rfilter, s.rfilter_stddev, s.rfilter_radius = abi.RFILTER_GAUSSIAN, stddev, 4 * stddev
+        elif rfilter == "box":
+            s.rfilter, s.rfilter_stddev = abi.RFILTER_BOX, 0.0
+            s.rfilter_radius = float(np.float32(box_radius) + np.float32(1e-5))   # box.cpp:39
+        else:
+            raise ValueError("unsupported rfilter " + rfilter)
+
+    def add_material(self, m):
+        self.materials.append(m)
+        return len(self.materials) - 1
+
+    def add_twosided(self, front, back=None):
+        """`twosided` adapter (src/bsdfs/twosided.cpp): front/back are Material records."""
+        m = abi.Material.from_buffer_copy(front)
+        m.flags |= abi.MAT_TWOSIDED
+        if back is not None:
+            self.materials.append(back)
+            m.back = len(self.materials) - 1
+        self.materials.append(m)
+        return len(self.materials) - 1
+
+    def add_mesh(self, positions, indices, material, normals=None, texcoords=None, area_radiance=None,
+                 sampling_weight=1.0):
+        """A triangle-mesh shape; `area_radiance` attaches an `area` emitter (src/emitters/area.cpp)."""
+        positions = np.ascontiguousarray(positions, dtype=np.float32).reshape(-1, 3)
+        indices = np.ascontiguousarray(indices, dtype=np.uint32).reshape(-1, 3)
+        nv, nt = positions.shape[0], indices.shape[0]
+        if nt and int(indices.max()) >= nv:
+            raise ValueError("triangle index out of range")
+        sh = dict(first_vertex=self._nv, n_vertices=nv, first_tri=self._nt, n_tris=nt, material=material,
+                  emitter=-1, has_normals=normals is not None, has_texcoords=texcoords is not None)
+        self._pos.append(positions)
+        self._nrm.append(np.ascontiguousarray(normals, dtype=np.float32).reshape(-1, 3) if normals is not None
+                         else np.zeros((nv, 3), np.float32))
+        self._uv.append(np.ascontiguousarray(texcoords, dtype=np.float32).reshape(-1, 2) if texcoords is not None
+                        else np.zeros((nv, 2), np.float32))
+        self._idx.append(indices + np.uint32(self._nv))
+        self._nv += nv
+        self._nt += nt
+        self.shapes.append(sh)
+        if area_radiance is not None:
+            e = abi.Emitter()
+            e.type, e.shape = abi.EMITTER_AREA, len(self.shapes) - 1
+            e.radiance = _f3(area_radiance)
+            e.sampling_weight = sampling_weight
+            self.emitters.append(e)
+            sh["emitter"] = len(self.emitters) - 1
+        return len(self.shapes) - 1
+
+    def add_point_light(self, position, intensity, sampling_weight=1.0):
+        e = abi.Emitter()
+        e.type, e.shape = abi.EMITTER_POINT, -1
+        e.radiance, e.position, e.sampling_weight = _f3(intensity), _f3(position), sampling_weight
+        self.emitters.append(e)
+
+    def add_constant_env(self, radiance, sampling_weight=1.0):
+        e = abi.Emitter()
+        e.type, e.shape = abi.EMITTER_CONSTANT, -1
+        e.radiance, e.sampling_weight = _f3(radiance), sampling_weight
+        self.emitters.append(e)
+
+    # -- convenience geometry --------------------------------------------------
+    def add_quad(self, p0, p1, p2, p3, material, **kw):
+        """Two triangles (p0,p1,p2), (p0,p2,p3)."""
+        return self.add_mesh(np.array([p0, p1, p2, p3], np.float32), np.array([[0, 1, 2], [0, 2, 3]], np.uint32),
+                             material, **kw)
+
+    # -- flatten ------------------------------------------------------------------
+    @property
+    def n_tris(self):
+        return self._nt
+
+    def arrays(self):
+        pos = np.ascontiguousarray(np.concatenate(self._pos)) if self._pos else np.zeros((0, 3), np.float32)
+        nrm = np.ascontiguousarray(np.concatenate(self._nrm)) if self._nrm else np.zeros((0, 3), np.float32)
+        uv = np.ascontiguousarray(np.concatenate(self._uv)) if self._uv else np.zeros((0, 2), np.float32)
+        idx = np.ascontiguousarray(np.concatenate(self._idx)) if self._idx else np.zeros((0, 3), np.uint32)
+        return pos, nrm, uv, idx
+
+    def desc(self):
+        """Returns (MtsbSceneDesc, keepalive)."""
+        pos, nrm, uv, idx = self.arrays()
+        shapes = (abi.Shape * max(1, len(self.shapes)))()
+        for i, s in enumerate(self.shapes):
+            shapes[i].first_vertex, shapes[i].n_vertices = s["first_vertex"], s["n_vertices"]
+            shapes[i].first_tri, shapes[i].n_tris = s["first_tri"], s["n_tris"]
+            shapes[i].material, shapes[i].emitter = s["material"], s["emitter"]
+            shapes[i].has_normals, shapes[i].has_texcoords = int(s["has_normals"]), int(s["has_texcoords"])
+        mats = (abi.Material * max(1, len(self.materials)))(*self.materials)
+        ems = (abi.Emitter * max(1, len(self.emitters)))(*self.emitters)
+        d = abi.SceneDesc()
+        d.abi_version = abi.ABI_VERSION
+        d.n_shapes, d.n_materials, d.n_emitters = len(self.shapes), len(self.materials), len(self.emitters)
+        d.n_vertices, d.n_tris = pos.shape[0], idx.shape[0]
+        d.shapes, d.materials, d.emitters = shapes, mats, ems
+        d.positions = abi.ptr(pos, C.c_float)
+        d.normals = abi.ptr(nrm, C.c_float)
+        d.texcoords = abi.ptr(uv, C.c_float)
+        d.indices = abi.ptr(idx, C.c_uint32)
+        d.sensor = self.sensor
+        d.integrator = self.integrator
+        keep = (pos, nrm, uv, idx, shapes, mats, ems)
+        return d, keep

@@ -1,0 +1,330 @@
+// ORACLE -- TEST INFRASTRUCTURE ONLY.  Not part of the product path.
+// Scene-level restatement: intersection record, emitters, direct sampling, sensor, film.
+#pragma once
+#include "orc_math.h"
+#include "orc_bsdf.h"
+#include "orc_accel.h"
+#include <vector>
+#include <mutex>
+
+namespace orc {
+
+// Subset of Intersection (include/mitsuba/render/shape.h:30-190) that `path` reads.
+struct Its {
+    bool valid;
+    float t;
+    V3 p;
+    V3 geoN;          // geoFrame.n
+    Frame sh;         // shFrame
+    P2 uv;
+    V3 wi;            // local
+    uint32_t shape, prim;   // prim = global primitive index
+    V3 toWorld(V3 v) const { return sh.toWorld(v); }
+    V3 toLocal(V3 v) const { return sh.toLocal(v); }
+};
+
+// DirectSamplingRecord (include/mitsuba/render/common.h) fields used by `path`
+struct DRec {
+    V3 ref, refN;
+    V3 p, n, d;
+    float dist, pdf;
+    int measure;      // 0 solid angle, 1 discrete, 2 area
+    int emitter;      // index or -1
+};
+enum { kSolidAngle = 0, kDiscrete = 1 };
+
+// DiscreteDistribution: include/mitsuba/core/pmf.h:101-188
+struct Pmf {
+    std::vector<float> cdf;   // cdf[0] = 0
+    float sum, normalization;
+    Pmf() : sum(0), normalization(0) { cdf.push_back(0.0f); }
+    void append(float v) { cdf.push_back(cdf.back() + v); }
+    float normalize() {
+        sum = cdf.back();
+        if (sum > 0) {
+            normalization = 1.0f / sum;
+            for (size_t i = 1; i < cdf.size(); ++i) cdf[i] *= normalization;
+            cdf.back() = 1.0f;
+        } else normalization = 0.0f;
+        return sum;
+    }
+    float operator[](size_t i) const { return cdf[i + 1] - cdf[i]; }
+    size_t sample(float v) const {                                   // pmf.h:124-136
+        size_t entry = std::lower_bound(cdf.begin(), cdf.end(), v) - cdf.begin();
+        size_t index = std::min(cdf.size() - 2, (size_t) std::max((ptrdiff_t) 0, (ptrdiff_t) entry - 1));
+        while ((*this)[index] == 0 && index < cdf.size() - 1) ++index;
+        return index;
+    }
+    size_t sampleReuse(float &v, float &pdf) const {                 // pmf.h:183-188
+        size_t index = sample(v);
+        pdf = (*this)[index];
+        v = (v - cdf[index]) / (cdf[index + 1] - cdf[index]);
+        return index;
+    }
+    size_t sampleReuse(float &v) const { float p; return sampleReuse(v, p); }
+};
+
+struct Film {
+    int w, h, border;            // crop size, border = ceil(radius - 0.5)   (rfilter.cpp:50)
+    float radius, scaleFactor;
+    float table[33];             // MTS_FILTER_RESOLUTION = 31 -> 32 entries (+1 guard)
+    std::vector<float> data;     // (h+2b) x (w+2b) x 5
+    uint64_t bad;
+    int stride() const { return w + 2 * border; }
+};
+
+struct Scene {
+    MtsbSceneDesc sd;            // pointers refer to the owned copies below
+    std::vector<MtsbShape> shapes;
+    std::vector<MtsbMaterial> materials;
+    std::vector<MtsbEmitter> emitters;
+    std::vector<float> positions, normals, texcoords;
+    std::vector<uint32_t> indices;
+    std::vector<uint32_t> triShape;           // global prim -> shape
+    Accel accel;
+    ExternalTraceFn ext; void *extUser;
+    Pmf emitterPdf;                            // scene.cpp:375-381
+    std::vector<Pmf> areaPdf;                  // per shape that is an emitter (trimesh.cpp:388-403)
+    std::vector<float> invArea;                // per shape
+    int envEmitter;
+    V3 bsphereC; float bsphereR;               // constant.cpp:67-71
+    // sensor (closed form of perspective.cpp:127-150)
+    float nearX, nearY;                        // near*tan(xfov/2), same / aspect
+    Film film;
+    Scene() : ext(nullptr), extUser(nullptr), envEmitter(-1) {}
+
+    V3 pos(uint32_t i) const { return V3(positions[3 * i], positions[3 * i + 1], positions[3 * i + 2]); }
+    V3 nrm(uint32_t i) const { return V3(normals[3 * i], normals[3 * i + 1], normals[3 * i + 2]); }
+    P2 tex(uint32_t i) const { return P2{texcoords[2 * i], texcoords[2 * i + 1]}; }
+};
+
+inline V3 xformPoint(const float *m, V3 p) {     // affine part of a row-major 4x4
+    return V3(m[0] * p.x + m[1] * p.y + m[2] * p.z + m[3],
+              m[4] * p.x + m[5] * p.y + m[6] * p.z + m[7],
+              m[8] * p.x + m[9] * p.y + m[10] * p.z + m[11]);
+}
+inline V3 xformVec(const float *m, V3 v) {
+    return V3(m[0] * v.x + m[1] * v.y + m[2] * v.z,
+              m[4] * v.x + m[5] * v.y + m[6] * v.z,
+              m[8] * v.x + m[9] * v.y + m[10] * v.z);
+}
+
+// ShapeKDTree::fillIntersectionRecord<true>: include/mitsuba/render/skdtree.h:343-430
+inline void fillIntersection(const Scene &sc, const MtsbRay &ray, const MtsbHit &hit, Its &its) {
+    its.valid = hit.prim != MTSB_NO_HIT;
+    its.t = hit.t;
+    if (!its.valid) return;
+    uint32_t s = sc.triShape[hit.prim];
+    const MtsbShape &sh = sc.shapes[s];
+    const uint32_t *ix = &sc.indices[3 * (size_t) hit.prim];
+    const V3 b(1 - hit.u - hit.v, hit.u, hit.v);
+    const V3 p0 = sc.pos(ix[0]), p1 = sc.pos(ix[1]), p2 = sc.pos(ix[2]);
+    its.p = p0 * b.x + p1 * b.y + p2 * b.z;
+    V3 side1 = p1 - p0, side2 = p2 - p0;
+    V3 faceNormal = cross(side1, side2);
+    float len = length(faceNormal);
+    if (!isZero(faceNormal)) faceNormal = faceNormal / len;
+    V3 dpdu = side1;
+    V3 shN;
+    if (sh.has_normals) {
+        V3 n0 = sc.nrm(ix[0]), n1 = sc.nrm(ix[1]), n2 = sc.nrm(ix[2]);
+        shN = normalize(n0 * b.x + n1 * b.y + n2 * b.z);
+        if (dot(faceNormal, shN) < 0) faceNormal = -faceNormal;
+    } else shN = faceNormal;
+    its.geoN = faceNormal;
+    if (sh.has_texcoords && !sc.texcoords.empty()) {
+        P2 t0 = sc.tex(ix[0]), t1 = sc.tex(ix[1]), t2 = sc.tex(ix[2]);
+        its.uv = P2{t0.x * b.x + t1.x * b.y + t2.x * b.z, t0.y * b.x + t1.y * b.y + t2.y * b.z};
+    } else its.uv = P2{b.y, b.z};
+    its.shape = s; its.prim = hit.prim;
+    its.sh = shadingFrame(shN, dpdu);
+    its.wi = its.toLocal(-V3(ray.d[0], ray.d[1], ray.d[2]));
+}
+
+// ---- emitters ----------------------------------------------------------------
+// AreaLight::eval  src/emitters/area.cpp:104-109
+inline V3 areaEval(const MtsbEmitter &e, V3 shN, V3 d) {
+    if (dot(shN, d) <= 0) return V3(0.0f);
+    return rgb(e.radiance);
+}
+
+// BSphere::rayIntersect  include/mitsuba/core/bsphere.h:88-95
+inline bool bsphereIntersect(V3 c, float r, V3 o, V3 d, float &nearT, float &farT) {
+    V3 oc = o - c;
+    float A = lengthSquared(d), B = 2 * dot(oc, d), C = lengthSquared(oc) - r * r;
+    return solveQuadratic(A, B, C, nearT, farT);
+}
+
+// Emitter::sampleDirect for the three emitter types; returns value (radiance/pdf)
+inline V3 emitterSampleDirect(const Scene &sc, int ei, DRec &dRec, P2 u) {
+    const MtsbEmitter &e = sc.emitters[ei];
+    if (e.type == MTSB_EMITTER_AREA) {
+        // area.cpp:158-173 -> Shape::sampleDirect shape.cpp:102-115 -> TriMesh::samplePosition
+        // trimesh.cpp:412-423 -> Triangle::sample triangle.cpp:24-62
+        const MtsbShape &sh = sc.shapes[e.shape];
+        float sy = u.y;
+        size_t index = sc.areaPdf[e.shape].sampleReuse(sy);
+        const uint32_t *ix = &sc.indices[3 * ((size_t) sh.first_tri + index)];
+        V3 p0 = sc.pos(ix[0]), p1 = sc.pos(ix[1]), p2 = sc.pos(ix[2]);
+        P2 bary = squareToUniformTriangle(P2{u.x, sy});
+        V3 sideA = p1 - p0, sideB = p2 - p0;
+        dRec.p = p0 + (sideA * bary.x) + (sideB * bary.y);
+        if (sh.has_normals) {
+            V3 n0 = sc.nrm(ix[0]), n1 = sc.nrm(ix[1]), n2 = sc.nrm(ix[2]);
+            dRec.n = normalize(n0 * (1.0f - bary.x - bary.y) + n1 * bary.x + n2 * bary.y);
+        } else dRec.n = normalize(cross(sideA, sideB));
+        dRec.pdf = sc.invArea[e.shape];
+        dRec.d = dRec.p - dRec.ref;
+        float distSquared = lengthSquared(dRec.d);
+        dRec.dist = std::sqrt(distSquared);
+        dRec.d = dRec.d / dRec.dist;
+        float dp = absDot(dRec.d, dRec.n);
+        dRec.pdf *= dp != 0 ? (distSquared / dp) : 0.0f;
+        dRec.measure = kSolidAngle;
+        if (dot(dRec.d, dRec.refN) >= 0 && dot(dRec.d, dRec.n) < 0 && dRec.pdf != 0)
+            return rgb(e.radiance) / dRec.pdf;
+        dRec.pdf = 0.0f;
+        return V3(0.0f);
+    } else if (e.type == MTSB_EMITTER_POINT) {
+        // point.cpp:131-147
+        dRec.p = rgb(e.position);
+        dRec.pdf = 1.0f; dRec.measure = kDiscrete;
+        dRec.d = dRec.p - dRec.ref;
+        dRec.dist = length(dRec.d);
+        float invDist = 1.0f / dRec.dist;
+        dRec.d *= invDist;
+        dRec.n = V3(0.0f);
+        return rgb(e.radiance) * (invDist * invDist);
+    } else {
+        // constant.cpp:173-215
+        V3 d; float pdf;
+        if (!isZero(dRec.refN)) {
+            d = squareToCosineHemisphere(u);
+            pdf = squareToCosineHemispherePdf(d);
+            d = frameFromNormal(dRec.refN).toWorld(d);
+        } else {
+            d = squareToUniformSphere(u);
+            pdf = kInvFourPi;
+        }
+        float nearT, farT;
+        dRec.pdf = 0.0f;
+        if (!bsphereIntersect(sc.bsphereC, sc.bsphereR, dRec.ref, d, nearT, farT)) return V3(0.0f);
+        if (!(nearT < 0 && farT > 0)) return V3(0.0f);
+        dRec.p = dRec.ref + d * farT;
+        dRec.n = normalize(sc.bsphereC - dRec.p);
+        dRec.measure = kSolidAngle;
+        dRec.d = d; dRec.dist = farT; dRec.pdf = pdf;
+        if (!isZero(dRec.refN) && dot(dRec.d, dRec.refN) <= 0) return V3(0.0f);
+        return rgb(e.radiance) / pdf;
+    }
+}
+
+// Emitter::pdfDirect
+inline float emitterPdfDirect(const Scene &sc, int ei, const DRec &dRec) {
+    const MtsbEmitter &e = sc.emitters[ei];
+    if (e.type == MTSB_EMITTER_AREA) {
+        // area.cpp:175-182 -> Shape::pdfDirect shape.cpp:117-126
+        if (dot(dRec.d, dRec.refN) >= 0 && dot(dRec.d, dRec.n) < 0) {
+            float pdfPos = sc.invArea[e.shape];
+            if (dRec.measure == kSolidAngle) return pdfPos * (dRec.dist * dRec.dist) / absDot(dRec.d, dRec.n);
+            return 0.0f;
+        }
+        return 0.0f;
+    } else if (e.type == MTSB_EMITTER_POINT) {
+        return dRec.measure == kDiscrete ? 1.0f : 0.0f;                 // point.cpp:149-151
+    } else {
+        // constant.cpp:217-232
+        float pdfSA;
+        if (!isZero(dRec.refN)) pdfSA = kInvPi * std::max(0.0f, dot(dRec.d, dRec.refN));
+        else pdfSA = kInvFourPi;
+        return dRec.measure == kSolidAngle ? pdfSA : 0.0f;
+    }
+}
+
+// Scene::sampleEmitterDirect scene.cpp:828-855 (visibility test done by the caller so that the
+// unit tests can look at the unoccluded record)
+inline V3 sampleEmitterDirectNoVis(const Scene &sc, DRec &dRec, P2 u) {
+    dRec.emitter = -1; dRec.pdf = 0;
+    if (sc.emitters.empty()) return V3(0.0f);
+    float emPdf;
+    float sx = u.x;
+    size_t index = sc.emitterPdf.sampleReuse(sx, emPdf);
+    V3 value = emitterSampleDirect(sc, (int) index, dRec, P2{sx, u.y});
+    if (dRec.pdf != 0) {
+        dRec.emitter = (int) index;
+        dRec.pdf *= emPdf;
+        value = value / emPdf;
+        return value;
+    }
+    return V3(0.0f);
+}
+// Scene::pdfEmitterDirect scene.cpp:975-978, pdfEmitterDiscrete scene.h:852-854
+inline float pdfEmitterDirect(const Scene &sc, const DRec &dRec) {
+    return emitterPdfDirect(sc, dRec.emitter, dRec) * sc.emitters[dRec.emitter].sampling_weight * sc.emitterPdf.normalization;
+}
+
+// ---- sensor: PerspectiveCamera::sampleRayDifferential perspective.cpp:286-317 ----
+inline void sensorRay(const Scene &sc, P2 samplePos, MtsbRay &ray) {
+    const MtsbSensor &se = sc.sd.sensor;
+    // near-plane point: closed form of m_sampleToCamera(Point(px/cropW, py/cropH, 0)) (:127-136,:296-298)
+    float a = (samplePos.x + (float) se.crop_x) / (float) se.film_width;
+    float b = (samplePos.y + (float) se.crop_y) / (float) se.film_height;
+    V3 nearP((1.0f - 2.0f * a) * sc.nearX, (1.0f - 2.0f * b) * sc.nearY, se.near_clip);
+    V3 d = normalize(nearP);
+    float invZ = 1.0f / d.z;
+    ray.mint = se.near_clip * invZ;
+    ray.maxt = se.far_clip * invZ;
+    V3 o = xformPoint(se.to_world, V3(0.0f));
+    V3 wd = xformVec(se.to_world, d);
+    ray.o[0] = o.x; ray.o[1] = o.y; ray.o[2] = o.z;
+    ray.d[0] = wd.x; ray.d[1] = wd.y; ray.d[2] = wd.z;
+}
+
+// ---- film: ReconstructionFilter::configure rfilter.cpp:36-55; GaussianFilter::eval gaussian.cpp:50-55;
+//      BoxFilter box.cpp:36-50; ImageBlock::put imageblock.h:143-206 --------------------------------
+inline float rfilterEval(const MtsbSensor &se, float x) {
+    if (se.rfilter == MTSB_RFILTER_GAUSSIAN) {
+        float alpha = -1.0f / (2.0f * se.rfilter_stddev * se.rfilter_stddev);
+        return std::max(0.0f, std::exp(alpha * x * x) - std::exp(alpha * se.rfilter_radius * se.rfilter_radius));
+    }
+    return std::fabs(x) <= se.rfilter_radius ? 1.0f : 0.0f;
+}
+inline void filmInit(Film &f, const MtsbSensor &se) {
+    const int RES = 31;
+    f.w = se.crop_width; f.h = se.crop_height;
+    f.radius = se.rfilter_radius;
+    float sum = 0.0f;
+    for (int i = 0; i < RES; ++i) { float v = rfilterEval(se, (f.radius * i) / RES); f.table[i] = v; sum += v; }
+    f.table[RES] = 0.0f; f.table[RES + 1] = 0.0f;
+    f.scaleFactor = RES / f.radius;
+    f.border = (int) std::ceil(f.radius - 0.5f);
+    sum *= 2 * f.radius / RES;
+    float normalization = 1.0f / sum;
+    for (int i = 0; i < RES; ++i) f.table[i] *= normalization;
+    f.data.assign((size_t) (f.h + 2 * f.border) * (f.w + 2 * f.border) * 5, 0.0f);
+    f.bad = 0;
+}
+inline float filmEvalDiscretized(const Film &f, float x) {
+    return f.table[std::min((int) std::fabs(x * f.scaleFactor), 31)];
+}
+// put into a buffer covering [ox-border, ox+bw+border) x [oy-border, oy+bh+border) (block semantics)
+inline bool blockPut(const Film &f, float *buf, int ox, int oy, int bw, int bh, P2 _pos, const float *value5) {
+    for (int i = 0; i < 5; ++i) if (!std::isfinite(value5[i])) return false;
+    const int sx = bw + 2 * f.border, sy = bh + 2 * f.border;
+    const float px = _pos.x - 0.5f - (ox - f.border), py = _pos.y - 0.5f - (oy - f.border);
+    int minx = std::max((int) std::ceil(px - f.radius), 0), miny = std::max((int) std::ceil(py - f.radius), 0);
+    int maxx = std::min((int) std::floor(px + f.radius), sx - 1), maxy = std::min((int) std::floor(py + f.radius), sy - 1);
+    float wx[16], wy[16];
+    for (int x = minx, i = 0; x <= maxx; ++x) wx[i++] = filmEvalDiscretized(f, x - px);
+    for (int y = miny, i = 0; y <= maxy; ++y) wy[i++] = filmEvalDiscretized(f, y - py);
+    for (int y = miny, yr = 0; y <= maxy; ++y, ++yr) {
+        float *dest = buf + ((size_t) y * sx + minx) * 5;
+        for (int x = minx, xr = 0; x <= maxx; ++x, ++xr) {
+            const float weight = wx[xr] * wy[yr];
+            for (int k = 0; k < 5; ++k) *dest++ += weight * value5[k];
+        }
+    }
+    return true;
+}
+
+}  // namespace orc
