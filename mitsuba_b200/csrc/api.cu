@@ -1,0 +1,273 @@
+// api.cu -- C ABI: library state, scene creation / destruction (include/mtsb200.h).
+// mtsb_scene_create replaces Scene::initialize (reference src/librender/scene.cpp:322-384):
+// it copies the flattened scene to the device, builds the sampling tables the emitters need
+// (DiscreteDistribution, include/mitsuba/core/pmf.h:101-188; TriMesh::prepareSamplingTable,
+// src/librender/trimesh.cpp:388-403) and builds the BVH on the GPU.
+#include "scene.h"
+#include "trace.cuh"
+#include <map>
+#include <mutex>
+#include <cmath>
+#include <cstring>
+
+namespace mtsb {
+
+static thread_local std::string g_error;
+static int g_device = -1;
+static int g_sm_count = 0;
+
+void set_error(const std::string &s) { g_error = s; }
+int cuda_fail(cudaError_t e, const char *what, const char *file, int line) {
+    char buf[512];
+    snprintf(buf, sizeof(buf), "CUDA error %d (%s) at %s:%d in %s", (int) e, cudaGetErrorString(e), file, line, what);
+    g_error = buf;
+    cudaGetLastError();
+    return e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver ? MTSB_ERR_NO_DEVICE : MTSB_ERR_CUDA;
+}
+
+static int ensure_device() {
+    if (g_device >= 0) return MTSB_OK;
+    return mtsb_init(-1);
+}
+
+// ring of work counters for the persistent kernels
+static std::mutex g_counter_mutex;
+static std::map<int, std::pair<uint32_t *, uint32_t>> g_counters;   // device -> (ring, next)
+static const uint32_t kCounterRing = 4096;
+
+uint32_t *trace_work_counter(Scene *s, cudaStream_t st) {
+    std::lock_guard<std::mutex> g(g_counter_mutex);
+    auto &e = g_counters[s->device];
+    if (!e.first) {
+        if (cudaMalloc((void **) &e.first, kCounterRing * sizeof(uint32_t)) != cudaSuccess) { set_error("cudaMalloc(work counters) failed"); return nullptr; }
+        e.second = 0;
+    }
+    uint32_t *p = e.first + (e.second++ % kCounterRing);
+    if (cudaMemsetAsync(p, 0, sizeof(uint32_t), st) != cudaSuccess) { set_error("cudaMemsetAsync(work counter) failed"); return nullptr; }
+    return p;
+}
+
+int device_sm_count() { return g_sm_count > 0 ? g_sm_count : 148; }
+
+int trace_grid(Scene *s, const void *kernel) {
+    static std::mutex m;
+    static std::map<const void *, int> cache;
+    std::lock_guard<std::mutex> g(m);
+    auto it = cache.find(kernel);
+    if (it != cache.end()) return it->second;
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, MTSB_TRACE_BLOCK, 0) != cudaSuccess || per_sm <= 0) {
+        set_error("occupancy query failed"); cudaGetLastError(); return -1;
+    }
+    int grid = per_sm * (g_sm_count > 0 ? g_sm_count : 148);
+    cache[kernel] = grid;
+    return grid;
+}
+
+}  // namespace mtsb
+
+using namespace mtsb;
+
+extern "C" int mtsb_abi_version(void) { return MTSB_ABI_VERSION; }
+extern "C" const char *mtsb_last_error(void) { return g_error.c_str(); }
+
+extern "C" int mtsb_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+extern "C" int mtsb_init(int device) {
+    int n = mtsb_device_count();
+    if (n <= 0) { set_error("no CUDA device present (this library has no CPU fallback)"); return MTSB_ERR_NO_DEVICE; }
+    if (device < 0) {
+        if (cudaGetDevice(&device) != cudaSuccess) device = 0;
+    }
+    if (device >= n) { set_error("mtsb_init: device index out of range"); return MTSB_ERR_INVALID; }
+    MTSB_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    MTSB_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) { set_error(std::string("device is not sm_100-class: ") + prop.name); return MTSB_ERR_NO_DEVICE; }
+    g_device = device; g_sm_count = prop.multiProcessorCount;
+    MTSB_CUDA(cudaFree(0));
+    return MTSB_OK;
+}
+
+static int validate(const MtsbSceneDesc *d) {
+    if (!d) { set_error("scene description is NULL"); return MTSB_ERR_INVALID; }
+    if (d->abi_version != MTSB_ABI_VERSION) { set_error("scene description: ABI version mismatch"); return MTSB_ERR_INVALID; }
+    if (d->n_tris > 0xFFFFFFF0ull / 3 || d->n_vertices > 0xFFFFFFF0ull) { set_error("scene too large for 32-bit primitive ids"); return MTSB_ERR_INVALID; }
+    if ((d->n_shapes && !d->shapes) || (d->n_materials && !d->materials) || (d->n_emitters && !d->emitters) ||
+        (d->n_vertices && !d->positions) || (d->n_tris && !d->indices)) { set_error("scene description: NULL array"); return MTSB_ERR_INVALID; }
+    uint64_t tri_sum = 0;
+    for (uint32_t i = 0; i < d->n_shapes; ++i) {
+        const MtsbShape &sh = d->shapes[i];
+        if ((uint64_t) sh.first_tri != tri_sum) { set_error("shapes must tile the triangle array in order"); return MTSB_ERR_INVALID; }
+        tri_sum += sh.n_tris;
+        if (sh.material >= (int32_t) d->n_materials || sh.emitter >= (int32_t) d->n_emitters) { set_error("shape refers to a missing material/emitter"); return MTSB_ERR_INVALID; }
+        if ((uint64_t) sh.first_vertex + sh.n_vertices > d->n_vertices) { set_error("shape vertex range out of bounds"); return MTSB_ERR_INVALID; }
+        if (sh.has_normals && !d->normals) { set_error("shape has_normals but normals == NULL"); return MTSB_ERR_INVALID; }
+    }
+    if (tri_sum != d->n_tris) { set_error("shape triangle counts do not add up to n_tris"); return MTSB_ERR_INVALID; }
+    for (uint32_t i = 0; i < d->n_materials; ++i) {
+        const MtsbMaterial &m = d->materials[i];
+        if (m.type > MTSB_BSDF_NULL || m.distribution > MTSB_DISTR_GGX || m.back >= (int32_t) d->n_materials) { set_error("bad material record"); return MTSB_ERR_INVALID; }
+    }
+    int n_env = 0;
+    for (uint32_t i = 0; i < d->n_emitters; ++i) {
+        const MtsbEmitter &e = d->emitters[i];
+        if (e.type > MTSB_EMITTER_CONSTANT) { set_error("bad emitter type"); return MTSB_ERR_INVALID; }
+        if (e.type == MTSB_EMITTER_AREA && (e.shape < 0 || e.shape >= (int32_t) d->n_shapes)) { set_error("area emitter without a shape"); return MTSB_ERR_INVALID; }
+        if (e.type == MTSB_EMITTER_CONSTANT && ++n_env > 1) { set_error("only one environment emitter is allowed (scene.cpp:575-579)"); return MTSB_ERR_INVALID; }
+    }
+    const MtsbSensor &se = d->sensor;
+    if (se.film_width <= 0 || se.film_height <= 0 || se.crop_width <= 0 || se.crop_height <= 0 || se.crop_x < 0 || se.crop_y < 0 ||
+        se.crop_x + se.crop_width > se.film_width || se.crop_y + se.crop_height > se.film_height) { set_error("bad film / crop size"); return MTSB_ERR_INVALID; }
+    if (!(se.rfilter_radius > 0) || se.rfilter_radius > 7.5f || se.rfilter > MTSB_RFILTER_BOX) { set_error("bad reconstruction filter"); return MTSB_ERR_INVALID; }
+    if (!(se.fov_x_deg > 0 && se.fov_x_deg < 180) || !(se.near_clip > 0) || !(se.far_clip > se.near_clip)) { set_error("bad sensor parameters"); return MTSB_ERR_INVALID; }
+    return MTSB_OK;
+}
+
+static float rfilter_eval(const MtsbSensor &se, float x) {
+    if (se.rfilter == MTSB_RFILTER_GAUSSIAN) {      // gaussian.cpp:50-55
+        float alpha = -1.0f / (2.0f * se.rfilter_stddev * se.rfilter_stddev);
+        return std::max(0.0f, std::exp(alpha * x * x) - std::exp(alpha * se.rfilter_radius * se.rfilter_radius));
+    }
+    return std::fabs(x) <= se.rfilter_radius ? 1.0f : 0.0f;   // box.cpp:36-50
+}
+
+extern "C" int mtsb_scene_create(const MtsbSceneDesc *d, mtsb_scene_t *out) {
+    if (!out) { set_error("mtsb_scene_create: out == NULL"); return MTSB_ERR_INVALID; }
+    *out = nullptr;
+    int rc = validate(d);
+    if (rc) return rc;
+    rc = ensure_device();
+    if (rc) return rc;
+    Scene *s = new Scene();
+    s->device = g_device;
+    auto fail = [&](int code) { mtsb_scene_destroy(reinterpret_cast<mtsb_scene_t>(s)); return code; };
+    if (cudaSetDevice(s->device) != cudaSuccess) return fail(MTSB_ERR_CUDA);
+    if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess) { set_error("cudaStreamCreate failed"); return fail(MTSB_ERR_CUDA); }
+    SceneView &v = s->v;
+    v.n_shapes = d->n_shapes; v.n_materials = d->n_materials; v.n_emitters = d->n_emitters;
+    v.sensor = d->sensor; v.integrator = d->integrator;
+    if ((rc = dev_upload(s, &v.positions, d->positions, 3 * (size_t) d->n_vertices))) return fail(rc);
+    if (d->normals) { if ((rc = dev_upload(s, &v.normals, d->normals, 3 * (size_t) d->n_vertices))) return fail(rc); } else v.normals = nullptr;
+    if (d->texcoords) { if ((rc = dev_upload(s, &v.texcoords, d->texcoords, 2 * (size_t) d->n_vertices))) return fail(rc); } else v.texcoords = nullptr;
+    if ((rc = dev_upload(s, &v.indices, d->indices, 3 * (size_t) d->n_tris))) return fail(rc);
+    if ((rc = dev_upload(s, &v.shapes, d->shapes, (size_t) d->n_shapes))) return fail(rc);
+    if ((rc = dev_upload(s, &v.materials, d->materials, (size_t) d->n_materials))) return fail(rc);
+    if ((rc = dev_upload(s, &v.emitters, d->emitters, (size_t) d->n_emitters))) return fail(rc);
+    {   // primitive -> shape map (ShapeKDTree::findShape, skdtree.h:205-210, as a table)
+        std::vector<uint32_t> ts((size_t) d->n_tris);
+        for (uint32_t i = 0; i < d->n_shapes; ++i)
+            for (uint32_t j = 0; j < d->shapes[i].n_tris; ++j) ts[(size_t) d->shapes[i].first_tri + j] = i;
+        if ((rc = dev_upload(s, &v.tri_shape, ts.data(), ts.size()))) return fail(rc);
+    }
+    {   // emitter selection pmf (scene.cpp:375-381) and per-mesh area pmfs (trimesh.cpp:388-403)
+        std::vector<float> cdf(1, 0.0f);
+        v.env_emitter = -1;
+        for (uint32_t i = 0; i < d->n_emitters; ++i) {
+            cdf.push_back(cdf.back() + d->emitters[i].sampling_weight);
+            if (d->emitters[i].type == MTSB_EMITTER_CONSTANT) v.env_emitter = (int) i;
+        }
+        float sum = cdf.back();
+        v.emitter_norm = 0.0f;
+        if (d->n_emitters && sum > 0) {
+            v.emitter_norm = 1.0f / sum;
+            for (size_t i = 1; i < cdf.size(); ++i) cdf[i] *= v.emitter_norm;
+            cdf.back() = 1.0f;
+        }
+        if ((rc = dev_upload(s, &v.emitter_cdf, cdf.data(), cdf.size()))) return fail(rc);
+        std::vector<float> acdf; std::vector<uint32_t> aoff(d->n_shapes, 0xFFFFFFFFu); std::vector<float> inv_area(d->n_shapes, 0.0f);
+        for (uint32_t si = 0; si < d->n_shapes; ++si) {
+            const MtsbShape &sh = d->shapes[si];
+            if (sh.emitter < 0) continue;
+            aoff[si] = (uint32_t) acdf.size();
+            size_t base = acdf.size();
+            acdf.push_back(0.0f);
+            for (uint32_t j = 0; j < sh.n_tris; ++j) {
+                const uint32_t *ix = d->indices + 3 * ((size_t) sh.first_tri + j);
+                const float *p0 = d->positions + 3 * (size_t) ix[0], *p1 = d->positions + 3 * (size_t) ix[1], *p2 = d->positions + 3 * (size_t) ix[2];
+                volatile float ax = p1[0] - p0[0], ay = p1[1] - p0[1], az = p1[2] - p0[2];
+                volatile float bx = p2[0] - p0[0], by = p2[1] - p0[1], bz = p2[2] - p0[2];
+                volatile float cx = ay * bz - az * by, cy = az * bx - ax * bz, cz = ax * by - ay * bx;
+                volatile float area = 0.5f * std::sqrt(cx * cx + cy * cy + cz * cz);      // Triangle::surfaceArea, triangle.cpp:64-70
+                acdf.push_back(acdf.back() + area);
+            }
+            float total = acdf.back();
+            if (total > 0) {
+                float norm = 1.0f / total;
+                for (size_t i = base + 1; i < acdf.size(); ++i) acdf[i] *= norm;
+                acdf.back() = 1.0f;
+            }
+            inv_area[si] = 1.0f / total;
+        }
+        if ((rc = dev_upload(s, &v.area_cdf, acdf.data(), acdf.size()))) return fail(rc);
+        if ((rc = dev_upload(s, &v.area_cdf_offset, aoff.data(), aoff.size()))) return fail(rc);
+        if ((rc = dev_upload(s, &v.inv_area, inv_area.data(), inv_area.size()))) return fail(rc);
+    }
+    if ((rc = build_bvh(s, v.positions, v.indices, d->n_tris))) return fail(rc);
+    {   // Scene::m_aabb -> bounding sphere of the environment emitter (scene.cpp:388-414, constant.cpp:67-71)
+        float lo[3], hi[3];
+        for (int k = 0; k < 3; ++k) { lo[k] = d->n_tris ? v.box_lo[k] : 0.0f; hi[k] = d->n_tris ? v.box_hi[k] : 0.0f; }
+        auto grow = [&](const float *p) { for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], p[k]); hi[k] = std::max(hi[k], p[k]); } };
+        float cam[3] = {d->sensor.to_world[3], d->sensor.to_world[7], d->sensor.to_world[11]};
+        grow(cam);
+        for (uint32_t i = 0; i < d->n_emitters; ++i) if (d->emitters[i].type == MTSB_EMITTER_POINT) grow(d->emitters[i].position);
+        float r2 = 0;
+        for (int k = 0; k < 3; ++k) { v.bsphere_c[k] = (hi[k] + lo[k]) * 0.5f; float e = v.bsphere_c[k] - hi[k]; r2 += e * e; }
+        v.bsphere_r = std::max(1e-4f, std::sqrt(r2) * 1.5f);
+    }
+    {   // perspective projection constants and the film / filter table (rfilter.cpp:36-55)
+        const MtsbSensor &se = d->sensor;
+        double aspect = (double) se.film_width / (double) se.film_height;
+        double tan_half = std::tan(0.5 * (double) se.fov_x_deg * 3.14159265358979323846 / 180.0);
+        v.near_x = (float) ((double) se.near_clip * tan_half);
+        v.near_y = (float) ((double) se.near_clip * tan_half / aspect);
+        const int RES = 31;
+        float sum = 0.0f;
+        for (int i = 0; i < RES; ++i) { float val = rfilter_eval(se, (se.rfilter_radius * i) / RES); v.filter_table[i] = val; sum += val; }
+        v.filter_table[RES] = 0.0f;
+        sum *= 2 * se.rfilter_radius / RES;
+        float normalization = 1.0f / sum;
+        for (int i = 0; i < RES; ++i) v.filter_table[i] *= normalization;
+        v.filter_radius = se.rfilter_radius; v.filter_scale = RES / se.rfilter_radius;
+        v.film_border = (int) std::ceil(se.rfilter_radius - 0.5f);
+        v.film_w = se.crop_width; v.film_h = se.crop_height;
+        size_t nf = (size_t) (v.film_w + 2 * v.film_border) * (v.film_h + 2 * v.film_border) * 5;
+        if ((rc = dev_alloc(s, &v.film, nf))) return fail(rc);
+        if (cudaMemsetAsync(v.film, 0, nf * sizeof(float), s->stream) != cudaSuccess) return fail(MTSB_ERR_CUDA);
+        if ((rc = dev_alloc(s, &s->d_film_bad, 1))) return fail(rc);
+        if (cudaMemsetAsync(s->d_film_bad, 0, sizeof(unsigned long long), s->stream) != cudaSuccess) return fail(MTSB_ERR_CUDA);
+    }
+    s->info.n_emitters = d->n_emitters;
+    if (cudaStreamSynchronize(s->stream) != cudaSuccess) { set_error("scene upload failed"); return fail(MTSB_ERR_CUDA); }
+    *out = reinterpret_cast<mtsb_scene_t>(s);
+    return MTSB_OK;
+}
+
+extern "C" int mtsb_scene_info(mtsb_scene_t scene, MtsbSceneInfo *info) {
+    Scene *s = reinterpret_cast<Scene *>(scene);
+    if (!s || !info) { set_error("mtsb_scene_info: bad argument"); return MTSB_ERR_INVALID; }
+    *info = s->info;
+    return MTSB_OK;
+}
+
+extern "C" void mtsb_scene_destroy(mtsb_scene_t scene) {
+    Scene *s = reinterpret_cast<Scene *>(scene);
+    if (!s) return;
+    cudaSetDevice(s->device);
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    render_free(s);
+    for (void *p : s->allocs) cudaFree(p);
+    if (s->stream) cudaStreamDestroy(s->stream);
+    delete s;
+}
+
+extern "C" int mtsb_cancel(mtsb_scene_t scene) {
+    Scene *s = reinterpret_cast<Scene *>(scene);
+    if (!s) { set_error("mtsb_cancel: bad argument"); return MTSB_ERR_INVALID; }
+    s->cancel.store(1);
+    return MTSB_OK;
+}

@@ -1,0 +1,583 @@
+// render.cu -- wavefront formulation of MonteCarloIntegrator::renderBlock + MIPathTracer::Li
+// (reference: src/librender/integrator.cpp:196-244, src/integrators/path/path.cpp:121-296).
+//
+// One path sample = one slot of the SoA path state.  A pass renders `spp_pass` samples of every
+// pixel of a set of 32x32 tiles.  Per bounce the stages are separate kernels over queues:
+//
+//   k_trace<closest>   rays[cur]            -> hits                      (trace.cuh)
+//   k_sort             hits                 -> one queue per BSDF model (+ miss queue)
+//   k_shade<MODEL>     queue[MODEL]         -> emitter hit + MIS, Russian roulette, emitter
+//                                              sampling + BSDF eval (-> shadow queue),
+//                                              BSDF sampling (-> rays[1-cur])
+//   k_miss             queue[MISS]          -> environment term
+//   k_trace<any>       shadow queue         -> adds the pending contribution when unoccluded
+//
+// and at the end of the pass k_splat accumulates every tile in shared memory and adds it to
+// the film (ImageBlock::put + the overlap-add of BlockedRenderProcess::processResult).
+//
+// Loop restructuring with respect to path.cpp: the reference traces the BSDF ray inside
+// iteration k and then finishes iteration k (emitter hit with MIS :259-266, break on miss
+// :274, Russian roulette :278-288).  Here that tail runs at the head of the shading stage of
+// iteration k+1, in the same order, so every sample sees the same sequence of decisions.
+#include "render.cuh"
+#include "trace.cuh"
+#include "shading.h"
+#include "sensor.h"
+#include "rng.h"
+#include <cooperative_groups.h>
+#include <cstring>
+#include <algorithm>
+
+namespace cg = cooperative_groups;
+
+namespace mtsb {
+
+#define MTSB_TILE 32
+#define MTSB_SHADE_BLOCK 128
+
+__device__ __forceinline__ uint32_t queue_push(uint32_t *counter) {
+    cg::coalesced_group g = cg::coalesced_threads();
+    uint32_t base = 0;
+    if (g.thread_rank() == 0) base = atomicAdd(counter, g.size());
+    return g.shfl(base, 0) + g.thread_rank();
+}
+
+__device__ __forceinline__ uint32_t compact1by1(uint32_t x) {
+    x &= 0x55555555u; x = (x ^ (x >> 1)) & 0x33333333u; x = (x ^ (x >> 2)) & 0x0f0f0f0fu;
+    x = (x ^ (x >> 4)) & 0x00ff00ffu; x = (x ^ (x >> 8)) & 0x0000ffffu; return x;
+}
+
+__device__ __forceinline__ void store_ray(RayIn *rays, uint32_t i, const RayIn &r) {
+    reinterpret_cast<float4 *>(rays)[2 * (size_t) i] = make_float4(r.ox, r.oy, r.oz, r.mint);
+    reinterpret_cast<float4 *>(rays)[2 * (size_t) i + 1] = make_float4(r.dx, r.dy, r.dz, r.maxt);
+}
+__device__ __forceinline__ RayIn load_ray(const RayIn *rays, uint32_t i) {
+    const float4 a = reinterpret_cast<const float4 *>(rays)[2 * (size_t) i], b = reinterpret_cast<const float4 *>(rays)[2 * (size_t) i + 1];
+    RayIn r; r.ox = a.x; r.oy = a.y; r.oz = a.z; r.mint = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z; r.maxt = b.w; return r;
+}
+
+// slot -> pixel of the pass (Morton order inside the tile keeps a warp on a compact pixel patch)
+__device__ __forceinline__ bool slot_pixel(const SceneView &sc, const PathBuffers &pb, const PassInfo &ps, uint32_t slot,
+                                           int &px, int &py, uint32_t &s_local) {
+    const uint32_t per_tile = MTSB_TILE * MTSB_TILE * ps.spp_pass;
+    const uint32_t tile_local = slot / per_tile, r = slot % per_tile;
+    const uint32_t pix = r / ps.spp_pass; s_local = r % ps.spp_pass;
+    const int tile = pb.tiles[ps.tile_first + tile_local];
+    px = (tile % (int) ps.tiles_x) * MTSB_TILE + (int) compact1by1(pix);
+    py = (tile / (int) ps.tiles_x) * MTSB_TILE + (int) compact1by1(pix >> 1);
+    return px < sc.film_w && py < sc.film_h;
+}
+__device__ __forceinline__ SampleStream slot_stream(const SceneView &sc, const PassInfo &ps, int px, int py, uint32_t s_local) {
+    const uint64_t pixel = (uint64_t) (py + sc.sensor.crop_y) * (uint64_t) sc.sensor.film_width + (uint64_t) (px + sc.sensor.crop_x);
+    return SampleStream(ps.seed, (pixel << 24) | (uint64_t) (ps.s_first + s_local));
+}
+
+__global__ void k_pass_begin(PathBuffers pb) {
+    Counters *c = pb.ctr;
+    c->n_rays[0] = c->n_rays[1] = 0; c->n_shadow = 0;
+    for (int i = 0; i < Q_COUNT; ++i) c->n_q[i] = 0;
+}
+
+// integrator.cpp:218-241: pixel offset from the sampler, sensor ray, new radiance query
+__global__ void k_raygen(SceneView sc, PathBuffers pb, PassInfo ps, uint32_t n_slots) {
+    for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n_slots; slot += gridDim.x * blockDim.x) {
+        int px, py; uint32_t s_local;
+        const bool valid = slot_pixel(sc, pb, ps, slot, px, py, s_local);
+        if (!valid) { pb.refn_flags[slot] = make_float4(0, 0, 0, __uint_as_float(0u)); continue; }
+        float u[4];
+        slot_stream(sc, ps, px, py, s_local).block4(0, 0, u);
+        const float sx = (float) px + u[0], sy = (float) py + u[1];
+        RayIn ray;
+        sensor_ray(sc.sensor, sc.near_x, sc.near_y, sx, sy, ray);
+        pb.spos[slot] = make_float2(sx, sy);
+        pb.thr_eta[slot] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+        pb.L_bpdf[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        pb.refn_flags[slot] = make_float4(0, 0, 0, __uint_as_float(1u | PF_FIRST | PF_VALID));
+        const uint32_t q = queue_push(&pb.ctr->n_rays[0]);
+        store_ray(pb.rays[0], q, ray);
+        pb.ray_slot[0][q] = slot;
+    }
+}
+
+__global__ void k_bounce_prepare(PathBuffers pb, int cur) {
+    Counters *c = pb.ctr;
+    c->closest += c->n_rays[cur];
+    c->shadow += c->n_shadow;
+    c->n_shadow = 0; c->n_rays[1 - cur] = 0;
+    for (int i = 0; i < Q_COUNT; ++i) c->n_q[i] = 0;
+}
+__global__ void k_pass_end(PathBuffers pb) { Counters *c = pb.ctr; c->shadow += c->n_shadow; c->n_shadow = 0; }
+
+// bins the hits of this bounce by scattering model
+__global__ void k_sort(SceneView sc, PathBuffers pb, int cur) {
+    const uint32_t n = pb.ctr->n_rays[cur];
+    for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < n; q += gridDim.x * blockDim.x) {
+        const uint32_t prim = pb.hits[q].prim;
+        int which = Q_MISS;
+        if (prim != MTSB_NO_HIT_ID) {
+            const int mat = sc.shapes[sc.tri_shape[prim]].material;
+            if (mat < 0) which = Q_NULL;
+            else {
+                const MtsbMaterial &m = sc.materials[mat];
+                which = m.type == MTSB_BSDF_DIFFUSE ? Q_DIFFUSE : m.type == MTSB_BSDF_ROUGHCONDUCTOR ? Q_CONDUCTOR
+                      : m.type == MTSB_BSDF_ROUGHDIELECTRIC ? Q_DIELECTRIC : Q_NULL;
+                if ((m.flags & MTSB_MAT_TWOSIDED) && m.back >= 0 && sc.materials[m.back].type != m.type) which = Q_GENERIC;
+            }
+        }
+        const unsigned active = __activemask();
+        const unsigned peers = __match_any_sync(active, which);
+        const int leader = __ffs(peers) - 1;
+        uint32_t base = 0;
+        if ((int) (threadIdx.x & 31) == leader) base = atomicAdd(&pb.ctr->n_q[which], (uint32_t) __popc(peers));
+        base = __shfl_sync(peers, base, leader);
+        pb.q[which][base + (uint32_t) __popc(peers & ((1u << (threadIdx.x & 31)) - 1u))] = q;
+    }
+}
+
+struct RenderConst { int max_depth, rr_depth, strict_normals, hide_emitters; };
+
+template <int Q> __device__ __forceinline__ V3 eval_q(const MtsbMaterial *mats, int id, V3 wi, V3 wo) {
+    if (Q == Q_GENERIC) return bsdf_eval(mats, id, wi, wo);
+    const MtsbMaterial &m = resolve_twosided_eval(mats, mats[id], wi, wo);
+    if (Q == Q_DIFFUSE) return diffuse_eval(m, wi, wo);
+    if (Q == Q_CONDUCTOR) return roughconductor_eval(m, wi, wo);
+    if (Q == Q_DIELECTRIC) return roughdielectric_eval(m, wi, wo);
+    return V3(0.0f);
+}
+template <int Q> __device__ __forceinline__ float pdf_q(const MtsbMaterial *mats, int id, V3 wi, V3 wo) {
+    if (Q == Q_GENERIC) return bsdf_pdf(mats, id, wi, wo);
+    const MtsbMaterial &m = resolve_twosided_eval(mats, mats[id], wi, wo);
+    if (Q == Q_DIFFUSE) return diffuse_pdf(wi, wo);
+    if (Q == Q_CONDUCTOR) return roughconductor_pdf(m, wi, wo);
+    if (Q == Q_DIELECTRIC) return roughdielectric_pdf(m, wi, wo);
+    return 0.0f;
+}
+template <int Q> __device__ __forceinline__ bool sample_q(const MtsbMaterial *mats, int id, V3 wi, P2 u, float u1, BsdfSample &s) {
+    if (Q == Q_GENERIC) return bsdf_sample(mats, id, wi, u, u1, s);
+    const MtsbMaterial *m = &mats[id];
+    bool flip = false;
+    if ((m->flags & MTSB_MAT_TWOSIDED) && cosTheta(wi) < 0) { wi.z *= -1; flip = true; if (m->back >= 0) m = &mats[m->back]; }
+    bool ok;
+    if (Q == Q_DIFFUSE) ok = diffuse_sample(*m, wi, u, s);
+    else if (Q == Q_CONDUCTOR) ok = roughconductor_sample(*m, wi, u, s);
+    else if (Q == Q_DIELECTRIC) ok = roughdielectric_sample(*m, wi, u, u1, s);
+    else ok = false;
+    if (flip && ok && !isZero(s.weight) && s.pdf != 0) s.wo.z *= -1;
+    return ok;
+}
+
+template <int Q>
+__global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBuffers pb, PassInfo ps, RenderConst rc, int cur) {
+    const uint32_t n = pb.ctr->n_q[Q];
+    unsigned long long shade_events = 0, path_len = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t q = pb.q[Q][i];
+        const uint32_t slot = pb.ray_slot[cur][q];
+        const RayIn ray = load_ray(pb.rays[cur], q);
+        const uint4 hraw = reinterpret_cast<const uint4 *>(pb.hits)[q];
+        const uint32_t prim = hraw.x; const float hu = __uint_as_float(hraw.y), hv = __uint_as_float(hraw.z), ht = __uint_as_float(hraw.w);
+        const float4 te = pb.thr_eta[slot], lb = pb.L_bpdf[slot], rf = pb.refn_flags[slot];
+        V3 thr(te.x, te.y, te.z), L(lb.x, lb.y, lb.z);
+        float eta = te.w; const float bsdfPdfPrev = lb.w;
+        const V3 prevRefN(rf.x, rf.y, rf.z);
+        uint32_t fl = __float_as_uint(rf.w);
+        int depth = (int) (fl & PF_DEPTH_MASK);
+        const bool first = (fl & PF_FIRST) != 0;
+        const V3 rd(ray.dx, ray.dy, ray.dz);
+
+        Its its;
+        fill_intersection(sc, rd, prim, hu, hv, its);
+        const MtsbShape &shape = sc.shapes[its.shape];
+        const int mat = shape.material;
+        bool alive = true;
+
+        if (first) {
+            fl |= PF_ALPHA;
+            // path.cpp:150-152 (scattered is false on the first segment)
+            if (shape.emitter >= 0 && !rc.hide_emitters) L += thr * area_eval(sc.emitters[shape.emitter], its.sh.n, -rd);
+        } else {
+            // tail of the previous iteration: emitter hit by the BSDF ray (path.cpp:230-234, 259-266)
+            if (shape.emitter >= 0) {
+                const V3 value = area_eval(sc.emitters[shape.emitter], its.sh.n, -rd);
+                DRec dRec;
+                dRec.ref = V3(ray.ox, ray.oy, ray.oz); dRec.refN = prevRefN; dRec.p = its.p; dRec.n = its.sh.n;
+                dRec.d = rd; dRec.dist = ht; dRec.measure = MTSB_MEASURE_SOLID_ANGLE; dRec.emitter = shape.emitter;
+                const float lumPdf = pdf_emitter_direct(sc, dRec);
+                L += thr * value * mi_weight(bsdfPdfPrev, lumPdf);
+            }
+            // Russian roulette (path.cpp:278-288)
+            const int d0 = depth++;
+            if (d0 >= rc.rr_depth) {
+                const float qq = fminf(maxComp(thr) * eta * eta, 0.95f);
+                int px, py; uint32_t s_local; slot_pixel(sc, pb, ps, slot, px, py, s_local);
+                float u[4]; slot_stream(sc, ps, px, py, s_local).block4((uint32_t) d0, 1, u);
+                if (u[1] >= qq) alive = false;
+                else thr = thr / qq;
+            }
+            if (alive && !(depth <= rc.max_depth || rc.max_depth < 0)) alive = false;      // while condition :137
+        }
+        // path.cpp:158-167
+        if (alive && ((depth >= rc.max_depth && rc.max_depth > 0) ||
+                      (rc.strict_normals && dot(rd, its.geoN) * cosTheta(its.wi) >= 0))) alive = false;
+
+        bool spawned = false;
+        if (alive) {
+            ++shade_events;
+            const bool haveMat = (Q != Q_NULL) && mat >= 0;
+            DRec dRec;
+            dRec.ref = its.p; dRec.refN = V3(0.0f); dRec.emitter = -1;
+            float u[4] = {0, 0, 0, 0};
+            if (haveMat) {
+                int px, py; uint32_t s_local; slot_pixel(sc, pb, ps, slot, px, py, s_local);
+                const SampleStream ss = slot_stream(sc, ps, px, py, s_local);
+                ss.block4((uint32_t) depth, 0, u);
+                const MtsbMaterial &m0 = sc.materials[mat];
+                if (!bsdf_has_back_or_transmission(m0)) dRec.refN = its.sh.n;              // records.inl:175-179
+                // ---- direct illumination (path.cpp:174-202) ----
+                P2 ue; ue.x = u[0]; ue.y = u[1];
+                const V3 value = sample_emitter_direct(sc, dRec, ue);
+                if (dRec.pdf != 0 && !isZero(value)) {
+                    const V3 wo = its.sh.toLocal(dRec.d);
+                    const V3 bsdfVal = eval_q<Q>(sc.materials, mat, its.wi, wo);
+                    if (!isZero(bsdfVal) && (!rc.strict_normals || dot(its.geoN, dRec.d) * cosTheta(wo) > 0)) {
+                        const MtsbEmitter &em = sc.emitters[dRec.emitter];
+                        const bool onSurface = em.type != MTSB_EMITTER_POINT;
+                        const float bp = (onSurface && dRec.measure == MTSB_MEASURE_SOLID_ANGLE) ? pdf_q<Q>(sc.materials, mat, its.wi, wo) : 0.0f;
+                        const V3 contrib = thr * value * bsdfVal * mi_weight(dRec.pdf, bp);
+                        // shadow segment of Scene::sampleEmitterDirect (scene.cpp:840-846)
+                        RayIn sr; sr.ox = dRec.ref.x; sr.oy = dRec.ref.y; sr.oz = dRec.ref.z; sr.dx = dRec.d.x; sr.dy = dRec.d.y; sr.dz = dRec.d.z;
+                        sr.mint = MTSB_EPSILON; sr.maxt = dRec.dist * (1 - MTSB_SHADOW_EPSILON);
+                        const uint32_t sq = queue_push(&pb.ctr->n_shadow);
+                        store_ray(pb.srays, sq, sr);
+                        pb.scontrib[sq] = make_float4(contrib.x, contrib.y, contrib.z, __uint_as_float(slot));
+                    }
+                }
+                // ---- BSDF sampling (path.cpp:208-221) ----
+                float u1 = 0.0f;
+                if (Q == Q_DIELECTRIC || Q == Q_GENERIC) {
+                    bool need = (Q == Q_DIELECTRIC);
+                    if (Q == Q_GENERIC) need = sc.materials[bsdf_effective_material(sc.materials, mat, its.wi.z)].type == MTSB_BSDF_ROUGHDIELECTRIC;
+                    if (need) { float v[4]; ss.block4((uint32_t) depth, 1, v); u1 = v[0]; }
+                }
+                BsdfSample bs;
+                P2 ub; ub.x = u[2]; ub.y = u[3];
+                const bool ok = sample_q<Q>(sc.materials, mat, its.wi, ub, u1, bs);
+                if (ok && !isZero(bs.weight)) {
+                    fl |= PF_SCATTERED;
+                    const V3 wo = its.sh.toWorld(bs.wo);
+                    if (!(rc.strict_normals && dot(its.geoN, wo) * cosTheta(bs.wo) <= 0)) {
+                        RayIn nr; nr.ox = its.p.x; nr.oy = its.p.y; nr.oz = its.p.z; nr.dx = wo.x; nr.dy = wo.y; nr.dz = wo.z;
+                        nr.mint = MTSB_EPSILON; nr.maxt = MTSB_INF;
+                        const uint32_t nq = queue_push(&pb.ctr->n_rays[1 - cur]);
+                        store_ray(pb.rays[1 - cur], nq, nr);
+                        pb.ray_slot[1 - cur][nq] = slot;
+                        thr *= bs.weight; eta *= bs.eta;
+                        pb.thr_eta[slot] = make_float4(thr.x, thr.y, thr.z, eta);
+                        pb.L_bpdf[slot] = make_float4(L.x, L.y, L.z, bs.pdf);
+                        fl = (fl & ~(PF_DEPTH_MASK | PF_FIRST)) | ((uint32_t) depth & PF_DEPTH_MASK);
+                        pb.refn_flags[slot] = make_float4(dRec.refN.x, dRec.refN.y, dRec.refN.z, __uint_as_float(fl));
+                        spawned = true;
+                    }
+                }
+            }
+        }
+        if (!spawned) {
+            path_len += (unsigned long long) depth;
+            pb.L_bpdf[slot] = make_float4(L.x, L.y, L.z, 0.0f);
+            fl = (fl & ~PF_DEPTH_MASK) | ((uint32_t) depth & PF_DEPTH_MASK);
+            pb.refn_flags[slot] = make_float4(0, 0, 0, __uint_as_float(fl));
+        }
+    }
+    for (int o = 16; o; o >>= 1) { shade_events += __shfl_xor_sync(0xFFFFFFFFu, shade_events, o); path_len += __shfl_xor_sync(0xFFFFFFFFu, path_len, o); }
+    if ((threadIdx.x & 31) == 0) {
+        if (shade_events) atomicAdd(&pb.ctr->shade, shade_events);
+        if (path_len) atomicAdd(&pb.ctr->path_len, path_len);
+    }
+}
+
+// rays that left the scene: environment term (path.cpp:138-145 first segment; :237-246, 259-266 afterwards)
+__global__ void k_miss(SceneView sc, PathBuffers pb, RenderConst rc, int cur) {
+    const uint32_t n = pb.ctr->n_q[Q_MISS];
+    unsigned long long path_len = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t q = pb.q[Q_MISS][i];
+        const uint32_t slot = pb.ray_slot[cur][q];
+        float4 lb = pb.L_bpdf[slot];
+        const float4 rf = pb.refn_flags[slot];
+        const uint32_t fl = __float_as_uint(rf.w);
+        path_len += (unsigned long long) (fl & PF_DEPTH_MASK);
+        if (sc.env_emitter >= 0) {
+            const float4 te = pb.thr_eta[slot];
+            const V3 thr(te.x, te.y, te.z);
+            const V3 value = ld3(sc.emitters[sc.env_emitter].radiance);       // constant.cpp:242-244
+            if (fl & PF_FIRST) {
+                if (!rc.hide_emitters) { lb.x += thr.x * value.x; lb.y += thr.y * value.y; lb.z += thr.z * value.z; }
+            } else {
+                const RayIn ray = load_ray(pb.rays[cur], q);
+                // fillDirectSamplingRecord (constant.cpp:246-260): the ray must start inside the bounding sphere
+                float nearT, farT;
+                const V3 o(ray.ox, ray.oy, ray.oz), d(ray.dx, ray.dy, ray.dz);
+                if (bsphere_intersect(sc.bsphere_c, sc.bsphere_r, o, d, nearT, farT) && !(nearT > 0 || farT < 0)) {
+                    DRec dRec; dRec.ref = o; dRec.refN = V3(rf.x, rf.y, rf.z); dRec.p = o; dRec.n = V3(0.0f); dRec.d = d; dRec.dist = farT;
+                    dRec.measure = MTSB_MEASURE_SOLID_ANGLE; dRec.emitter = sc.env_emitter;
+                    const float w = mi_weight(lb.w, pdf_emitter_direct(sc, dRec));
+                    lb.x += thr.x * value.x * w; lb.y += thr.y * value.y * w; lb.z += thr.z * value.z * w;
+                }
+            }
+        }
+        lb.w = 0.0f;
+        pb.L_bpdf[slot] = lb;
+    }
+    for (int o = 16; o; o >>= 1) path_len += __shfl_xor_sync(0xFFFFFFFFu, path_len, o);
+    if ((threadIdx.x & 31) == 0 && path_len) atomicAdd(&pb.ctr->path_len, path_len);
+}
+
+// epilogue of the shadow-ray pass: unoccluded -> add the pending emitter contribution
+struct ShadowResolve {
+    const float4 *contrib; float4 *L_bpdf;
+    __device__ __forceinline__ void operator()(uint32_t i, const RayIn &, const HitOut &h) const {
+        if (h.prim != MTSB_NO_HIT_ID) return;
+        const float4 c = contrib[i];
+        const uint32_t slot = __float_as_uint(c.w);
+        float4 l = L_bpdf[slot];
+        l.x += c.x; l.y += c.y; l.z += c.z;
+        L_bpdf[slot] = l;
+    }
+};
+
+// ImageBlock::put for every sample of one 32x32 tile, accumulated in shared memory, then one
+// add per bordered pixel into the film (imageblock.h:143-206, renderproc.cpp:149-156).
+__global__ void __launch_bounds__(256) k_splat(SceneView sc, PathBuffers pb, PassInfo ps, unsigned long long *bad) {
+    extern __shared__ float s_tile[];
+    const int b = sc.film_border, side = MTSB_TILE + 2 * b;
+    const int n_acc = side * side * 5;
+    for (int i = threadIdx.x; i < n_acc; i += blockDim.x) s_tile[i] = 0.0f;
+    __syncthreads();
+    const int tile = pb.tiles[ps.tile_first + blockIdx.x];
+    const int ox = (tile % (int) ps.tiles_x) * MTSB_TILE, oy = (tile / (int) ps.tiles_x) * MTSB_TILE;
+    const int bw = min(MTSB_TILE, sc.film_w - ox), bh = min(MTSB_TILE, sc.film_h - oy);
+    const uint32_t per_tile = MTSB_TILE * MTSB_TILE * ps.spp_pass;
+    const uint32_t slot0 = blockIdx.x * per_tile;
+    unsigned long long n_bad = 0;
+    for (uint32_t i = threadIdx.x; i < per_tile; i += blockDim.x) {
+        const uint32_t slot = slot0 + i;
+        const uint32_t fl = __float_as_uint(pb.refn_flags[slot].w);
+        if (!(fl & PF_VALID)) continue;
+        const float4 lb = pb.L_bpdf[slot];
+        const float2 sp = pb.spos[slot];
+        const float v[5] = {lb.x, lb.y, lb.z, (fl & PF_ALPHA) ? 1.0f : 0.0f, 1.0f};
+        if (!(isfinite(v[0]) && isfinite(v[1]) && isfinite(v[2]))) { ++n_bad; continue; }      // imageblock.h:147-153
+        Footprint f;
+        film_footprint(sc, sp.x, sp.y, ox, oy, bw + 2 * b, bh + 2 * b, f);
+        for (int y = 0; y < f.ny; ++y)
+            for (int x = 0; x < f.nx; ++x) {
+                const float w = f.wx[x] * f.wy[y];
+                float *dest = s_tile + ((f.miny + y) * side + (f.minx + x)) * 5;
+#pragma unroll
+                for (int k = 0; k < 5; ++k) atomicAdd(dest + k, w * v[k]);
+            }
+    }
+    __syncthreads();
+    const int fsx = sc.film_w + 2 * b;
+    for (int i = threadIdx.x; i < n_acc; i += blockDim.x) {
+        const float val = s_tile[i];
+        if (val == 0.0f) continue;
+        const int k = i % 5, p = i / 5, x = p % side, y = p / side;
+        if (x >= bw + 2 * b || y >= bh + 2 * b) continue;
+        atomicAdd(sc.film + ((size_t) (oy + y) * fsx + (ox + x)) * 5 + k, val);
+    }
+    if (n_bad) atomicAdd(bad, n_bad);
+}
+
+// ---- host side ---------------------------------------------------------------------------
+int render_free(Scene *s) {
+    PathBuffers *pb = s->paths;
+    if (!pb) return MTSB_OK;
+    for (int i = 0; i < 2; ++i) { cudaFree(pb->rays[i]); cudaFree(pb->ray_slot[i]); }
+    cudaFree(pb->hits); cudaFree(pb->srays); cudaFree(pb->scontrib); cudaFree(pb->thr_eta); cudaFree(pb->L_bpdf);
+    cudaFree(pb->refn_flags); cudaFree(pb->spos);
+    for (int i = 0; i < Q_COUNT; ++i) cudaFree(pb->q[i]);
+    cudaFree(pb->ctr); cudaFree(pb->tiles);
+    if (pb->h_ctr) cudaFreeHost(pb->h_ctr);
+    delete pb;
+    s->paths = nullptr;
+    return MTSB_OK;
+}
+
+static int ensure_buffers(Scene *s, uint32_t capacity, uint32_t n_tiles) {
+    if (s->paths && s->paths->capacity >= capacity && s->paths->tiles_capacity >= n_tiles) return MTSB_OK;
+    render_free(s);
+    PathBuffers *pb = new PathBuffers();
+    memset(pb, 0, sizeof(*pb));
+    s->paths = pb;
+    pb->capacity = capacity; pb->tiles_capacity = n_tiles;
+    const size_t c = capacity;
+    for (int i = 0; i < 2; ++i) { MTSB_CUDA(cudaMalloc((void **) &pb->rays[i], c * sizeof(RayIn))); MTSB_CUDA(cudaMalloc((void **) &pb->ray_slot[i], c * 4)); }
+    MTSB_CUDA(cudaMalloc((void **) &pb->hits, c * sizeof(HitOut)));
+    MTSB_CUDA(cudaMalloc((void **) &pb->srays, c * sizeof(RayIn)));
+    MTSB_CUDA(cudaMalloc((void **) &pb->scontrib, c * sizeof(float4)));
+    MTSB_CUDA(cudaMalloc((void **) &pb->thr_eta, c * sizeof(float4)));
+    MTSB_CUDA(cudaMalloc((void **) &pb->L_bpdf, c * sizeof(float4)));
+    MTSB_CUDA(cudaMalloc((void **) &pb->refn_flags, c * sizeof(float4)));
+    MTSB_CUDA(cudaMalloc((void **) &pb->spos, c * sizeof(float2)));
+    for (int i = 0; i < Q_COUNT; ++i) MTSB_CUDA(cudaMalloc((void **) &pb->q[i], c * 4));
+    MTSB_CUDA(cudaMalloc((void **) &pb->ctr, sizeof(Counters)));
+    MTSB_CUDA(cudaMalloc((void **) &pb->tiles, (size_t) std::max(1u, n_tiles) * sizeof(int)));
+    MTSB_CUDA(cudaMallocHost((void **) &pb->h_ctr, sizeof(Counters)));
+    return MTSB_OK;
+}
+
+struct StageTimer {
+    struct Span { cudaEvent_t a, b; int stage; };
+    std::vector<Span> spans; std::vector<cudaEvent_t> pool; size_t next = 0; cudaStream_t st;
+    explicit StageTimer(cudaStream_t s) : st(s) {}
+    cudaEvent_t get() { if (next == pool.size()) { cudaEvent_t e; cudaEventCreate(&e); pool.push_back(e); } return pool[next++]; }
+    void begin(int stage) { Span sp; sp.a = get(); sp.b = nullptr; sp.stage = stage; cudaEventRecord(sp.a, st); spans.push_back(sp); }
+    void end() { Span &sp = spans.back(); sp.b = get(); cudaEventRecord(sp.b, st); }
+    void collect(float *out, int n_stage) {
+        for (int i = 0; i < n_stage; ++i) out[i] = 0;
+        for (auto &sp : spans) { float ms = 0; if (sp.b && cudaEventElapsedTime(&ms, sp.a, sp.b) == cudaSuccess) out[sp.stage] += ms; }
+    }
+    ~StageTimer() { for (auto e : pool) cudaEventDestroy(e); }
+};
+enum { ST_RAYGEN = 0, ST_CLOSEST, ST_SHADE, ST_ANY, ST_SPLAT, ST_N };
+
+static int shade_grid(size_t n_upper, int sm_count) {
+    size_t need = (n_upper + MTSB_SHADE_BLOCK - 1) / MTSB_SHADE_BLOCK;
+    size_t cap = (size_t) sm_count * 16;
+    return (int) std::max<size_t>(1, std::min(need, cap));
+}
+
+}  // namespace mtsb
+
+using namespace mtsb;
+
+extern "C" int mtsb_render(mtsb_scene_t scene, const MtsbRenderParams *params, MtsbStats *stats) {
+    Scene *s = reinterpret_cast<Scene *>(scene);
+    if (!s || !params) { set_error("mtsb_render: bad argument"); return MTSB_ERR_INVALID; }
+    if (params->tile_count < 0 || (params->tile_count > 0 && (params->tile_index < 0 || params->tile_index >= params->tile_count)) || params->spp_offset < 0) {
+        set_error("mtsb_render: bad tile partition / sample offset"); return MTSB_ERR_INVALID;
+    }
+    MTSB_CUDA(cudaSetDevice(s->device));
+    const int sm_count = device_sm_count();
+    const SceneView &v = s->v;
+    const int spp = params->spp > 0 ? params->spp : v.integrator.sample_count;
+    if (spp <= 0 || (uint64_t) spp + (uint64_t) params->spp_offset >= (1ull << 24)) { set_error("mtsb_render: sample count out of range"); return MTSB_ERR_INVALID; }
+    const int tile_count = params->tile_count > 0 ? params->tile_count : 1, tile_index = params->tile_count > 0 ? params->tile_index : 0;
+    const uint32_t tiles_x = (uint32_t) (v.film_w + MTSB_TILE - 1) / MTSB_TILE, tiles_y = (uint32_t) (v.film_h + MTSB_TILE - 1) / MTSB_TILE;
+    std::vector<int> tiles;
+    for (uint32_t t = 0; t < tiles_x * tiles_y; ++t) if ((int) (t % (uint32_t) tile_count) == tile_index) tiles.push_back((int) t);
+    const uint64_t launches0 = s->launches;
+    s->cancel.store(0);
+    if (!(params->flags & MTSB_RENDER_KEEP_FILM)) {
+        size_t nf = (size_t) (v.film_w + 2 * v.film_border) * (v.film_h + 2 * v.film_border) * 5;
+        MTSB_CUDA(cudaMemsetAsync(v.film, 0, nf * sizeof(float), s->stream));
+        MTSB_CUDA(cudaMemsetAsync(s->d_film_bad, 0, sizeof(unsigned long long), s->stream));
+    }
+    if (stats) memset(stats, 0, sizeof(*stats));
+    if (tiles.empty()) { MTSB_CUDA(cudaStreamSynchronize(s->stream)); return MTSB_OK; }
+
+    // pass shape: about 8M path slots in flight
+    const uint64_t target = 8ull << 20;
+    const uint64_t px_per_tile = MTSB_TILE * MTSB_TILE;
+    uint32_t spp_pass = params->spp_per_pass > 0 ? (uint32_t) params->spp_per_pass
+                                                 : (uint32_t) std::max<uint64_t>(1, std::min<uint64_t>((uint64_t) spp, target / (tiles.size() * px_per_tile)));
+    spp_pass = std::min<uint32_t>(spp_pass, (uint32_t) spp);
+    uint32_t tiles_per_pass = (uint32_t) std::max<uint64_t>(1, std::min<uint64_t>(tiles.size(), target / (px_per_tile * spp_pass)));
+    const uint32_t capacity = (uint32_t) (tiles_per_pass * px_per_tile * spp_pass);
+    int rc = ensure_buffers(s, capacity, (uint32_t) tiles.size());
+    if (rc) return rc;
+    PathBuffers &pb = *s->paths;
+    MTSB_CUDA(cudaMemcpyAsync(pb.tiles, tiles.data(), tiles.size() * sizeof(int), cudaMemcpyHostToDevice, s->stream));
+    MTSB_CUDA(cudaMemsetAsync(pb.ctr, 0, sizeof(Counters), s->stream));
+
+    RenderConst rcst; rcst.max_depth = v.integrator.max_depth; rcst.rr_depth = v.integrator.rr_depth;
+    rcst.strict_normals = v.integrator.strict_normals; rcst.hide_emitters = v.integrator.hide_emitters;
+    StageTimer timer(s->stream);
+    cudaEvent_t ev0, ev1; cudaEventCreate(&ev0); cudaEventCreate(&ev1);
+    cudaEventRecord(ev0, s->stream);
+    const size_t splat_smem = (size_t) (MTSB_TILE + 2 * v.film_border) * (MTSB_TILE + 2 * v.film_border) * 5 * sizeof(float);
+    uint32_t n_passes = 0;
+    uint64_t samples = 0;
+    int status = MTSB_OK;
+    ShadowResolve resolve{pb.scontrib, pb.L_bpdf};
+
+    for (uint32_t t0 = 0; t0 < tiles.size() && status == MTSB_OK; t0 += tiles_per_pass) {
+        const uint32_t nt = std::min<uint32_t>(tiles_per_pass, (uint32_t) tiles.size() - t0);
+        for (uint32_t s0 = 0; s0 < (uint32_t) spp && status == MTSB_OK; s0 += spp_pass) {
+            PassInfo ps; ps.tile_first = t0; ps.n_tiles = nt; ps.spp_pass = std::min<uint32_t>(spp_pass, (uint32_t) spp - s0);
+            ps.s_first = (uint32_t) params->spp_offset + s0; ps.tiles_x = tiles_x; ps.seed = params->seed;
+            const uint32_t n_slots = (uint32_t) (nt * px_per_tile * ps.spp_pass);
+            ++n_passes;
+            timer.begin(ST_RAYGEN);
+            k_pass_begin<<<1, 1, 0, s->stream>>>(pb);
+            k_raygen<<<shade_grid(n_slots, sm_count), MTSB_SHADE_BLOCK, 0, s->stream>>>(v, pb, ps, n_slots);
+            s->launches += 2;
+            timer.end();
+            uint32_t n_cur = n_slots;     // upper bound for the first bounce
+            int cur = 0;
+            for (int bounce = 0;; ++bounce) {
+                timer.begin(ST_CLOSEST);
+                rc = launch_trace_kernel<false>(s, pb.rays[cur], &pb.ctr->n_rays[cur], n_cur, StoreHit{pb.hits}, s->stream);
+                timer.end();
+                if (rc) { status = rc; break; }
+                timer.begin(ST_SHADE);
+                const int g = shade_grid(n_cur, sm_count);
+                k_bounce_prepare<<<1, 1, 0, s->stream>>>(pb, cur);
+                k_sort<<<g, MTSB_SHADE_BLOCK, 0, s->stream>>>(v, pb, cur);
+                k_shade<Q_DIFFUSE><<<g, MTSB_SHADE_BLOCK, 0, s->stream>>>(v, pb, ps, rcst, cur);
+                k_shade<Q_CONDUCTOR><<<g, MTSB_SHADE_BLOCK, 0, s->stream>>>(v, pb, ps, rcst, cur);
+                k_shade<Q_DIELECTRIC><<<g, MTSB_SHADE_BLOCK, 0, s->stream>>>(v, pb, ps, rcst, cur);
+                k_shade<Q_NULL><<<g, MTSB_SHADE_BLOCK, 0, s->stream>>>(v, pb, ps, rcst, cur);
+                k_shade<Q_GENERIC><<<g, MTSB_SHADE_BLOCK, 0, s->stream>>>(v, pb, ps, rcst, cur);
+                k_miss<<<g, MTSB_SHADE_BLOCK, 0, s->stream>>>(v, pb, rcst, cur);
+                s->launches += 8;
+                timer.end();
+                timer.begin(ST_ANY);
+                rc = launch_trace_kernel<true>(s, pb.srays, &pb.ctr->n_shadow, n_cur, resolve, s->stream);
+                timer.end();
+                if (rc) { status = rc; break; }
+                cudaError_t e = cudaMemcpyAsync(pb.h_ctr, pb.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, s->stream);
+                if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+                if (e != cudaSuccess) { status = cuda_fail(e, "wavefront bounce", __FILE__, __LINE__); break; }
+                if (s->cancel.load()) { status = MTSB_ERR_CANCELLED; set_error("render cancelled"); break; }
+                n_cur = pb.h_ctr->n_rays[1 - cur];
+                cur ^= 1;
+                if (n_cur == 0) break;
+            }
+            if (status != MTSB_OK) break;
+            timer.begin(ST_SPLAT);
+            k_pass_end<<<1, 1, 0, s->stream>>>(pb);
+            k_splat<<<nt, 256, splat_smem, s->stream>>>(v, pb, ps, s->d_film_bad);
+            s->launches += 2;
+            timer.end();
+            samples += (uint64_t) n_slots;
+        }
+    }
+    cudaEventRecord(ev1, s->stream);
+    cudaError_t e = cudaStreamSynchronize(s->stream);
+    if (e != cudaSuccess && status == MTSB_OK) status = cuda_fail(e, "mtsb_render", __FILE__, __LINE__);
+    if (status == MTSB_OK) { e = cudaGetLastError(); if (e != cudaSuccess) status = cuda_fail(e, "mtsb_render kernels", __FILE__, __LINE__); }
+    if (stats && status == MTSB_OK) {
+        Counters hc;
+        unsigned long long bad = 0;
+        cudaMemcpy(&hc, pb.ctr, sizeof(hc), cudaMemcpyDeviceToHost);
+        cudaMemcpy(&bad, s->d_film_bad, sizeof(bad), cudaMemcpyDeviceToHost);
+        float st[ST_N]; timer.collect(st, ST_N);
+        float total = 0; cudaEventElapsedTime(&total, ev0, ev1);
+        // samples counts slots of whole tiles; report the ones inside the crop window
+        uint64_t px_in = 0;
+        for (int t : tiles) {
+            int ox = (t % (int) tiles_x) * MTSB_TILE, oy = (t / (int) tiles_x) * MTSB_TILE;
+            px_in += (uint64_t) std::min(MTSB_TILE, v.film_w - ox) * (uint64_t) std::min(MTSB_TILE, v.film_h - oy);
+        }
+        stats->samples = px_in * (uint64_t) spp;
+        stats->closest_rays = hc.closest; stats->shadow_rays = hc.shadow; stats->shade_events = hc.shade;
+        stats->path_length_sum = hc.path_len; stats->kernel_launches = s->launches - launches0; stats->bad_samples = bad;
+        stats->ms_total = total; stats->ms_raygen = st[ST_RAYGEN]; stats->ms_trace_closest = st[ST_CLOSEST]; stats->ms_shade = st[ST_SHADE];
+        stats->ms_trace_any = st[ST_ANY]; stats->ms_splat = st[ST_SPLAT]; stats->n_passes = n_passes;
+        (void) samples;
+    }
+    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+    return status;
+}

@@ -1,0 +1,53 @@
+// scene.h -- host-side handle behind mtsb_scene_t: device pointers + small host tables.
+#pragma once
+#include <cuda_runtime.h>
+#include <string>
+#include <vector>
+#include <atomic>
+#include "../../include/mtsb200.h"
+#include "bvh.h"
+#include "scene_view.h"
+
+namespace mtsb {
+
+struct PathBuffers;   // render.cu
+
+struct Scene {
+    int device = 0;
+    SceneView v{};
+    std::vector<void *> allocs;             // everything to cudaFree on destroy
+    MtsbSceneInfo info{};
+    std::atomic<int> cancel{0};
+    unsigned long long *d_film_bad = nullptr;
+    PathBuffers *paths = nullptr;
+    uint64_t launches = 0;                  // kernels launched by this library for this scene
+    cudaStream_t stream = nullptr;
+};
+
+void set_error(const std::string &s);
+int cuda_fail(cudaError_t e, const char *what, const char *file, int line);
+#define MTSB_CUDA(x) do { cudaError_t e__ = (x); if (e__ != cudaSuccess) return mtsb::cuda_fail(e__, #x, __FILE__, __LINE__); } while (0)
+
+template <class T> int dev_alloc(Scene *s, T **p, size_t count) {
+    void *q = nullptr;
+    cudaError_t e = cudaMalloc(&q, count ? count * sizeof(T) : sizeof(T));
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc", __FILE__, __LINE__);
+    if (s) s->allocs.push_back(q);
+    *p = static_cast<T *>(q);
+    return MTSB_OK;
+}
+template <class T> int dev_upload(Scene *s, const T **p, const T *host, size_t count) {
+    T *q = nullptr;
+    int rc = dev_alloc(s, &q, count);
+    if (rc) return rc;
+    if (count) MTSB_CUDA(cudaMemcpy(q, host, count * sizeof(T), cudaMemcpyHostToDevice));
+    *p = q;
+    return MTSB_OK;
+}
+
+int build_bvh(Scene *s, const float *d_positions, const uint32_t *d_indices, uint64_t n_tris);
+int render_free(Scene *s);
+
+inline unsigned grid_for(size_t n, unsigned block) { return (unsigned) ((n + block - 1) / block); }
+
+}  // namespace mtsb

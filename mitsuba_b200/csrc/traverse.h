@@ -1,0 +1,208 @@
+// traverse.h -- closest-hit / any-hit ray query against the 8-wide BVH.
+//
+// Replaces ShapeKDTree::rayIntersect (reference: src/librender/skdtree.cpp:112-148 closest,
+// :213-232 any-hit) and SAHKDTree3D::rayIntersectHavran (include/mitsuba/render/sahkdtree3.h:178-308).
+// What is kept from the reference, bit for bit:
+//   * the scene-box clip with the enlarged box (include/mitsuba/core/aabb.h:308-338),
+//   * the adaptive epsilon (skdtree.cpp:127-130 / :219-222),
+//   * the triangle test and its acceptance rule (include/mitsuba/render/triaccel.h:102-168):
+//     inclusive [mint,maxt], u>=0, v>=0, u+v<=1, an accepted hit shrinks maxt, equal t re-accepts.
+// What is new: the search structure (bvh.h) and a traversal written as a resumable state
+// machine, so that a persistent warp can swap finished rays for fresh ones between steps.
+#pragma once
+#include "bvh.h"
+
+namespace mtsb {
+
+struct RayIn { float ox, oy, oz, mint, dx, dy, dz, maxt; };   // == MtsbRay
+struct HitOut { uint32_t prim; float u, v, t; };              // == MtsbHit
+#define MTSB_NO_HIT_ID 0xFFFFFFFFu
+
+// AABB::rayIntersect (aabb.h:308-338) on the enlarged scene box + the interval logic of
+// ShapeKDTree::rayIntersect.  Returns false when the query interval is empty.
+MTSB_HD bool ray_interval(const RayIn &r, const float *box_lo, const float *box_hi, bool any_hit,
+                          float &mint, float &maxt) {
+    float nearT = -MTSB_INF, farT = MTSB_INF;
+    const float o[3] = {r.ox, r.oy, r.oz}, d[3] = {r.dx, r.dy, r.dz};
+#if MTSB_DEVICE_CODE
+#pragma unroll
+#endif
+    for (int i = 0; i < 3; ++i) {
+        const float origin = o[i], minVal = box_lo[i], maxVal = box_hi[i];
+        if (d[i] == 0.0f) {
+            if (origin < minVal || origin > maxVal) return false;
+        } else {
+            const float rcp = fdiv(1.0f, d[i]);
+            float t1 = fmul(fsub(minVal, origin), rcp), t2 = fmul(fsub(maxVal, origin), rcp);
+            if (t1 > t2) { float tmp = t1; t1 = t2; t2 = tmp; }
+            nearT = fmaxf(t1, nearT);
+            farT = fminf(t2, farT);
+            if (!(nearT <= farT)) return false;
+        }
+    }
+    float rayMinT = r.mint;
+    if (rayMinT == MTSB_EPSILON) {
+        float m = fmaxf(fmaxf(fabsf(r.ox), fabsf(r.oy)), fabsf(r.oz));
+        if (!any_hit) m = fmaxf(m, MTSB_EPSILON);
+        rayMinT = fmul(rayMinT, m);
+    }
+    mint = nearT; maxt = farT;
+    if (rayMinT > mint) mint = rayMinT;
+    if (r.maxt < maxt) maxt = r.maxt;
+    return maxt > mint;
+}
+
+// TriAccel::rayIntersect, triaccel.h:102-168 (operation order and rounding preserved)
+MTSB_HD bool tri_test(const U4 q0, const U4 q1, const U4 q2, float ox, float oy, float oz, float dx, float dy, float dz,
+                      float mint, float maxt, float &u, float &v, float &t) {
+    const uint32_t k = q0.x;
+    const float n_u = u2f(q0.y), n_v = u2f(q0.z), n_d = u2f(q0.w);
+    const float a_u = u2f(q1.x), a_v = u2f(q1.y), b_nu = u2f(q1.z), b_nv = u2f(q1.w);
+    const float c_nu = u2f(q2.x), c_nv = u2f(q2.y);
+    float o_u, o_v, o_k, d_u, d_v, d_k;
+    if (k == 0) { o_u = oy; o_v = oz; o_k = ox; d_u = dy; d_v = dz; d_k = dx; }
+    else if (k == 1) { o_u = oz; o_v = ox; o_k = oy; d_u = dz; d_v = dx; d_k = dy; }
+    else if (k == 2) { o_u = ox; o_v = oy; o_k = oz; d_u = dx; d_v = dy; d_k = dz; }
+    else return false;
+    t = fdiv(fsub(fsub(fsub(n_d, fmul(o_u, n_u)), fmul(o_v, n_v)), o_k),
+             fadd(fadd(fmul(d_u, n_u), fmul(d_v, n_v)), d_k));
+    if (t < mint || t > maxt) return false;
+    const float hu = fsub(fadd(o_u, fmul(t, d_u)), a_u);
+    const float hv = fsub(fadd(o_v, fmul(t, d_v)), a_v);
+    u = fadd(fmul(hv, b_nu), fmul(hu, b_nv));
+    v = fadd(fmul(hu, c_nu), fmul(hv, c_nv));
+    return u >= 0.0f && v >= 0.0f && fadd(u, v) <= 1.0f;
+}
+
+#if MTSB_DEVICE_CODE
+MTSB_HD U4 ld16(const U4 *p) { return __ldg(p); }
+#else
+MTSB_HD U4 ld16(const U4 *p) { return *p; }
+#endif
+
+// Plain per-thread stack (registers / local memory).  The CUDA kernels substitute a
+// shared-memory short stack with local-memory overflow (trace.cu).
+template <int N> struct LocalStack {
+    uint32_t sx[N], sy[N]; int sp;
+    MTSB_HD void reset() { sp = 0; }
+    MTSB_HD bool empty() const { return sp == 0; }
+    MTSB_HD void push(uint32_t x, uint32_t y) { if (sp < N) { sx[sp] = x; sy[sp] = y; ++sp; } }
+    MTSB_HD void pop(uint32_t &x, uint32_t &y) { --sp; x = sx[sp]; y = sy[sp]; }
+};
+
+template <class Stack> struct Traversal {
+    float ox, oy, oz, dx, dy, dz, tmin, tmax;
+    float idx, idy, idz;
+    uint32_t octinv;
+    uint32_t ng_x, ng_y;          // current node group: (child base, hit bits<<24 | imask)
+    HitOut hit;
+    Stack stack;
+    uint32_t steps;               // nodes visited (statistics)
+
+    MTSB_HD void begin(const RayIn &r, float mint, float maxt) {
+        ox = r.ox; oy = r.oy; oz = r.oz; dx = r.dx; dy = r.dy; dz = r.dz; tmin = mint; tmax = maxt;
+        const float ooeps = 8.271806125530277e-25f;   // 2^-80
+        idx = 1.0f / (fabsf(dx) > ooeps ? dx : copysignf(ooeps, dx));
+        idy = 1.0f / (fabsf(dy) > ooeps ? dy : copysignf(ooeps, dy));
+        idz = 1.0f / (fabsf(dz) > ooeps ? dz : copysignf(ooeps, dz));
+        octinv = (dx >= 0.0f ? 1u : 0u) | (dy >= 0.0f ? 2u : 0u) | (dz >= 0.0f ? 4u : 0u);
+        ng_x = 0; ng_y = 0x80000000u;
+        hit.prim = MTSB_NO_HIT_ID; hit.u = 0; hit.v = 0; hit.t = MTSB_INF;
+        stack.reset();
+        steps = 0;
+    }
+
+    // One node visit (+ the triangles it references).  Returns true when the query is finished.
+    template <bool ANY> MTSB_HD bool step(const U4 *nodes, const U4 *tris) {
+        // ---- take the nearest pending child of the current group ----
+        const uint32_t hits_imask = ng_y;
+        const int bit = bfind(hits_imask);
+        const uint32_t base = ng_x;
+        ng_y &= ~(1u << bit);
+        if (ng_y > 0x00FFFFFFu) stack.push(ng_x, ng_y);
+        const uint32_t slot = ((uint32_t) bit - 24u) ^ octinv;
+        const uint32_t rel = (uint32_t) popc(hits_imask & ~(0xFFFFFFFFu << slot) & 0xFFu);
+        const U4 *np = nodes + 5 * (size_t) (base + rel);
+        const U4 n0 = ld16(np), n1 = ld16(np + 1), n2 = ld16(np + 2), n3 = ld16(np + 3), n4 = ld16(np + 4);
+        ++steps;
+
+        const uint32_t e_imask = n0.w;
+        const float sdx = u2f((e_imask & 0xffu) << 23) * idx;
+        const float sdy = u2f(((e_imask >> 8) & 0xffu) << 23) * idy;
+        const float sdz = u2f(((e_imask >> 16) & 0xffu) << 23) * idz;
+        const float ax = (u2f(n0.x) - ox) * idx, ay = (u2f(n0.y) - oy) * idy, az = (u2f(n0.z) - oz) * idz;
+        // near / far planes by ray direction sign
+        const bool nx = dx < 0.0f, ny = dy < 0.0f, nz = dz < 0.0f;
+        const uint32_t lox0 = n2.x, lox1 = n2.y, loy0 = n2.z, loy1 = n2.w, loz0 = n3.x, loz1 = n3.y;
+        const uint32_t hix0 = n3.z, hix1 = n3.w, hiy0 = n4.x, hiy1 = n4.y, hiz0 = n4.z, hiz1 = n4.w;
+        const uint32_t nearx[2] = {nx ? hix0 : lox0, nx ? hix1 : lox1}, farx[2] = {nx ? lox0 : hix0, nx ? lox1 : hix1};
+        const uint32_t neary[2] = {ny ? hiy0 : loy0, ny ? hiy1 : loy1}, fary[2] = {ny ? loy0 : hiy0, ny ? loy1 : hiy1};
+        const uint32_t nearz[2] = {nz ? hiz0 : loz0, nz ? hiz1 : loz1}, farz[2] = {nz ? loz0 : hiz0, nz ? loz1 : hiz1};
+        const uint32_t meta[2] = {n1.z, n1.w};
+        uint32_t hitmask = 0;
+#if MTSB_DEVICE_CODE
+#pragma unroll
+#endif
+        for (int h = 0; h < 2; ++h) {
+#if MTSB_DEVICE_CODE
+#pragma unroll
+#endif
+            for (int j = 0; j < 4; ++j) {
+                const int sh = 8 * j;
+                const uint32_t m = (meta[h] >> sh) & 0xffu;
+                const float tnx = (float) ((nearx[h] >> sh) & 0xffu) * sdx + ax;
+                const float tny = (float) ((neary[h] >> sh) & 0xffu) * sdy + ay;
+                const float tnz = (float) ((nearz[h] >> sh) & 0xffu) * sdz + az;
+                const float tfx = (float) ((farx[h] >> sh) & 0xffu) * sdx + ax;
+                const float tfy = (float) ((fary[h] >> sh) & 0xffu) * sdy + ay;
+                const float tfz = (float) ((farz[h] >> sh) & 0xffu) * sdz + az;
+                const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
+                const float cmax = fminf(fminf(tfx, tfy), fminf(tfz, tmax));
+                if (cmin <= cmax) {
+                    const uint32_t is_inner = (m & (m << 1)) & 0x10u;
+                    const uint32_t bit_index = (m ^ (is_inner ? octinv : 0u)) & 0x1fu;
+                    hitmask |= ((m >> 5) & 7u) << bit_index;
+                }
+            }
+        }
+        ng_x = n1.x;
+        ng_y = (hitmask & 0xFF000000u) | (e_imask >> 24);
+        uint32_t tg = hitmask & 0x00FFFFFFu;
+        const U4 *tp = tris + 3 * (size_t) n1.y;
+
+        // ---- triangles referenced by this node ----
+        while (tg) {
+            const int i = bfind(tg);
+            tg &= ~(1u << i);
+            const U4 q0 = ld16(tp + 3 * i), q1 = ld16(tp + 3 * i + 1), q2 = ld16(tp + 3 * i + 2);
+            float u, v, t;
+            if (tri_test(q0, q1, q2, ox, oy, oz, dx, dy, dz, tmin, tmax, u, v, t)) {
+                hit.prim = q2.z; hit.u = u; hit.v = v; hit.t = t;
+                if (ANY) return true;
+                tmax = t;
+            }
+        }
+
+        // ---- next group ----
+        if (ng_y <= 0x00FFFFFFu) {
+            if (stack.empty()) return true;
+            stack.pop(ng_x, ng_y);
+        }
+        return false;
+    }
+};
+
+// Whole query for one ray (used by the emulation build and by small device helpers).
+template <bool ANY, class Stack>
+MTSB_HD void trace_one(const RayIn &r, const float *box_lo, const float *box_hi, const U4 *nodes, const U4 *tris,
+                       uint32_t n_nodes, HitOut &out) {
+    out.prim = MTSB_NO_HIT_ID; out.u = 0; out.v = 0; out.t = MTSB_INF;
+    float mint, maxt;
+    if (n_nodes == 0 || !ray_interval(r, box_lo, box_hi, ANY, mint, maxt)) return;
+    Traversal<Stack> tr;
+    tr.begin(r, mint, maxt);
+    while (!tr.template step<ANY>(nodes, tris)) {}
+    out = tr.hit;   // closest: hit.t stays +inf when nothing was accepted (skdtree.cpp:137-140)
+}
+
+}  // namespace mtsb

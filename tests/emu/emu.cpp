@@ -1,0 +1,122 @@
+// TEST TARGET ONLY -- CPU emulation of the kernel bodies of mitsuba_b200/csrc (bvh.h, traverse.h).
+//
+// The product library has no host execution path.  This file compiles the SAME per-thread
+// kernel bodies with g++ (MTSB_EMU) and runs them in sequential loops, so that the BVH
+// builder and the traversal logic can be checked against the oracle on the GPU-less CI box
+// (`pytest -m "not gpu"`).  Nothing under mitsuba_b200/ loads it.
+#define MTSB_EMU 1
+#include "../../mitsuba_b200/csrc/bvh.h"
+#include "../../mitsuba_b200/csrc/traverse.h"
+#include "../../mitsuba_b200/csrc/sensor.h"
+#include <vector>
+#include <algorithm>
+#include <numeric>
+#include <cstring>
+#include <cmath>
+
+using namespace mtsb;
+
+struct EmuScene {
+    std::vector<Node8> nodes;
+    std::vector<TriRec> tris;
+    float tight_lo[3], tight_hi[3], box_lo[3], box_hi[3];
+    uint32_t n_tris;
+};
+
+extern "C" void *emu_build(const float *positions, const uint32_t *indices, uint32_t n) {
+    EmuScene *s = new EmuScene();
+    s->n_tris = n;
+    for (int k = 0; k < 3; ++k) { s->tight_lo[k] = s->tight_hi[k] = s->box_lo[k] = s->box_hi[k] = 0; }
+    if (n == 0) return s;
+    std::vector<TriRec> tri_tmp(n);
+    std::vector<float> prim_lo(3 * (size_t) n), prim_hi(3 * (size_t) n);
+    float tlo[3] = {INFINITY, INFINITY, INFINITY}, thi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (uint32_t i = 0; i < n; ++i) {
+        tri_setup(i, positions, indices, &tri_tmp[i], &prim_lo[3 * (size_t) i], &prim_hi[3 * (size_t) i]);
+        for (int k = 0; k < 3; ++k) { tlo[k] = std::min(tlo[k], prim_lo[3 * (size_t) i + k]); thi[k] = std::max(thi[k], prim_hi[3 * (size_t) i + k]); }
+    }
+    for (int k = 0; k < 3; ++k) {
+        volatile float lo = tlo[k] - ((thi[k] - tlo[k]) * 1e-3f + 1e-3f);
+        volatile float hi = thi[k] + ((thi[k] - lo) * 1e-3f + 1e-3f);
+        s->box_lo[k] = lo; s->box_hi[k] = hi; s->tight_lo[k] = tlo[k]; s->tight_hi[k] = thi[k];
+    }
+    V3 slo(tlo[0], tlo[1], tlo[2]);
+    V3 sinv(thi[0] > tlo[0] ? 1.0f / (thi[0] - tlo[0]) : 0.0f, thi[1] > tlo[1] ? 1.0f / (thi[1] - tlo[1]) : 0.0f,
+            thi[2] > tlo[2] ? 1.0f / (thi[2] - tlo[2]) : 0.0f);
+    float diag = std::sqrt((thi[0] - tlo[0]) * (thi[0] - tlo[0]) + (thi[1] - tlo[1]) * (thi[1] - tlo[1]) + (thi[2] - tlo[2]) * (thi[2] - tlo[2]));
+    float amax = 0; for (int k = 0; k < 3; ++k) amax = std::max(amax, std::max(std::fabs(tlo[k]), std::fabs(thi[k])));
+    const float leaf_pad = 4e-6f * std::max(diag, amax) + 1e-30f;
+
+    std::vector<uint64_t> keys(n); std::vector<uint32_t> vals(n);
+    for (uint32_t i = 0; i < n; ++i) keys[i] = morton_key(&prim_lo[3 * (size_t) i], &prim_hi[3 * (size_t) i], slo, sinv);
+    std::iota(vals.begin(), vals.end(), 0u);
+    std::stable_sort(vals.begin(), vals.end(), [&](uint32_t a, uint32_t b) { return keys[a] < keys[b]; });
+    std::vector<uint64_t> skeys(n);
+    for (uint32_t i = 0; i < n; ++i) skeys[i] = keys[vals[i]];
+
+    std::vector<Node8> nodes(std::max<uint32_t>(1, n));
+    std::vector<TriRec> tri_out(n);
+    std::vector<uint32_t> wbin(std::max<uint32_t>(1, n), 0), left(n), right(n), first(n), last(n), parent(2 * (size_t) n, 0), flags(n, 0);
+    std::vector<float> node_lo(6 * (size_t) n), node_hi(6 * (size_t) n);
+    uint32_t counters[2] = {1, 0};
+    WideBuildArgs a;
+    a.n = (int) n; a.left = left.data(); a.right = right.data(); a.first = first.data(); a.last = last.data();
+    a.node_lo = node_lo.data(); a.node_hi = node_hi.data(); a.sorted_prim = vals.data(); a.tri_in = tri_tmp.data();
+    a.nodes = nodes.data(); a.wbin = wbin.data(); a.tri_out = tri_out.data(); a.counters = counters; a.leaf_pad = leaf_pad;
+    uint32_t n_nodes = 1;
+    if (n <= MTSB_LEAF_MAX) {
+        for (int k = 0; k < 3; ++k) { node_lo[k] = tlo[k]; node_hi[k] = thi[k]; }
+        wide_node_build(0, a, true);
+    } else {
+        for (int i = 0; i < (int) n - 1; ++i) radix_tree_node(i, (int) n, skeys.data(), left.data(), right.data(), parent.data(), first.data(), last.data());
+        for (int j = 0; j < (int) n; ++j)
+            fit_from_leaf(j, (int) n, vals.data(), prim_lo.data(), prim_hi.data(), left.data(), right.data(), parent.data(), node_lo.data(), node_hi.data(), flags.data());
+        uint32_t begin = 0, end = 1;
+        while (begin < end) {
+            for (uint32_t w = begin; w < end; ++w) wide_node_build(w, a, false);
+            begin = end; end = counters[0];
+        }
+        n_nodes = end;
+    }
+    nodes.resize(n_nodes);
+    s->nodes.swap(nodes); s->tris.swap(tri_out);
+    return s;
+}
+
+extern "C" void emu_destroy(void *h) { delete static_cast<EmuScene *>(h); }
+
+extern "C" void emu_info(void *h, uint32_t *n_nodes, float *tight6, float *enlarged6) {
+    EmuScene *s = static_cast<EmuScene *>(h);
+    *n_nodes = (uint32_t) s->nodes.size();
+    for (int k = 0; k < 3; ++k) { tight6[k] = s->tight_lo[k]; tight6[3 + k] = s->tight_hi[k]; enlarged6[k] = s->box_lo[k]; enlarged6[3 + k] = s->box_hi[k]; }
+}
+
+// returns the total number of node visits (traversal statistics)
+extern "C" uint64_t emu_trace(void *h, const RayIn *rays, size_t n, int mode, HitOut *hits) {
+    EmuScene *s = static_cast<EmuScene *>(h);
+    uint64_t steps = 0;
+    const U4 *nodes = reinterpret_cast<const U4 *>(s->nodes.data()), *tris = reinterpret_cast<const U4 *>(s->tris.data());
+    for (size_t i = 0; i < n; ++i) {
+        HitOut out; out.prim = MTSB_NO_HIT_ID; out.u = out.v = 0; out.t = INFINITY;
+        float mint, maxt;
+        if (!s->nodes.empty() && ray_interval(rays[i], s->box_lo, s->box_hi, mode == 1, mint, maxt)) {
+            Traversal<LocalStack<64>> tr;
+            tr.begin(rays[i], mint, maxt);
+            if (mode == 1) { while (!tr.step<true>(nodes, tris)) {} }
+            else { while (!tr.step<false>(nodes, tris)) {} }
+            out = tr.hit; steps += tr.steps;
+        }
+        hits[i] = out;
+    }
+    return steps;
+}
+
+// copies of the triangle records in leaf order (for structural checks)
+extern "C" void emu_tris(void *h, TriRec *out) {
+    EmuScene *s = static_cast<EmuScene *>(h);
+    std::memcpy(out, s->tris.data(), s->tris.size() * sizeof(TriRec));
+}
+
+extern "C" void emu_sensor_rays(const MtsbSensor *se, float near_x, float near_y, const float *pos, size_t n, RayIn *rays) {
+    for (size_t i = 0; i < n; ++i) sensor_ray(*se, near_x, near_y, pos[2 * i], pos[2 * i + 1], rays[i]);
+}
