@@ -1,0 +1,319 @@
+#!/usr/bin/env python
+"""bench.py -- path samples/s of the B200 `path` integrator on BASELINE.json's configuration.
+
+Own arm (default):  python bench.py [--gpus N] [--steps K] [--warmup W]
+  One "step" = one full render of the workload (every pixel, every sample) through mtsb_render.
+  N = 1: configs[1] -- synthetic 1M-triangle scene, GGX roughconductor + diffuse, 1920x1080,
+         256 spp, maxDepth 10 (the configuration the metric is quoted on).
+  N > 1: launched by torchrun, one rank per GPU.  The image is partitioned by interleaved
+         32x32 tiles (tile % N == rank) and every rank renders N x 256 spp of its tiles, so the
+         per-GPU work is fixed ("weak" scaling); one NCCL reduce of the film to rank 0 ends a step.
+  value   = path samples of all ranks / device time (CUDA events inside mtsb_render, max over ranks)
+  e2e     = same metric through the C ABI with HOST buffers: scene description in host memory ->
+            mtsb_scene_create (H2D + BVH build) -> mtsb_render -> mtsb_film_develop (D2H), every step.
+Reference arm:      python bench.py --impl reference ...
+  The reference's CPU implementation of the same path on the host cores: the kd-tree /
+  TriAccel compiled from the reference tree (oracle/_ref) under the restated Li loop (oracle/),
+  all host threads, on a bounded sample of the same workload (a subset of 32x32 blocks).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "path_samples_per_s"
+UNIT = "samples/s"
+WORKLOADS = {
+    # name: (builder name, kwargs, triangles label, closest-hit bytes/ray, shadow bytes/ray)   SURVEY.md 8(d)
+    "cfg1_1m": ("scene_1m", dict(width=1920, height=1080, spp=256, max_depth=10), "1M", 720, 708),
+    "cfg0_cbox": ("cbox", dict(width=512, height=512, spp=64, max_depth=8), "32", 400, 388),
+    "cfg2_10m": ("scene_10m", dict(width=1920, height=1080, spp=512, max_depth=10), "10M", 880, 868),
+}
+SHADE_BYTES = 276      # per shade event
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="cfg1_1m", choices=sorted(WORKLOADS))
+    ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (testing only; the JSON line says so)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
+    return ap.parse_args()
+
+
+def make_builder(args):
+    from mitsuba_b200 import scenes
+    fn, kw, _, _, _ = WORKLOADS[args.workload]
+    kw = dict(kw)
+    if args.spp > 0:
+        kw["spp"] = args.spp
+    return getattr(scenes, fn)(**kw), kw
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+                for nm, v in zip(names, r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+class CpuReference:
+    """The reference's CPU path on the host cores: kd-tree + TriAccel compiled from the reference tree
+    (oracle/_ref) under the restated Li loop (oracle/).  Built once; every step() renders a bounded
+    sample of the workload (a subset of the 32x32 blocks of the spiral at reduced spp)."""
+
+    def __init__(self, builder, threads=0):
+        import oracle                                     # checker / CPU baseline only (never on the product path)
+        oracle.build(ref=os.path.isdir("/root/reference/include/mitsuba"))
+        self.use_ref = oracle.ref_available()
+        t0 = time.time()
+        self.orc = oracle.Oracle(builder, use_ref_kdtree=self.use_ref)
+        self.build_s = time.time() - t0
+        self.threads = threads
+        w, h, _ = self.orc.film_size()
+        self.total_blocks = ((w + 31) // 32) * ((h + 31) // 32)
+        self.full_spp = builder.integrator.sample_count
+        st = self.orc.render(spp=1, seed=1, threads=threads, max_blocks=min(self.total_blocks, 64))
+        self.rate = st.samples / max(st.seconds, 1e-6)
+        self.kind = "reference" if self.use_ref else "port"
+
+    def step(self, seconds, seed=2):
+        want = self.rate * seconds
+        blocks = int(min(self.total_blocks, max(min(self.total_blocks, 64), want / (1024.0 * min(self.full_spp, 16)))))
+        spp = int(max(1, min(self.full_spp, want / (1024.0 * blocks))))
+        st = self.orc.render(spp=spp, seed=seed, threads=self.threads, max_blocks=blocks)
+        self.rate = st.samples / max(st.seconds, 1e-6)
+        sample = ("%d of %d 32x32 blocks (evenly spaced along the spiral) at %d spp = %d path samples in %.1f s; %s"
+                  % (blocks, self.total_blocks, spp, st.samples, st.seconds,
+                     "kd-tree + TriAccel compiled from the reference tree under the restated Li loop" if self.use_ref
+                     else "CPU restatement (oracle/) with its own BVH"))
+        return st.samples / st.seconds, int(st.threads), sample, st
+
+
+def run_reference_arm(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    builder, kw = make_builder(args)
+    ref = CpuReference(builder)
+    per_step = max(2.0, min(20.0, 100.0 / max(1, args.steps + args.warmup)))
+    vals, secs = [], []
+    cores, sample = 0, ""
+    for i in range(args.warmup + args.steps):
+        v, cores, sample, st = ref.step(per_step, seed=2 + i)
+        if i >= args.warmup:
+            vals.append(v)
+            secs.append(st.seconds)
+    value = float(np.sum([v * s for v, s in zip(vals, secs)]) / np.sum(secs))
+    out = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(secs)), "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": args.workload, **kw, "note": "reference CPU path on the host cores; each step is a bounded sample"},
+           "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": ref.kind, "sample": sample,
+                            "kd_build_s": round(ref.build_s, 2)},
+           "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(out), flush=True)
+
+
+class _DevPtr:
+    """Zero-copy torch view of a device pointer owned by the library (the film)."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (ptr, False), "version": 2}
+
+
+def host_bytes(builder):
+    pos, nrm, uv, idx = builder.arrays()
+    return int(pos.nbytes + nrm.nbytes + uv.nbytes + idx.nbytes)
+
+
+def run_b200_arm(args):
+    import torch
+    import torch.distributed as dist
+    from mitsuba_b200 import lib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the B200 arm has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    lib.init(local)
+
+    builder, kw = make_builder(args)
+    spp = kw["spp"]
+    total_spp = spp * world                     # weak scaling: N x spp of the same image, tiles interleaved over ranks
+    scene = lib.Scene(builder)
+    info = scene.info()
+    film_ptr, film_n = scene.film_device_ptr()
+    film_t = torch.as_tensor(_DevPtr(film_ptr, film_n), device="cuda") if world > 1 else None
+    flush = torch.empty(160 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(seed):
+        flush.zero_()                                   # L2 flush between timed iterations
+        torch.cuda.synchronize()
+        st = scene.render(spp=total_spp, seed=seed, tile_index=rank, tile_count=world)
+        ms = st.ms_total
+        if world > 1:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            dist.reduce(film_t, dst=0, op=dist.ReduceOp.SUM)
+            e1.record()
+            torch.cuda.synchronize()
+            ms += e0.elapsed_time(e1)
+        return st, ms
+
+    for i in range(args.warmup):
+        step(100 + i)
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    t_wall0 = time.time()
+    dev_ms, stats = 0.0, []
+    for i in range(args.steps):
+        st, ms = step(200 + i)
+        dev_ms += ms
+        stats.append(st)
+    barrier()
+    wall_s = time.time() - t_wall0
+    clk = clocks.stop() if rank == 0 else None
+
+    samples_rank = float(sum(s.samples for s in stats))
+    agg = torch.tensor([dev_ms, samples_rank, float(sum(s.closest_rays for s in stats)), float(sum(s.shadow_rays for s in stats)),
+                        float(sum(s.kernel_launches for s in stats))], dtype=torch.float64, device="cuda")
+    mx = agg.clone()
+    if world > 1:
+        dist.all_reduce(agg, op=dist.ReduceOp.SUM)
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    max_ms = float(mx[0])
+    samples_all, rays_all, launches_all = float(agg[1]), float(agg[2] + agg[3]), int(agg[4])
+    value = samples_all / (max_ms * 1e-3)
+
+    # ---- end to end through the C ABI with host buffers (scene in host memory -> image in host memory) ----
+    scene.close()
+    barrier()
+    e2e_t0 = time.time()
+    e2e_samples = 0.0
+    d2h = 0
+    for i in range(args.steps):
+        sc = lib.Scene(builder)                                     # H2D of the scene arrays + BVH build
+        st = sc.render(spp=total_spp, seed=300 + i, tile_index=rank, tile_count=world)
+        if world > 1:
+            p, n = sc.film_device_ptr()
+            dist.reduce(torch.as_tensor(_DevPtr(p, n), device="cuda"), dst=0, op=dist.ReduceOp.SUM)
+        if rank == 0:
+            img = sc.film_develop()                                 # D2H of the developed image
+            d2h = int(img.nbytes)
+        e2e_samples += st.samples
+        sc.close()
+    barrier()
+    e2e_s = time.time() - e2e_t0
+    e2e_all = torch.tensor([e2e_samples], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e_all, op=dist.ReduceOp.SUM)
+    e2e_value = float(e2e_all[0]) / e2e_s
+
+    if rank == 0:
+        _, _, tris, b_c, b_s = WORKLOADS[args.workload]
+        s0 = stats[-1]
+        # roofline of the dominant kernel (closest-hit traversal): algorithmic bytes / launch time
+        closest = float(sum(s.closest_rays for s in stats)); ms_closest = float(sum(s.ms_trace_closest for s in stats))
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        achieved = closest * b_c / (ms_closest * 1e-3) / 1e9 if ms_closest > 0 else 0.0
+        out = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": max_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, **kw, "triangles": int(info.n_tris), "spp_total": total_spp,
+                       "partition": "tile %% %d, %d spp per rank-tile" % (world, total_spp), "bvh_nodes": int(info.n_bvh_nodes),
+                       "bvh_build_ms": round(float(info.build_ms), 2), "l2": "flushed between steps (160 MB write); per-step working set >> L2",
+                       "spp_override": bool(args.spp)},
+            "mrays_per_s": rays_all / (max_ms * 1e-3) / 1e6,
+            "rays_per_sample": rays_all / samples_all,
+            "wall_s_timed_region": wall_s,
+            "stage_ms_last_step": {"raygen": s0.ms_raygen, "trace_closest": s0.ms_trace_closest, "shade": s0.ms_shade,
+                                   "trace_any": s0.ms_trace_any, "splat": s0.ms_splat, "total": s0.ms_total, "passes": s0.n_passes},
+            "roofline": {"bound": "hbm", "kernel": "k_trace<closest>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
+                         "bytes_per_ray": b_c},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": host_bytes(builder), "d2h_bytes_per_step": d2h,
+                    "includes": "mtsb_scene_create (H2D + GPU BVH build) + mtsb_render + film reduce + mtsb_film_develop (D2H) per step"},
+            "gpu_launches": launches_all, "clocks": clk,
+        }
+        if not args.no_cpu_baseline and world == 1:
+            ref = CpuReference(builder)
+            v, cores, sample, _ = ref.step(args.cpu_seconds)
+            out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": ref.kind, "sample": sample,
+                                   "kd_build_s": round(ref.build_s, 2)}
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference_arm(a)
+    else:
+        run_b200_arm(a)

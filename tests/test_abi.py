@@ -1,0 +1,55 @@
+"""CPU: the C-ABI library loads, exports every symbol include/mtsb200.h declares, refuses to
+compute without a GPU, and the product package never touches the oracle."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+from mitsuba_b200 import abi, lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    src = open(os.path.join(ROOT, "include", "mtsb200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(mtsb_[a-z_0-9]+)\s*\(", src)))
+
+
+def test_header_and_binding_agree():
+    assert _declared() == sorted(lib.SYMBOLS)
+
+
+def test_library_exports_every_symbol():
+    assert os.path.exists(lib.LIB_PATH), "build the library first (__graft_entry__.build())"
+    L = C.CDLL(lib.LIB_PATH)
+    for s in lib.SYMBOLS:
+        assert hasattr(L, s), s
+    assert L.mtsb_abi_version() == abi.ABI_VERSION
+
+
+def test_struct_sizes_match_header():
+    assert C.sizeof(abi.Material) == 80 and C.sizeof(abi.Shape) == 32 and C.sizeof(abi.Emitter) == 48
+    assert abi.RAY_DTYPE.itemsize == 32 and abi.HIT_DTYPE.itemsize == 16
+
+
+def test_no_cpu_fallback():
+    """Without a device the product must fail loudly (MTSB_ERR_NO_DEVICE), never compute on the host."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from mitsuba_b200 import scenes
+    with pytest.raises(lib.MtsbError) as e:
+        lib.Scene(scenes.cbox(width=8, height=8, spp=1))
+    assert e.value.code == abi.ERR_NO_DEVICE
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "mitsuba_b200")
+    for dp, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                txt = open(os.path.join(dp, f), errors="replace").read()
+                assert not re.search(r"^\s*(import|from)\s+oracle\b", txt, flags=re.M), f
+                assert "liboracle" not in txt and "libmtsref" not in txt and "orc_" not in txt, f

@@ -1,0 +1,89 @@
+"""GPU: the wavefront `path` integrator (mtsb_render) against the oracle's Li loop.
+Random streams differ (counter-based vs sequential), so image parity is statistical:
+relMSE against a high-spp oracle image and the 3-sigma mean-luminance interval."""
+import numpy as np
+import pytest
+
+from mitsuba_b200 import abi, scenes
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+LUM = np.array([0.212671, 0.715160, 0.072169])
+
+
+def rel_mse(img, ref):
+    return float(np.mean((img - ref) ** 2 / (ref ** 2 + 1e-2)))
+
+
+def check_render(gpu_lib, oracle_mod, b, spp, ref_spp, label):
+    sc, orc = gpu_lib.Scene(b), oracle_mod.Oracle(b)
+    ref_stats = orc.render(spp=ref_spp, seed=11)
+    ref = orc.film_develop().astype(np.float64)
+    cpu_stats = orc.render(spp=spp, seed=5)
+    cpu = orc.film_develop().astype(np.float64)
+    st = sc.render(spp=spp, seed=7)
+    gpu = sc.film_develop().astype(np.float64)
+    assert st.samples == cpu_stats.samples and st.bad_samples == 0
+    assert np.isfinite(gpu).all()
+    # mean luminance inside the 3-sigma Monte Carlo interval of the per-sample estimator
+    n = ref_stats.samples
+    mean_ref = ref_stats.lum_sum / n
+    var = max(ref_stats.lum_sq_sum / n - mean_ref ** 2, 0.0)
+    sigma = np.sqrt(var / st.samples + var / n)
+    lum_gpu = float((gpu @ LUM).mean())
+    lum_ref = float((ref @ LUM).mean())
+    assert abs(lum_gpu - lum_ref) <= 3 * sigma + 1e-3 * lum_ref, (label, lum_gpu, lum_ref, sigma)
+    # relMSE at equal spp no worse than the CPU oracle's own (plus slack for a different random stream)
+    e_gpu, e_cpu = rel_mse(gpu, ref), rel_mse(cpu, ref)
+    assert e_gpu <= 1.25 * e_cpu + 1e-4, (label, e_gpu, e_cpu)
+    # same amount of work per sample: ray counts and path length (reference statistics counters)
+    for f, tol in (("closest_rays", 0.02), ("shade_events", 0.02), ("path_length_sum", 0.02)):
+        a, c = getattr(st, f) / st.samples, getattr(cpu_stats, f) / cpu_stats.samples
+        assert abs(a - c) <= tol * c, (label, f, a, c)
+    assert st.shadow_rays <= cpu_stats.shadow_rays        # zero-contribution shadow rays are not traced
+    sc.close()
+    return e_gpu, e_cpu
+
+
+def test_cbox_diffuse_area_light(gpu_lib, oracle_mod):
+    """BASELINE configs[0] at reduced resolution: cbox, maxDepth 8, diffuse, one area light."""
+    check_render(gpu_lib, oracle_mod, scenes.cbox(width=96, height=96, spp=32), 32, 256, "cbox")
+
+
+def test_cbox_twosided_unbounded_depth(gpu_lib, oracle_mod):
+    check_render(gpu_lib, oracle_mod, scenes.cbox(width=64, height=64, spp=16, max_depth=-1, twosided=True), 16, 128, "cbox-2s")
+
+
+def test_mixed_materials_env_and_area(gpu_lib, oracle_mod):
+    """configs[2] family at small size: diffuse / roughdielectric / roughconductor (Beckmann + GGX),
+    constant environment + area lights, maxDepth 10, rrDepth 5."""
+    b = scenes.scene_10m(width=96, height=54, spp=32, nu=24, nv=12, n_obj=12)
+    check_render(gpu_lib, oracle_mod, b, 32, 256, "mixed")
+
+
+def test_tile_and_sample_partition_is_exact(gpu_lib):
+    """Tile-interleaved and sample-split renders add up to the single-call render (8e):
+    the RNG is keyed by (pixel, global sample index), so only the fp32 add order differs."""
+    b = scenes.cbox(width=80, height=48, spp=8)
+    sc = gpu_lib.Scene(b)
+    sc.render(spp=8, seed=3)
+    whole = sc.film_download().astype(np.float64)
+    sc.film_clear()
+    for r in range(3):
+        sc.render(spp=8, seed=3, tile_index=r, tile_count=3, keep_film=True)
+    tiles = sc.film_download().astype(np.float64)
+    assert np.allclose(tiles, whole, rtol=1e-4, atol=1e-4)
+    sc.film_clear()
+    sc.render(spp=5, seed=3, spp_offset=0, keep_film=True)
+    sc.render(spp=3, seed=3, spp_offset=5, keep_film=True, spp_per_pass=2)
+    split = sc.film_download().astype(np.float64)
+    assert np.allclose(split, whole, rtol=1e-4, atol=1e-4)
+    sc.close()
+
+
+def test_point_light_and_hide_emitters(gpu_lib, oracle_mod):
+    b = scenes.cbox(width=48, height=48, spp=16)
+    b.add_point_light([278, 400, 279], [4e5, 4e5, 4e5])
+    b.set_integrator(max_depth=5, rr_depth=3, hide_emitters=True, sample_count=16)
+    check_render(gpu_lib, oracle_mod, b, 16, 128, "point")
