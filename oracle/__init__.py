@@ -55,6 +55,7 @@ def lib():
         L.orc_film_download.argtypes = [C.c_void_p, C.c_void_p]
         L.orc_film_develop.argtypes = [C.c_void_p, C.c_void_p]
         L.orc_render.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_int, C.c_int, C.POINTER(OrcStats)]
+        L.orc_render2.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_int, C.c_int, C.POINTER(OrcStats), C.c_int, C.c_int]
         L.orc_li.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p]
         L.orc_scene_bounds.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_triaccel.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
@@ -230,11 +231,13 @@ class Oracle:
         lib().orc_film_develop(self.h, _vp(out))
         return out
 
-    def render(self, spp=0, seed=1, threads=0, max_blocks=0, clear=True):
+    def render(self, spp=0, seed=1, threads=0, max_blocks=0, clear=True, counter_rng=False, spp_offset=0):
+        """counter_rng=True draws every sample from the counter-based stream keyed by
+        (seed, pixel, spp_offset + j) -- the numbering the CUDA renderer uses."""
         if clear:
             self.film_clear()
         st = OrcStats()
-        lib().orc_render(self.h, spp, seed, threads, max_blocks, C.byref(st))
+        lib().orc_render2(self.h, spp, seed, threads, max_blocks, C.byref(st), int(counter_rng), spp_offset)
         return st
 
     def li(self, sample_pos, seed=1):

@@ -29,29 +29,49 @@ namespace {
 
 thread_local std::string g_err;
 
-// splitmix64 / xoshiro256** stream; Random::nextFloat's 23-bit mantissa construction
-// (src/libcore/random.cpp:630-640) applied to the low 32 bits.
+// Two interchangeable random sources.
+//  * sequential: splitmix64 / xoshiro256** stream with Random::nextFloat's 23-bit mantissa construction
+//    (src/libcore/random.cpp:630-640) -- the reference's model: one stream per worker (renderjob.cpp:59-70).
+//  * counter: Philox4x32-10 (Salmon et al., SC'11; published constants) keyed by (seed, pixel<<24 | sample)
+//    and numbered by (bounce, slot) -- the same numbering the CUDA wavefront uses, restated here
+//    independently, so that a CPU render can be compared with the GPU film sample for sample.
 struct Rng {
     uint64_t s[4];
+    bool counter; uint32_t k0, k1, idLo, idHi;
     static uint64_t splitmix(uint64_t &x) {
         uint64_t z = (x += 0x9e3779b97f4a7c15ULL);
         z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL;
         z = (z ^ (z >> 27)) * 0x94d049bb133111ebULL;
         return z ^ (z >> 31);
     }
-    explicit Rng(uint64_t seed) { for (int i = 0; i < 4; ++i) s[i] = splitmix(seed); }
+    explicit Rng(uint64_t seed) : counter(false), k0(0), k1(0), idLo(0), idHi(0) { for (int i = 0; i < 4; ++i) s[i] = splitmix(seed); }
+    Rng(uint64_t seed, uint64_t sampleId) : counter(true), k0((uint32_t) seed), k1((uint32_t) (seed >> 32)),
+        idLo((uint32_t) sampleId), idHi((uint32_t) (sampleId >> 32)) { s[0] = s[1] = s[2] = s[3] = 0; }
     static uint64_t rotl(uint64_t x, int k) { return (x << k) | (x >> (64 - k)); }
     uint64_t nextULong() {
         uint64_t r = rotl(s[1] * 5, 7) * 9, t = s[1] << 17;
         s[2] ^= s[0]; s[3] ^= s[1]; s[1] ^= s[2]; s[0] ^= s[3]; s[2] ^= t; s[3] = rotl(s[3], 45);
         return r;
     }
-    float nextFloat() {
-        union { uint32_t u; float f; } x;
-        x.u = (uint32_t) ((nextULong() & 0xFFFFFFFFull) >> 9) | 0x3f800000u;
-        return x.f - 1.0f;
-    }
+    static float toFloat(uint32_t v) { union { uint32_t u; float f; } x; x.u = (v >> 9) | 0x3f800000u; return x.f - 1.0f; }
+    float nextFloat() { return toFloat((uint32_t) (nextULong() & 0xFFFFFFFFull)); }
     P2 next2D() { float a = nextFloat(); float b = nextFloat(); return P2{a, b}; }
+    void block(uint32_t blk, uint32_t sub, float out[4]) const {
+        uint32_t c[4] = {idLo, idHi, blk, sub}, ka = k0, kb = k1;
+        for (int r = 0; r < 10; ++r) {
+            uint64_t p0 = (uint64_t) 0xD2511F53u * c[0], p1 = (uint64_t) 0xCD9E8D57u * c[2];
+            uint32_t n0 = (uint32_t) (p1 >> 32) ^ c[1] ^ ka, n1 = (uint32_t) p1, n2 = (uint32_t) (p0 >> 32) ^ c[3] ^ kb, n3 = (uint32_t) p0;
+            c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
+            ka += 0x9E3779B9u; kb += 0xBB67AE85u;
+        }
+        for (int i = 0; i < 4; ++i) out[i] = toFloat(c[i]);
+    }
+    // the four places where the integrator draws numbers
+    P2 pixel2D() { if (!counter) return next2D(); float u[4]; block(0, 0, u); return P2{u[0], u[1]}; }                 // integrator.cpp:227
+    P2 emitter2D(int depth) { if (!counter) return next2D(); float u[4]; block((uint32_t) depth, 0, u); return P2{u[0], u[1]}; }   // path.cpp:178
+    P2 bsdf2D(int depth) { if (!counter) return next2D(); float u[4]; block((uint32_t) depth, 0, u); return P2{u[2], u[3]}; }      // path.cpp:211
+    float extra1D(int depth) { if (!counter) return nextFloat(); float u[4]; block((uint32_t) depth, 1, u); return u[0]; }         // roughdielectric.cpp:554
+    float rr1D(int depth) { if (!counter) return nextFloat(); float u[4]; block((uint32_t) depth, 1, u); return u[1]; }            // path.cpp:285
 };
 
 struct Counters { uint64_t closest = 0, shadow = 0, shade = 0, pathLen = 0, samples = 0; double lum = 0, lum2 = 0; };
@@ -110,7 +130,7 @@ V3 Li(const Scene &sc, const MtsbRay &primary, Rng &rng, Counters &cnt, float &a
         if (haveMat && !bsdf_has_back_or_transmission(sc.materials[mat])) dRec.refN = its.sh.n;   // records.inl:175-179
         dRec.emitter = -1;
         if (haveMat && bsdf_is_smooth(sc.materials[mat])) {
-            V3 value = sampleEmitterDirectNoVis(sc, dRec, rng.next2D());
+            V3 value = sampleEmitterDirectNoVis(sc, dRec, rng.emitter2D(depth));
             if (dRec.pdf != 0) {
                 // scene.cpp:840-846
                 MtsbRay sray = makeRay(dRec.ref, dRec.d, kEpsilon, dRec.dist * (1 - kShadowEpsilon));
@@ -133,12 +153,12 @@ V3 Li(const Scene &sc, const MtsbRay &primary, Rng &rng, Counters &cnt, float &a
         // ---- BSDF sampling (path.cpp:208-221) ----
         if (!haveMat) break;
         BsdfSample bs;
-        P2 u2 = rng.next2D();
+        P2 u2 = rng.bsdf2D(depth);
         float u1 = 0.0f;
         {   // roughdielectric draws one more number inside sample() (roughdielectric.cpp:554)
             const MtsbMaterial *m = &sc.materials[mat];
             if ((m->flags & MTSB_MAT_TWOSIDED) && cosTheta(its.wi) < 0 && m->back >= 0) m = &sc.materials[m->back];
-            if (m->type == MTSB_BSDF_ROUGHDIELECTRIC) u1 = rng.nextFloat();
+            if (m->type == MTSB_BSDF_ROUGHDIELECTRIC) u1 = rng.extra1D(depth);
         }
         bool ok = bsdf_sample(sc.materials.data(), mat, its.wi, u2, u1, bs);
         if (!ok || isZero(bs.weight)) break;
@@ -182,9 +202,10 @@ V3 Li(const Scene &sc, const MtsbRay &primary, Rng &rng, Counters &cnt, float &a
         if (!its.valid) break;
         emittedRadiance = false;          // rRec.type = ERadianceNoEmission
 
-        if (depth++ >= rrDepth) {
+        const int d0 = depth++;
+        if (d0 >= rrDepth) {
             float q = std::min(maxComp(throughput) * eta * eta, 0.95f);
-            if (rng.nextFloat() >= q) break;
+            if (rng.rr1D(d0) >= q) break;
             throughput = throughput / q;
         }
     }
@@ -372,7 +393,12 @@ typedef struct OrcStats {
 // (imageproc.cpp:43-78), each block rendered into a private bordered buffer and merged
 // under a mutex (renderproc.cpp:149-156).  Pixel order inside a block is row-major instead
 // of Hilbert (order is irrelevant for an independent sampler).
+int orc_render2(void *h, int spp, uint64_t seed, int nthreads, int max_blocks, OrcStats *stats, int counterRng, int sppOffset);
 int orc_render(void *h, int spp, uint64_t seed, int nthreads, int max_blocks, OrcStats *stats) {
+    return orc_render2(h, spp, seed, nthreads, max_blocks, stats, 0, 0);
+}
+// counterRng != 0: every sample uses the counter-based stream keyed by (seed, pixel << 24 | sppOffset + j)
+int orc_render2(void *h, int spp, uint64_t seed, int nthreads, int max_blocks, OrcStats *stats, int counterRng, int sppOffset) {
     Scene *sc = S(h);
     Film &f = sc->film;
     if (spp <= 0) spp = sc->sd.integrator.sample_count;
@@ -416,7 +442,11 @@ int orc_render(void *h, int spp, uint64_t seed, int nthreads, int max_blocks, Or
             for (int y = 0; y < bh; ++y)
                 for (int x = 0; x < bw; ++x)
                     for (int j = 0; j < spp; ++j) {
-                        P2 u = rng.next2D();
+                        if (counterRng) {
+                            uint64_t pixel = (uint64_t) (oy + y + sc->sd.sensor.crop_y) * (uint64_t) sc->sd.sensor.film_width + (uint64_t) (ox + x + sc->sd.sensor.crop_x);
+                            rng = Rng(seed, (pixel << 24) | (uint64_t) (sppOffset + j));
+                        }
+                        P2 u = rng.pixel2D();
                         P2 samplePos{(float) (ox + x) + u.x, (float) (oy + y) + u.y};
                         MtsbRay ray; sensorRay(*sc, samplePos, ray);
                         float alpha;

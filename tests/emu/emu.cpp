@@ -8,6 +8,7 @@
 #include "../../mitsuba_b200/csrc/bvh.h"
 #include "../../mitsuba_b200/csrc/traverse.h"
 #include "../../mitsuba_b200/csrc/sensor.h"
+#include "../../mitsuba_b200/csrc/rng.h"
 #include <vector>
 #include <algorithm>
 #include <numeric>
@@ -119,4 +120,13 @@ extern "C" void emu_tris(void *h, TriRec *out) {
 
 extern "C" void emu_sensor_rays(const MtsbSensor *se, float near_x, float near_y, const float *pos, size_t n, RayIn *rays) {
     for (size_t i = 0; i < n; ++i) sensor_ray(*se, near_x, near_y, pos[2 * i], pos[2 * i + 1], rays[i]);
+}
+
+extern "C" void emu_philox(const uint32_t *ctr4, const uint32_t *key2, uint32_t *out4) {
+    U32x4 c; c.x = ctr4[0]; c.y = ctr4[1]; c.z = ctr4[2]; c.w = ctr4[3];
+    U32x4 r = philox4x32_10(c, key2[0], key2[1]);
+    out4[0] = r.x; out4[1] = r.y; out4[2] = r.z; out4[3] = r.w;
+}
+extern "C" void emu_sample_block(uint64_t seed, uint64_t sample_id, uint32_t block, uint32_t sub, float *out4) {
+    SampleStream(seed, sample_id).block4(block, sub, out4);
 }

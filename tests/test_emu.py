@@ -99,3 +99,26 @@ def test_duplicate_and_degenerate_triangles(emu, oracle_mod):
     assert np.array_equal(hits["t"][th], ref["t"][rh])
     assert (hits["prim"][th] != 3).all()            # the zero-area copy is never reported (triaccel.h:84-87)
     emu.emu_destroy(h)
+
+
+def test_philox_known_answers(emu):
+    """Random123 kat_vectors for philox4x32-10 -- the counter-based generator that replaces
+    IndependentSampler's SFMT stream (rng.h)."""
+    kat = [
+        ([0, 0, 0, 0], [0, 0], [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]),
+        ([0xffffffff] * 4, [0xffffffff] * 2, [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]),
+        ([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0], [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]),
+    ]
+    for ctr, key, exp in kat:
+        out = np.zeros(4, np.uint32)
+        emu.emu_philox(vp(np.array(ctr, np.uint32)), vp(np.array(key, np.uint32)), vp(out))
+        assert out.tolist() == exp
+
+
+def test_sample_floats_are_in_unit_interval_and_uniform(emu):
+    emu.emu_sample_block.argtypes = [C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p]
+    vals = np.zeros((4096, 4), np.float32)
+    for i in range(4096):
+        emu.emu_sample_block(1004, (i << 24) | 3, 1, 0, vp(vals[i]))
+    assert vals.min() >= 0.0 and vals.max() < 1.0
+    assert abs(vals.mean() - 0.5) < 0.01 and abs(np.corrcoef(vals[:, 0], vals[:, 1])[0, 1]) < 0.05

@@ -1,6 +1,13 @@
 """GPU: the wavefront `path` integrator (mtsb_render) against the oracle's Li loop.
-Random streams differ (counter-based vs sequential), so image parity is statistical:
-relMSE against a high-spp oracle image and the 3-sigma mean-luminance interval."""
+
+Two kinds of check:
+ * same-stream parity -- the oracle is rendered with the counter-based random numbers the GPU uses
+   (oracle.render(counter_rng=True)); films must agree pixel by pixel (fp32 rounding only) and the
+   ray / shade / path-length counters must be identical up to rounding-induced decision flips;
+ * independent-stream parity -- against the oracle with its sequential generator (the reference's
+   model): mean luminance inside the 3-sigma Monte Carlo interval, relMSE against a high-spp oracle
+   image no worse than 3x the CPU oracle's own at equal spp (the squared-error estimator is heavy
+   tailed; the same-stream test is the sharp one).  Tolerances per SURVEY.md 8(d)."""
 import numpy as np
 import pytest
 
@@ -36,14 +43,62 @@ def check_render(gpu_lib, oracle_mod, b, spp, ref_spp, label):
     assert abs(lum_gpu - lum_ref) <= 3 * sigma + 1e-3 * lum_ref, (label, lum_gpu, lum_ref, sigma)
     # relMSE at equal spp no worse than the CPU oracle's own (plus slack for a different random stream)
     e_gpu, e_cpu = rel_mse(gpu, ref), rel_mse(cpu, ref)
-    assert e_gpu <= 1.25 * e_cpu + 1e-4, (label, e_gpu, e_cpu)
+    assert e_gpu <= 3.0 * e_cpu + 1e-4, (label, e_gpu, e_cpu)
     # same amount of work per sample: ray counts and path length (reference statistics counters)
     for f, tol in (("closest_rays", 0.02), ("shade_events", 0.02), ("path_length_sum", 0.02)):
         a, c = getattr(st, f) / st.samples, getattr(cpu_stats, f) / cpu_stats.samples
         assert abs(a - c) <= tol * c, (label, f, a, c)
-    assert st.shadow_rays <= cpu_stats.shadow_rays        # zero-contribution shadow rays are not traced
     sc.close()
     return e_gpu, e_cpu
+
+
+def check_same_stream(gpu_lib, oracle_mod, b, spp, label, seed=9):
+    """GPU film == oracle film when both draw the same random numbers."""
+    sc, orc = gpu_lib.Scene(b), oracle_mod.Oracle(b)
+    st = sc.render(spp=spp, seed=seed)
+    fg = sc.film_download().astype(np.float64)
+    ost = orc.render(spp=spp, seed=seed, counter_rng=True)
+    fo = orc.film_download().astype(np.float64)
+    bad = (np.abs(fg - fo) > 1e-3 * np.maximum(np.abs(fo), 1e-3))[..., :3].any(-1)
+    assert bad.mean() <= 2e-3, (label, int(bad.sum()), bad.size)
+    assert rel_mse(sc.film_develop().astype(np.float64), orc.film_develop().astype(np.float64)) < 1e-5
+    assert st.samples == ost.samples
+    for f in ("closest_rays", "shade_events", "path_length_sum"):
+        a, c = getattr(st, f), getattr(ost, f)
+        assert abs(a - c) <= 1e-3 * c + 2, (label, f, a, c)
+    # the GPU skips shadow rays whose contribution is already zero (BSDF value 0); never traces more
+    assert st.shadow_rays <= ost.shadow_rays, (label, st.shadow_rays, ost.shadow_rays)
+    sc.close()
+
+
+@pytest.mark.parametrize("max_depth", [1, 2, 3, 8, -1])
+def test_same_stream_cbox_depths(gpu_lib, oracle_mod, max_depth):
+    b = scenes.cbox(width=64, height=64, spp=2, max_depth=max_depth)
+    check_same_stream(gpu_lib, oracle_mod, b, 2, "cbox maxDepth=%d" % max_depth)
+
+
+def test_same_stream_cbox_box_filter_and_twosided(gpu_lib, oracle_mod):
+    from mitsuba_b200.scenedesc import look_at
+    b = scenes.cbox(width=50, height=37, spp=3, twosided=True)
+    b.set_sensor(look_at([278, 273, -800], [278, 273, -799], [0, 1, 0]), 39.3077, 50, 37, rfilter="box", near_clip=10.0, far_clip=2800.0)
+    check_same_stream(gpu_lib, oracle_mod, b, 3, "cbox box twosided")
+
+
+def test_same_stream_mixed_materials(gpu_lib, oracle_mod):
+    b = scenes.scene_10m(width=96, height=54, spp=4, nu=24, nv=12, n_obj=12)
+    check_same_stream(gpu_lib, oracle_mod, b, 4, "mixed")
+
+
+def test_same_stream_ggx_conductors_1m_family(gpu_lib, oracle_mod):
+    b = scenes.scene_1m(width=96, height=54, spp=4, nu=24, nv=12, n_obj=8)
+    check_same_stream(gpu_lib, oracle_mod, b, 4, "1m-small")
+
+
+def test_same_stream_point_light_hide_emitters_strict_normals(gpu_lib, oracle_mod):
+    b = scenes.cbox(width=48, height=48, spp=4)
+    b.add_point_light([278, 400, 279], [4e5, 4e5, 4e5])
+    b.set_integrator(max_depth=5, rr_depth=3, hide_emitters=True, strict_normals=True, sample_count=4)
+    check_same_stream(gpu_lib, oracle_mod, b, 4, "point+hide+strict")
 
 
 def test_cbox_diffuse_area_light(gpu_lib, oracle_mod):
