@@ -345,48 +345,79 @@ struct ShadowResolve {
     }
 };
 
-// ImageBlock::put for every sample of one 32x32 tile, accumulated in shared memory, then one
-// add per bordered pixel into the film (imageblock.h:143-206, renderproc.cpp:149-156).
+// ImageBlock::put for every sample of one 32x32 tile (imageblock.h:143-206) followed by the
+// overlap-add of the bordered block into the film (renderproc.cpp:149-156), written as a GATHER:
+// the samples of the tile are staged in shared memory (MTSB_SPLAT_CHUNK samples per pixel at a
+// time, row-major), then every thread owns bordered pixels and sums the samples whose footprint
+// covers them -- same weights as the scatter form, no shared-memory atomics, and a fixed
+// summation order inside the tile.  Only the final add into the film is atomic (tile borders overlap).
+#define MTSB_SPLAT_CHUNK 4
 __global__ void __launch_bounds__(256) k_splat(SceneView sc, PathBuffers pb, PassInfo ps, unsigned long long *bad) {
-    extern __shared__ float s_tile[];
+    extern __shared__ float4 s_stage[];                 // [chunk][1024] value (rgb, alpha or -1 = skip), then [chunk][1024] float2 positions
+    const int chunk = min((int) ps.spp_pass, MTSB_SPLAT_CHUNK);
+    float4 *s_val = s_stage;
+    float2 *s_pos = reinterpret_cast<float2 *>(s_stage + chunk * MTSB_TILE * MTSB_TILE);
     const int b = sc.film_border, side = MTSB_TILE + 2 * b;
-    const int n_acc = side * side * 5;
-    for (int i = threadIdx.x; i < n_acc; i += blockDim.x) s_tile[i] = 0.0f;
-    __syncthreads();
     const int tile = pb.tiles[ps.tile_first + blockIdx.x];
     const int ox = (tile % (int) ps.tiles_x) * MTSB_TILE, oy = (tile / (int) ps.tiles_x) * MTSB_TILE;
     const int bw = min(MTSB_TILE, sc.film_w - ox), bh = min(MTSB_TILE, sc.film_h - oy);
+    const int sx = bw + 2 * b, sy = bh + 2 * b;
     const uint32_t per_tile = MTSB_TILE * MTSB_TILE * ps.spp_pass;
     const uint32_t slot0 = blockIdx.x * per_tile;
-    unsigned long long n_bad = 0;
-    for (uint32_t i = threadIdx.x; i < per_tile; i += blockDim.x) {
-        const uint32_t slot = slot0 + i;
-        const uint32_t fl = __float_as_uint(pb.refn_flags[slot].w);
-        if (!(fl & PF_VALID)) continue;
-        const float4 lb = pb.L_bpdf[slot];
-        const float2 sp = pb.spos[slot];
-        const float v[5] = {lb.x, lb.y, lb.z, (fl & PF_ALPHA) ? 1.0f : 0.0f, 1.0f};
-        if (!(isfinite(v[0]) && isfinite(v[1]) && isfinite(v[2]))) { ++n_bad; continue; }      // imageblock.h:147-153
-        Footprint f;
-        film_footprint(sc, sp.x, sp.y, ox, oy, bw + 2 * b, bh + 2 * b, f);
-        for (int y = 0; y < f.ny; ++y)
-            for (int x = 0; x < f.nx; ++x) {
-                const float w = f.wx[x] * f.wy[y];
-                float *dest = s_tile + ((f.miny + y) * side + (f.minx + x)) * 5;
-#pragma unroll
-                for (int k = 0; k < 5; ++k) atomicAdd(dest + k, w * v[k]);
-            }
-    }
-    __syncthreads();
+    const float r = sc.filter_radius;
     const int fsx = sc.film_w + 2 * b;
-    for (int i = threadIdx.x; i < n_acc; i += blockDim.x) {
-        const float val = s_tile[i];
-        if (val == 0.0f) continue;
-        const int k = i % 5, p = i / 5, x = p % side, y = p / side;
-        if (x >= bw + 2 * b || y >= bh + 2 * b) continue;
-        atomicAdd(sc.film + ((size_t) (oy + y) * fsx + (ox + x)) * 5 + k, val);
+    unsigned long long n_bad = 0;
+    for (uint32_t c0 = 0; c0 < ps.spp_pass; c0 += (uint32_t) chunk) {
+        const int nc = min(chunk, (int) (ps.spp_pass - c0));
+        // ---- stage: slot (pixel in Morton order, sample) -> smem[sample][y][x] ----
+        for (int i = threadIdx.x; i < nc * MTSB_TILE * MTSB_TILE; i += blockDim.x) {
+            const uint32_t pix = (uint32_t) i / (uint32_t) nc, sl = (uint32_t) i % (uint32_t) nc;
+            const uint32_t slot = slot0 + pix * ps.spp_pass + c0 + sl;
+            const uint32_t fl = __float_as_uint(pb.refn_flags[slot].w);
+            const int x = (int) compact1by1(pix), y = (int) compact1by1(pix >> 1);
+            float4 val = make_float4(0, 0, 0, -1.0f);
+            float2 pos = make_float2(0, 0);
+            if (fl & PF_VALID) {
+                const float4 lb = pb.L_bpdf[slot];
+                if (isfinite(lb.x) && isfinite(lb.y) && isfinite(lb.z)) {               // imageblock.h:147-153
+                    val = make_float4(lb.x, lb.y, lb.z, (fl & PF_ALPHA) ? 1.0f : 0.0f);
+                    const float2 sp = pb.spos[slot];
+                    // position inside the bordered block: pos - 0.5 - (offset - border)
+                    pos = make_float2(sp.x - 0.5f - (float) (ox - b), sp.y - 0.5f - (float) (oy - b));
+                } else ++n_bad;
+            }
+            s_val[sl * MTSB_TILE * MTSB_TILE + y * MTSB_TILE + x] = val;
+            s_pos[sl * MTSB_TILE * MTSB_TILE + y * MTSB_TILE + x] = pos;
+        }
+        __syncthreads();
+        // ---- gather: one bordered pixel per thread iteration ----
+        for (int p = threadIdx.x; p < sx * sy; p += blockDim.x) {
+            const int X = p % sx, Y = p / sx;
+            // tile pixels whose samples can reach (X, Y): |X - px| <= r with px in [x' + b - 0.5, x' + b + 0.5)
+            const int x_lo = max(0, (int) ceilf((float) (X - b) - r - 0.5f)), x_hi = min(bw - 1, (int) floorf((float) (X - b) + r + 0.5f));
+            const int y_lo = max(0, (int) ceilf((float) (Y - b) - r - 0.5f)), y_hi = min(bh - 1, (int) floorf((float) (Y - b) + r + 0.5f));
+            float acc[5] = {0, 0, 0, 0, 0};
+            for (int sl = 0; sl < nc; ++sl)
+                for (int yy = y_lo; yy <= y_hi; ++yy)
+                    for (int xx = x_lo; xx <= x_hi; ++xx) {
+                        const int j = sl * MTSB_TILE * MTSB_TILE + yy * MTSB_TILE + xx;
+                        const float4 val = s_val[j];
+                        if (val.w < 0.0f) continue;
+                        const float2 pos = s_pos[j];
+                        // ImageBlock::put pixel range of this sample, clipped to the block
+                        if ((float) X < ceilf(pos.x - r) || (float) X > floorf(pos.x + r) ||
+                            (float) Y < ceilf(pos.y - r) || (float) Y > floorf(pos.y + r)) continue;
+                        const float w = filter_discretized(sc, (float) X - pos.x) * filter_discretized(sc, (float) Y - pos.y);
+                        acc[0] += w * val.x; acc[1] += w * val.y; acc[2] += w * val.z; acc[3] += w * val.w; acc[4] += w;
+                    }
+            float *dest = sc.film + ((size_t) (oy + Y) * fsx + (ox + X)) * 5;
+#pragma unroll
+            for (int k = 0; k < 5; ++k) if (acc[k] != 0.0f) atomicAdd(dest + k, acc[k]);
+        }
+        __syncthreads();
     }
-    if (n_bad) atomicAdd(bad, n_bad);
+    for (int o = 16; o; o >>= 1) n_bad += __shfl_xor_sync(0xFFFFFFFFu, n_bad, o);
+    if ((threadIdx.x & 31) == 0 && n_bad) atomicAdd(bad, n_bad);
 }
 
 // ---- host side ---------------------------------------------------------------------------
@@ -496,7 +527,8 @@ extern "C" int mtsb_render(mtsb_scene_t scene, const MtsbRenderParams *params, M
     StageTimer timer(s->stream);
     cudaEvent_t ev0, ev1; cudaEventCreate(&ev0); cudaEventCreate(&ev1);
     cudaEventRecord(ev0, s->stream);
-    const size_t splat_smem = (size_t) (MTSB_TILE + 2 * v.film_border) * (MTSB_TILE + 2 * v.film_border) * 5 * sizeof(float);
+    const size_t splat_smem = (size_t) MTSB_SPLAT_CHUNK * MTSB_TILE * MTSB_TILE * (sizeof(float4) + sizeof(float2));
+    MTSB_CUDA(cudaFuncSetAttribute(k_splat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) splat_smem));
     uint32_t n_passes = 0;
     uint64_t samples = 0;
     int status = MTSB_OK;

@@ -84,15 +84,23 @@ __global__ void __launch_bounds__(MTSB_TRACE_BLOCK) k_trace(TraceArgs a, Epilogu
             if (exhausted) break;
             continue;
         }
-        // ---- traverse until the warp has drained below the refill threshold ----
-        while (active) {
-            if (tr.template step<ANY>(a.nodes, a.tris)) {
+        // ---- lock-step traversal until the warp has drained below the refill threshold ----
+        // Each iteration: (a) lanes without pending triangles visit one node, (b) lanes with
+        // pending triangles test one, (c) pop / finish.  The three regions are warp-converged.
+        unsigned live;
+        do {
+            if (active && tr.wants_node()) tr.visit_node(a.nodes);
+            __syncwarp();
+            bool done = false;
+            if (active && tr.tg != 0) done = tr.template test_triangle<ANY>(a.tris);
+            __syncwarp();
+            if (active && (done || tr.advance())) {
                 ep(ray_idx, ray, tr.hit);
                 visited += tr.steps;
                 active = false;
             }
-            if (!exhausted && __popc(__activemask()) < MTSB_REFILL) break;
-        }
+            live = __ballot_sync(0xFFFFFFFFu, active);
+        } while (live != 0 && (exhausted || __popc(live) >= MTSB_REFILL));
     }
     if (a.stat_nodes) {
         for (int o = 16; o; o >>= 1) visited += __shfl_xor_sync(0xFFFFFFFFu, visited, o);

@@ -109,12 +109,21 @@ template <class Stack> struct Traversal {
         ng_x = 0; ng_y = 0x80000000u;
         hit.prim = MTSB_NO_HIT_ID; hit.u = 0; hit.v = 0; hit.t = MTSB_INF;
         stack.reset();
-        steps = 0;
+        steps = 0; tg = 0; tri_base = 0;
     }
 
-    // One node visit (+ the triangles it references).  Returns true when the query is finished.
-    template <bool ANY> MTSB_HD bool step(const U4 *nodes, const U4 *tris) {
-        // ---- take the nearest pending child of the current group ----
+    // The query is a small state machine with three transitions, so that a warp can run its 32
+    // rays in lock step: every iteration each lane (a) visits one node if it has no triangle
+    // pending, (b) tests ONE pending triangle, (c) pops the next group or finishes.  Lanes with
+    // many triangles therefore never hold back lanes that are descending.
+    // Invariant between iterations: tg != 0 (triangles pending) or ng_y has child-hit bits.
+    uint32_t tg;                  // pending triangle bits of the current node
+    uint32_t tri_base;            // first triangle record of the current node
+
+    MTSB_HD bool wants_node() const { return tg == 0; }
+
+    // (a) take the nearest pending child of the current group and intersect its 8 children
+    MTSB_HD void visit_node(const U4 *nodes) {
         const uint32_t hits_imask = ng_y;
         const int bit = bfind(hits_imask);
         const uint32_t base = ng_x;
@@ -167,28 +176,38 @@ template <class Stack> struct Traversal {
         }
         ng_x = n1.x;
         ng_y = (hitmask & 0xFF000000u) | (e_imask >> 24);
-        uint32_t tg = hitmask & 0x00FFFFFFu;
-        const U4 *tp = tris + 3 * (size_t) n1.y;
+        tg = hitmask & 0x00FFFFFFu;
+        tri_base = n1.y;
+    }
 
-        // ---- triangles referenced by this node ----
-        while (tg) {
-            const int i = bfind(tg);
-            tg &= ~(1u << i);
-            const U4 q0 = ld16(tp + 3 * i), q1 = ld16(tp + 3 * i + 1), q2 = ld16(tp + 3 * i + 2);
-            float u, v, t;
-            if (tri_test(q0, q1, q2, ox, oy, oz, dx, dy, dz, tmin, tmax, u, v, t)) {
-                hit.prim = q2.z; hit.u = u; hit.v = v; hit.t = t;
-                if (ANY) return true;
-                tmax = t;
-            }
-        }
-
-        // ---- next group ----
-        if (ng_y <= 0x00FFFFFFu) {
-            if (stack.empty()) return true;
-            stack.pop(ng_x, ng_y);
+    // (b) test one pending triangle; returns true when an any-hit query is satisfied
+    template <bool ANY> MTSB_HD bool test_triangle(const U4 *tris) {
+        const int i = bfind(tg);
+        tg &= ~(1u << i);
+        const U4 *tp = tris + 3 * ((size_t) tri_base + (size_t) i);
+        const U4 q0 = ld16(tp), q1 = ld16(tp + 1), q2 = ld16(tp + 2);
+        float u, v, t;
+        if (tri_test(q0, q1, q2, ox, oy, oz, dx, dy, dz, tmin, tmax, u, v, t)) {
+            hit.prim = q2.z; hit.u = u; hit.v = v; hit.t = t;
+            if (ANY) return true;
+            tmax = t;
         }
         return false;
+    }
+
+    // (c) next group: returns true when the query is finished
+    MTSB_HD bool advance() {
+        if (tg != 0 || ng_y > 0x00FFFFFFu) return false;
+        if (stack.empty()) return true;
+        stack.pop(ng_x, ng_y);
+        return false;
+    }
+
+    // one lock-step iteration for a single ray
+    template <bool ANY> MTSB_HD bool step(const U4 *nodes, const U4 *tris) {
+        if (wants_node()) visit_node(nodes);
+        if (tg != 0 && test_triangle<ANY>(tris)) return true;
+        return advance();
     }
 };
 
