@@ -37,6 +37,7 @@ MTSB_HD float fsub(float a, float b) { return __fsub_rn(a, b); }
 MTSB_HD float fdiv(float a, float b) { return __fdiv_rn(a, b); }
 MTSB_HD float fsqrt(float a) { return __fsqrt_rn(a); }
 MTSB_HD float frcp_fast(float a) { return __frcp_rn(a); }
+MTSB_HD float fdiv_approx(float a, float b) { return __fdividef(a, b); }
 MTSB_HD uint32_t f2u(float f) { return __float_as_uint(f); }
 MTSB_HD float u2f(uint32_t u) { return __uint_as_float(u); }
 MTSB_HD int bfind(uint32_t v) { return 31 - __clz(v); }
@@ -51,6 +52,7 @@ MTSB_HD float fsub(float a, float b) { return a - b; }
 MTSB_HD float fdiv(float a, float b) { return a / b; }
 MTSB_HD float fsqrt(float a) { return sqrtf(a); }
 MTSB_HD float frcp_fast(float a) { return 1.0f / a; }
+MTSB_HD float fdiv_approx(float a, float b) { return (a / b) * 1.0000002f; }   // deliberately not the exact quotient
 MTSB_HD uint32_t f2u(float f) { union { float f; uint32_t u; } x; x.f = f; return x.u; }
 MTSB_HD float u2f(uint32_t u) { union { float f; uint32_t u; } x; x.u = u; return x.f; }
 MTSB_HD int bfind(uint32_t v) { return v ? 31 - __builtin_clz(v) : -1; }

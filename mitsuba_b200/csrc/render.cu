@@ -354,10 +354,13 @@ struct ShadowResolve {
 #define MTSB_SPLAT_CHUNK 4
 __global__ void __launch_bounds__(256) k_splat(SceneView sc, PathBuffers pb, PassInfo ps, unsigned long long *bad) {
     extern __shared__ float4 s_stage[];                 // [chunk][1024] value (rgb, alpha or -1 = skip), then [chunk][1024] float2 positions
+    __shared__ float s_filter[32];                      // the discretised filter (a per-thread index into kernel parameters would serialise)
+    if (threadIdx.x < 32) s_filter[threadIdx.x] = sc.filter_table[threadIdx.x];
+    const float f_scale = sc.filter_scale;
     const int chunk = min((int) ps.spp_pass, MTSB_SPLAT_CHUNK);
     float4 *s_val = s_stage;
     float2 *s_pos = reinterpret_cast<float2 *>(s_stage + chunk * MTSB_TILE * MTSB_TILE);
-    const int b = sc.film_border, side = MTSB_TILE + 2 * b;
+    const int b = sc.film_border;
     const int tile = pb.tiles[ps.tile_first + blockIdx.x];
     const int ox = (tile % (int) ps.tiles_x) * MTSB_TILE, oy = (tile / (int) ps.tiles_x) * MTSB_TILE;
     const int bw = min(MTSB_TILE, sc.film_w - ox), bh = min(MTSB_TILE, sc.film_h - oy);
@@ -407,7 +410,8 @@ __global__ void __launch_bounds__(256) k_splat(SceneView sc, PathBuffers pb, Pas
                         // ImageBlock::put pixel range of this sample, clipped to the block
                         if ((float) X < ceilf(pos.x - r) || (float) X > floorf(pos.x + r) ||
                             (float) Y < ceilf(pos.y - r) || (float) Y > floorf(pos.y + r)) continue;
-                        const float w = filter_discretized(sc, (float) X - pos.x) * filter_discretized(sc, (float) Y - pos.y);
+                        const float w = s_filter[min((int) fabsf(((float) X - pos.x) * f_scale), 31)] *
+                                        s_filter[min((int) fabsf(((float) Y - pos.y) * f_scale), 31)];
                         acc[0] += w * val.x; acc[1] += w * val.y; acc[2] += w * val.z; acc[3] += w * val.w; acc[4] += w;
                     }
             float *dest = sc.film + ((size_t) (oy + Y) * fsx + (ox + X)) * 5;
@@ -508,8 +512,8 @@ extern "C" int mtsb_render(mtsb_scene_t scene, const MtsbRenderParams *params, M
     if (stats) memset(stats, 0, sizeof(*stats));
     if (tiles.empty()) { MTSB_CUDA(cudaStreamSynchronize(s->stream)); return MTSB_OK; }
 
-    // pass shape: about 8M path slots in flight
-    const uint64_t target = 8ull << 20;
+    // pass shape: about 16M path slots in flight
+    const uint64_t target = 16ull << 20;
     const uint64_t px_per_tile = MTSB_TILE * MTSB_TILE;
     uint32_t spp_pass = params->spp_per_pass > 0 ? (uint32_t) params->spp_per_pass
                                                  : (uint32_t) std::max<uint64_t>(1, std::min<uint64_t>((uint64_t) spp, target / (tiles.size() * px_per_tile)));

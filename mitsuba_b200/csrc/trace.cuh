@@ -8,7 +8,7 @@ namespace mtsb {
 #define MTSB_TRACE_BLOCK 128
 #define MTSB_SM_STACK 8        /* stack entries per thread kept in shared memory   */
 #define MTSB_LOCAL_STACK 56    /* overflow entries per thread in local memory      */
-#define MTSB_REFILL 20         /* refill a warp when fewer lanes than this are busy */
+#define MTSB_REFILL 26         /* refill a warp when fewer lanes than this are busy */
 
 // Shared-memory short stack with local-memory overflow.
 struct SmemStack {

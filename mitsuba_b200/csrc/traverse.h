@@ -64,8 +64,25 @@ MTSB_HD bool tri_test(const U4 q0, const U4 q1, const U4 q2, float ox, float oy,
     else if (k == 1) { o_u = oz; o_v = ox; o_k = oy; d_u = dz; d_v = dx; d_k = dy; }
     else if (k == 2) { o_u = ox; o_v = oy; o_k = oz; d_u = dx; d_v = dy; d_k = dz; }
     else return false;
-    t = fdiv(fsub(fsub(fsub(n_d, fmul(o_u, n_u)), fmul(o_v, n_v)), o_k),
-             fadd(fadd(fmul(d_u, n_u), fmul(d_v, n_v)), d_k));
+    const float num = fsub(fsub(fsub(n_d, fmul(o_u, n_u)), fmul(o_v, n_v)), o_k);
+    const float den = fadd(fadd(fmul(d_u, n_u), fmul(d_v, n_v)), d_k);
+    {
+        // Conservative early-out with an approximate quotient: a triangle is dropped here only when
+        // the exactly rounded evaluation below could not accept it (margins of ~64 ulp against the
+        // few ulp by which the two evaluations can differ).  Everything that survives is decided by
+        // the exact arithmetic, so accepted hits and their t,u,v are unchanged.
+        const float ta = fdiv_approx(num, den);
+        const float et = 8e-6f * fabsf(ta);
+        if (ta < mint - et || ta > maxt + et) return false;
+        const float pu = ta * d_u, pv = ta * d_v;
+        const float hua = (o_u + pu) - a_u, hva = (o_v + pv) - a_v;
+        const float ehu = 8e-6f * (fabsf(o_u) + fabsf(pu) + fabsf(a_u)), ehv = 8e-6f * (fabsf(o_v) + fabsf(pv) + fabsf(a_v));
+        const float ua = hva * b_nu + hua * b_nv, va = hua * c_nu + hva * c_nv;
+        const float eu = fabsf(b_nu) * ehv + fabsf(b_nv) * ehu + 8e-6f * (fabsf(hva * b_nu) + fabsf(hua * b_nv));
+        const float ev = fabsf(c_nu) * ehu + fabsf(c_nv) * ehv + 8e-6f * (fabsf(hua * c_nu) + fabsf(hva * c_nv));
+        if (ua < -eu || va < -ev || ua + va > 1.0f + eu + ev + 8e-6f) return false;
+    }
+    t = fdiv(num, den);
     if (t < mint || t > maxt) return false;
     const float hu = fsub(fadd(o_u, fmul(t, d_u)), a_u);
     const float hv = fsub(fadd(o_v, fmul(t, d_v)), a_v);
@@ -98,6 +115,9 @@ template <class Stack> struct Traversal {
     HitOut hit;
     Stack stack;
     uint32_t steps;               // nodes visited (statistics)
+#if !MTSB_DEVICE_CODE
+    uint32_t tri_tests = 0;       // triangle tests (emulation statistics only)
+#endif
 
     MTSB_HD void begin(const RayIn &r, float mint, float maxt) {
         ox = r.ox; oy = r.oy; oz = r.oz; dx = r.dx; dy = r.dy; dz = r.dz; tmin = mint; tmax = maxt;
@@ -147,7 +167,21 @@ template <class Stack> struct Traversal {
         const uint32_t nearx[2] = {nx ? hix0 : lox0, nx ? hix1 : lox1}, farx[2] = {nx ? lox0 : hix0, nx ? lox1 : hix1};
         const uint32_t neary[2] = {ny ? hiy0 : loy0, ny ? hiy1 : loy1}, fary[2] = {ny ? loy0 : hiy0, ny ? loy1 : hiy1};
         const uint32_t nearz[2] = {nz ? hiz0 : loz0, nz ? hiz1 : loz1}, farz[2] = {nz ? loz0 : hiz0, nz ? loz1 : hiz1};
-        const uint32_t meta[2] = {n1.z, n1.w};
+        // per-child bit position / bit pattern, four children per 32-bit word:
+        //   inner child (meta = 001sssss, s >= 24): one bit at 24 + (slot ^ octinv)
+        //   leaf  child (meta = uuuooooo)         : bits uuu at offset ooooo
+        const uint32_t octinv4 = octinv * 0x01010101u;
+        uint32_t bit_index4[2], child_bits4[2];
+#if MTSB_DEVICE_CODE
+#pragma unroll
+#endif
+        for (int h = 0; h < 2; ++h) {
+            const uint32_t meta4 = h == 0 ? n1.z : n1.w;
+            const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+            const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;          // 0xff in the bytes of inner children
+            bit_index4[h] = (meta4 ^ (octinv4 & inner_mask4)) & 0x1f1f1f1fu;
+            child_bits4[h] = (meta4 >> 5) & 0x07070707u;
+        }
         uint32_t hitmask = 0;
 #if MTSB_DEVICE_CODE
 #pragma unroll
@@ -158,7 +192,6 @@ template <class Stack> struct Traversal {
 #endif
             for (int j = 0; j < 4; ++j) {
                 const int sh = 8 * j;
-                const uint32_t m = (meta[h] >> sh) & 0xffu;
                 const float tnx = (float) ((nearx[h] >> sh) & 0xffu) * sdx + ax;
                 const float tny = (float) ((neary[h] >> sh) & 0xffu) * sdy + ay;
                 const float tnz = (float) ((nearz[h] >> sh) & 0xffu) * sdz + az;
@@ -167,11 +200,8 @@ template <class Stack> struct Traversal {
                 const float tfz = (float) ((farz[h] >> sh) & 0xffu) * sdz + az;
                 const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
                 const float cmax = fminf(fminf(tfx, tfy), fminf(tfz, tmax));
-                if (cmin <= cmax) {
-                    const uint32_t is_inner = (m & (m << 1)) & 0x10u;
-                    const uint32_t bit_index = (m ^ (is_inner ? octinv : 0u)) & 0x1fu;
-                    hitmask |= ((m >> 5) & 7u) << bit_index;
-                }
+                const uint32_t bits = ((child_bits4[h] >> sh) & 0xffu) << ((bit_index4[h] >> sh) & 0xffu);
+                hitmask |= (cmin <= cmax) ? bits : 0u;
             }
         }
         ng_x = n1.x;
@@ -184,6 +214,9 @@ template <class Stack> struct Traversal {
     template <bool ANY> MTSB_HD bool test_triangle(const U4 *tris) {
         const int i = bfind(tg);
         tg &= ~(1u << i);
+#if !MTSB_DEVICE_CODE
+        ++tri_tests;
+#endif
         const U4 *tp = tris + 3 * ((size_t) tri_base + (size_t) i);
         const U4 q0 = ld16(tp), q1 = ld16(tp + 1), q2 = ld16(tp + 2);
         float u, v, t;

@@ -92,6 +92,8 @@ extern "C" void emu_info(void *h, uint32_t *n_nodes, float *tight6, float *enlar
     for (int k = 0; k < 3; ++k) { tight6[k] = s->tight_lo[k]; tight6[3 + k] = s->tight_hi[k]; enlarged6[k] = s->box_lo[k]; enlarged6[3 + k] = s->box_hi[k]; }
 }
 
+static uint64_t g_tri_tests = 0;
+extern "C" uint64_t emu_tri_tests(void) { uint64_t v = g_tri_tests; g_tri_tests = 0; return v; }
 // returns the total number of node visits (traversal statistics)
 extern "C" uint64_t emu_trace(void *h, const RayIn *rays, size_t n, int mode, HitOut *hits) {
     EmuScene *s = static_cast<EmuScene *>(h);
@@ -105,7 +107,7 @@ extern "C" uint64_t emu_trace(void *h, const RayIn *rays, size_t n, int mode, Hi
             tr.begin(rays[i], mint, maxt);
             if (mode == 1) { while (!tr.step<true>(nodes, tris)) {} }
             else { while (!tr.step<false>(nodes, tris)) {} }
-            out = tr.hit; steps += tr.steps;
+            out = tr.hit; steps += tr.steps; g_tri_tests += tr.tri_tests;
         }
         hits[i] = out;
     }
