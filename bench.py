@@ -162,13 +162,6 @@ def run_reference_arm(args):
     print(json.dumps(out), flush=True)
 
 
-class _DevPtr:
-    """Zero-copy torch view of a device pointer owned by the library (the film)."""
-
-    def __init__(self, ptr, n):
-        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (ptr, False), "version": 2}
-
-
 def host_bytes(builder):
     pos, nrm, uv, idx = builder.arrays()
     return int(pos.nbytes + nrm.nbytes + uv.nbytes + idx.nbytes)
@@ -178,6 +171,7 @@ def run_b200_arm(args):
     import torch
     import torch.distributed as dist
     from mitsuba_b200 import lib
+    from mitsuba_b200 import dist as mdist
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -194,8 +188,7 @@ def run_b200_arm(args):
     total_spp = spp * world                     # weak scaling: N x spp of the same image, tiles interleaved over ranks
     scene = lib.Scene(builder)
     info = scene.info()
-    film_ptr, film_n = scene.film_device_ptr()
-    film_t = torch.as_tensor(_DevPtr(film_ptr, film_n), device="cuda") if world > 1 else None
+    film_t = mdist.film_tensor(scene) if world > 1 else None
     flush = torch.empty(160 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
 
     def barrier():
@@ -211,7 +204,7 @@ def run_b200_arm(args):
         if world > 1:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-            dist.reduce(film_t, dst=0, op=dist.ReduceOp.SUM)
+            mdist.reduce_film(film_t, dst=0)
             e1.record()
             torch.cuda.synchronize()
             ms += e0.elapsed_time(e1)
@@ -254,8 +247,8 @@ def run_b200_arm(args):
         sc = lib.Scene(builder)                                     # H2D of the scene arrays + BVH build
         st = sc.render(spp=total_spp, seed=300 + i, tile_index=rank, tile_count=world)
         if world > 1:
-            p, n = sc.film_device_ptr()
-            dist.reduce(torch.as_tensor(_DevPtr(p, n), device="cuda"), dst=0, op=dist.ReduceOp.SUM)
+            mdist.reduce_film(mdist.film_tensor(sc), dst=0)
+            torch.cuda.synchronize()
         if rank == 0:
             img = sc.film_develop()                                 # D2H of the developed image
             d2h = int(img.nbytes)

@@ -132,3 +132,95 @@ extern "C" void emu_philox(const uint32_t *ctr4, const uint32_t *key2, uint32_t 
 extern "C" void emu_sample_block(uint64_t seed, uint64_t sample_id, uint32_t block, uint32_t sub, float *out4) {
     SampleStream(seed, sample_id).block4(block, sub, out4);
 }
+
+// ---- experiment support: the same wide collapse fed by a top-down binned-SAH binary tree ----
+// (measures how much of the node-visit count is due to the Morton-order builder)
+namespace {
+struct SahBuilder {
+    const float *lo, *hi; std::vector<uint32_t> &order; std::vector<uint32_t> &left, &right, &first, &last; uint32_t n; uint32_t next_internal = 0;
+    SahBuilder(const float *l, const float *h, std::vector<uint32_t> &o, std::vector<uint32_t> &L, std::vector<uint32_t> &R, std::vector<uint32_t> &F, std::vector<uint32_t> &La, uint32_t nn)
+        : lo(l), hi(h), order(o), left(L), right(R), first(F), last(La), n(nn) {}
+    float cen(uint32_t p, int ax) const { return 0.5f * (lo[3 * (size_t) p + ax] + hi[3 * (size_t) p + ax]); }
+    static float area(const float *a, const float *b) { float x = b[0] - a[0], y = b[1] - a[1], z = b[2] - a[2]; return x * y + y * z + z * x; }
+    // returns unified node id of the subtree over order[b, e)
+    uint32_t build(uint32_t b, uint32_t e) {
+        if (e - b == 1) return n - 1 + b;
+        uint32_t id = next_internal++;
+        float clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (uint32_t i = b; i < e; ++i) for (int k = 0; k < 3; ++k) { float c = cen(order[i], k); clo[k] = std::min(clo[k], c); chi[k] = std::max(chi[k], c); }
+        const int NB = 32; int bestAx = -1, bestSplit = -1; float bestCost = INFINITY;
+        for (int ax = 0; ax < 3; ++ax) {
+            if (!(chi[ax] > clo[ax])) continue;
+            float blo[NB][3], bhi[NB][3]; uint32_t cnt[NB];
+            for (int q = 0; q < NB; ++q) { cnt[q] = 0; for (int k = 0; k < 3; ++k) { blo[q][k] = INFINITY; bhi[q][k] = -INFINITY; } }
+            float sc = NB / (chi[ax] - clo[ax]);
+            for (uint32_t i = b; i < e; ++i) {
+                uint32_t p = order[i]; int q = std::min(NB - 1, (int) ((cen(p, ax) - clo[ax]) * sc));
+                cnt[q]++; for (int k = 0; k < 3; ++k) { blo[q][k] = std::min(blo[q][k], lo[3 * (size_t) p + k]); bhi[q][k] = std::max(bhi[q][k], hi[3 * (size_t) p + k]); }
+            }
+            float ra[NB]; uint32_t rc[NB]; float alo[3] = {INFINITY, INFINITY, INFINITY}, ahi[3] = {-INFINITY, -INFINITY, -INFINITY}; uint32_t c = 0;
+            for (int q = NB - 1; q > 0; --q) { c += cnt[q]; for (int k = 0; k < 3; ++k) { alo[k] = std::min(alo[k], blo[q][k]); ahi[k] = std::max(ahi[k], bhi[q][k]); } ra[q] = c ? area(alo, ahi) : 0; rc[q] = c; }
+            for (int k = 0; k < 3; ++k) { alo[k] = INFINITY; ahi[k] = -INFINITY; } c = 0;
+            for (int q = 0; q < NB - 1; ++q) {
+                c += cnt[q]; for (int k = 0; k < 3; ++k) { alo[k] = std::min(alo[k], blo[q][k]); ahi[k] = std::max(ahi[k], bhi[q][k]); }
+                if (!c || !rc[q + 1]) continue;
+                float cost = area(alo, ahi) * c + ra[q + 1] * rc[q + 1];
+                if (cost < bestCost) { bestCost = cost; bestAx = ax; bestSplit = q; }
+            }
+        }
+        uint32_t mid;
+        if (bestAx < 0) mid = b + (e - b) / 2;
+        else {
+            float sc = NB / (chi[bestAx] - clo[bestAx]); float c0 = clo[bestAx]; int ax = bestAx, sp = bestSplit;
+            auto it = std::partition(order.begin() + b, order.begin() + e, [&](uint32_t p) { return std::min(NB - 1, (int) ((cen(p, ax) - c0) * sc)) <= sp; });
+            mid = (uint32_t) (it - order.begin());
+            if (mid == b || mid == e) mid = b + (e - b) / 2;
+        }
+        first[id] = b; last[id] = e - 1;
+        uint32_t l = build(b, mid), r = build(mid, e);
+        left[id] = l; right[id] = r;
+        return id;
+    }
+};
+}
+
+extern "C" void *emu_build_sah(const float *positions, const uint32_t *indices, uint32_t n) {
+    EmuScene *s = new EmuScene();
+    s->n_tris = n;
+    std::vector<TriRec> tri_tmp(n);
+    std::vector<float> prim_lo(3 * (size_t) n), prim_hi(3 * (size_t) n);
+    float tlo[3] = {INFINITY, INFINITY, INFINITY}, thi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (uint32_t i = 0; i < n; ++i) {
+        tri_setup(i, positions, indices, &tri_tmp[i], &prim_lo[3 * (size_t) i], &prim_hi[3 * (size_t) i]);
+        for (int k = 0; k < 3; ++k) { tlo[k] = std::min(tlo[k], prim_lo[3 * (size_t) i + k]); thi[k] = std::max(thi[k], prim_hi[3 * (size_t) i + k]); }
+    }
+    for (int k = 0; k < 3; ++k) {
+        volatile float lo = tlo[k] - ((thi[k] - tlo[k]) * 1e-3f + 1e-3f);
+        volatile float hi = thi[k] + ((thi[k] - lo) * 1e-3f + 1e-3f);
+        s->box_lo[k] = lo; s->box_hi[k] = hi; s->tight_lo[k] = tlo[k]; s->tight_hi[k] = thi[k];
+    }
+    float diag = std::sqrt((thi[0] - tlo[0]) * (thi[0] - tlo[0]) + (thi[1] - tlo[1]) * (thi[1] - tlo[1]) + (thi[2] - tlo[2]) * (thi[2] - tlo[2]));
+    float amax = 0; for (int k = 0; k < 3; ++k) amax = std::max(amax, std::max(std::fabs(tlo[k]), std::fabs(thi[k])));
+    std::vector<uint32_t> vals(n); std::iota(vals.begin(), vals.end(), 0u);
+    std::vector<uint32_t> left(n), right(n), first(n), last(n), parent(2 * (size_t) n, 0), flags(n, 0), wbin(n, 0);
+    SahBuilder sb(prim_lo.data(), prim_hi.data(), vals, left, right, first, last, n);
+    uint32_t root = sb.build(0, n);
+    (void) root;   // == 0 (pre-order numbering)
+    for (uint32_t i = 0; i + 1 < n; ++i) { parent[left[i]] = i; parent[right[i]] = i; }
+    parent[0] = 0xFFFFFFFFu;
+    std::vector<float> node_lo(6 * (size_t) n), node_hi(6 * (size_t) n);
+    for (int j = 0; j < (int) n; ++j)
+        fit_from_leaf(j, (int) n, vals.data(), prim_lo.data(), prim_hi.data(), left.data(), right.data(), parent.data(), node_lo.data(), node_hi.data(), flags.data());
+    std::vector<Node8> nodes(n); std::vector<TriRec> tri_out(n);
+    uint32_t counters[2] = {1, 0};
+    WideBuildArgs a;
+    a.n = (int) n; a.left = left.data(); a.right = right.data(); a.first = first.data(); a.last = last.data();
+    a.node_lo = node_lo.data(); a.node_hi = node_hi.data(); a.sorted_prim = vals.data(); a.tri_in = tri_tmp.data();
+    a.nodes = nodes.data(); a.wbin = wbin.data(); a.tri_out = tri_out.data(); a.counters = counters;
+    a.leaf_pad = 4e-6f * std::max(diag, amax) + 1e-30f;
+    uint32_t begin = 0, end = 1;
+    while (begin < end) { for (uint32_t w = begin; w < end; ++w) wide_node_build(w, a, false); begin = end; end = counters[0]; }
+    nodes.resize(end);
+    s->nodes.swap(nodes); s->tris.swap(tri_out);
+    return s;
+}
