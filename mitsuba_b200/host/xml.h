@@ -3,6 +3,9 @@
 // prolog, comments, elements with quoted attributes, self-closing tags, character entities.
 // Text content is ignored (scene files carry all data in attributes).
 #pragma once
+#include <cctype>
+#include <cstdlib>
+#include <cstring>
 #include <map>
 #include <memory>
 #include <stdexcept>

@@ -53,3 +53,32 @@ def test_product_never_imports_oracle():
                 txt = open(os.path.join(dp, f), errors="replace").read()
                 assert not re.search(r"^\s*(import|from)\s+oracle\b", txt, flags=re.M), f
                 assert "liboracle" not in txt and "libmtsref" not in txt and "orc_" not in txt, f
+
+
+def test_host_library_header_and_exports():
+    """include/mtsb200_host.h <-> libmtsb200host.so (the C++ scene loader / plugin mirror)."""
+    from mitsuba_b200 import hostlib
+    src = open(os.path.join(ROOT, "include", "mtsb200_host.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    declared = sorted(set(re.findall(r"\b(mtsbh_[a-z_0-9]+)\s*\(", src)))
+    assert declared == sorted(hostlib.SYMBOLS)
+    assert os.path.exists(hostlib.LIB_PATH), "build the host library first (__graft_entry__.build())"
+    L = C.CDLL(hostlib.LIB_PATH)
+    for s in hostlib.SYMBOLS:
+        assert hasattr(L, s), s
+
+
+def test_host_render_refuses_without_gpu():
+    """The render job goes through libmtsb200.so: without a device it must fail, not fall back."""
+    import numpy as np
+    from mitsuba_b200 import hostlib
+    try:
+        import torch
+        if torch.cuda.is_available():
+            pytest.skip("GPU present")
+    except ImportError:
+        pass
+    hs = hostlib.HostScene.load_file(os.path.join(ROOT, "scenes", "cbox.xml"), {"res": 16, "spp": 1})
+    with pytest.raises(lib.MtsbError) as ei:
+        hs.render()
+    assert ei.value.code == abi.ERR_NO_DEVICE
