@@ -239,12 +239,13 @@ def run_b200_arm(args):
 
     # ---- end to end through the C ABI with host buffers (scene in host memory -> image in host memory) ----
     scene.close()
+    desc_pair = builder.desc()          # the scene description as contiguous HOST buffers (the input of the C ABI)
     barrier()
     e2e_t0 = time.time()
     e2e_samples = 0.0
     d2h = 0
     for i in range(args.steps):
-        sc = lib.Scene(builder)                                     # H2D of the scene arrays + BVH build
+        sc = lib.Scene(desc_pair)                                   # H2D of the scene arrays + BVH build
         st = sc.render(spp=total_spp, seed=300 + i, tile_index=rank, tile_count=world)
         if world > 1:
             mdist.reduce_film(mdist.film_tensor(sc), dst=0)

@@ -27,6 +27,8 @@
 #include <cooperative_groups.h>
 #include <cstring>
 #include <algorithm>
+#include <map>
+#include <mutex>
 
 namespace cg = cooperative_groups;
 
@@ -425,9 +427,8 @@ __global__ void __launch_bounds__(256) k_splat(SceneView sc, PathBuffers pb, Pas
 }
 
 // ---- host side ---------------------------------------------------------------------------
-int render_free(Scene *s) {
-    PathBuffers *pb = s->paths;
-    if (!pb) return MTSB_OK;
+static void free_buffers(PathBuffers *pb) {
+    if (!pb) return;
     for (int i = 0; i < 2; ++i) { cudaFree(pb->rays[i]); cudaFree(pb->ray_slot[i]); }
     cudaFree(pb->hits); cudaFree(pb->srays); cudaFree(pb->scontrib); cudaFree(pb->thr_eta); cudaFree(pb->L_bpdf);
     cudaFree(pb->refn_flags); cudaFree(pb->spos);
@@ -435,16 +436,56 @@ int render_free(Scene *s) {
     cudaFree(pb->ctr); cudaFree(pb->tiles);
     if (pb->h_ctr) cudaFreeHost(pb->h_ctr);
     delete pb;
-    s->paths = nullptr;
+}
+
+// Path buffers are large (about 216 B per slot) and their size does not depend on the scene, so a
+// destroyed scene parks them in a per-device pool and the next scene's first render picks them up
+// instead of paying cudaMalloc / cudaFree of several GB again.  The pool keeps at most
+// MTSB_MAX_LANES sets per device for the life of the process.
+static std::mutex g_pool_mutex;
+static std::map<int, std::vector<PathBuffers *>> g_pool;
+
+int render_free(Scene *s) {
+    std::lock_guard<std::mutex> g(g_pool_mutex);
+    std::vector<PathBuffers *> &pool = g_pool[s->device];
+    for (int l = 0; l < MTSB_MAX_LANES; ++l) {
+        if (s->paths[l]) {
+            if (pool.size() < MTSB_MAX_LANES) pool.push_back(s->paths[l]);
+            else free_buffers(s->paths[l]);
+        }
+        s->paths[l] = nullptr;
+        if (s->lane_stream[l]) { cudaStreamDestroy(s->lane_stream[l]); s->lane_stream[l] = nullptr; }
+    }
     return MTSB_OK;
 }
 
-static int ensure_buffers(Scene *s, uint32_t capacity, uint32_t n_tiles) {
-    if (s->paths && s->paths->capacity >= capacity && s->paths->tiles_capacity >= n_tiles) return MTSB_OK;
-    render_free(s);
+static int ensure_buffers(Scene *s, int lane, uint32_t capacity, uint32_t n_tiles) {
+    if (!s->lane_stream[lane]) MTSB_CUDA(cudaStreamCreateWithFlags(&s->lane_stream[lane], cudaStreamNonBlocking));
+    if (s->paths[lane] && s->paths[lane]->capacity >= capacity && s->paths[lane]->tiles_capacity >= n_tiles) return MTSB_OK;
+    {
+        std::lock_guard<std::mutex> g(g_pool_mutex);
+        std::vector<PathBuffers *> &pool = g_pool[s->device];
+        if (s->paths[lane]) { free_buffers(s->paths[lane]); s->paths[lane] = nullptr; }
+        for (size_t i = 0; i < pool.size(); ++i)
+            if (pool[i]->capacity >= capacity && pool[i]->capacity <= 2 * (size_t) capacity) {
+                s->paths[lane] = pool[i];
+                pool.erase(pool.begin() + (long) i);
+                break;
+            }
+        if (!s->paths[lane]) { for (PathBuffers *p : pool) free_buffers(p); pool.clear(); }    // make room before a new allocation
+    }
+    if (s->paths[lane]) {
+        PathBuffers *pb = s->paths[lane];
+        if (pb->tiles_capacity < n_tiles) {
+            cudaFree(pb->tiles); pb->tiles = nullptr;
+            MTSB_CUDA(cudaMalloc((void **) &pb->tiles, (size_t) std::max(1u, n_tiles) * sizeof(int)));
+            pb->tiles_capacity = n_tiles;
+        }
+        return MTSB_OK;
+    }
     PathBuffers *pb = new PathBuffers();
     memset(pb, 0, sizeof(*pb));
-    s->paths = pb;
+    s->paths[lane] = pb;
     pb->capacity = capacity; pb->tiles_capacity = n_tiles;
     const size_t c = capacity;
     for (int i = 0; i < 2; ++i) { MTSB_CUDA(cudaMalloc((void **) &pb->rays[i], c * sizeof(RayIn))); MTSB_CUDA(cudaMalloc((void **) &pb->ray_slot[i], c * 4)); }
@@ -463,15 +504,20 @@ static int ensure_buffers(Scene *s, uint32_t capacity, uint32_t n_tiles) {
 }
 
 struct StageTimer {
-    struct Span { cudaEvent_t a, b; int stage; };
+    struct Span { cudaEvent_t a, b; int stage; uint32_t n; };
     std::vector<Span> spans; std::vector<cudaEvent_t> pool; size_t next = 0; cudaStream_t st;
     explicit StageTimer(cudaStream_t s) : st(s) {}
     cudaEvent_t get() { if (next == pool.size()) { cudaEvent_t e; cudaEventCreate(&e); pool.push_back(e); } return pool[next++]; }
-    void begin(int stage) { Span sp; sp.a = get(); sp.b = nullptr; sp.stage = stage; cudaEventRecord(sp.a, st); spans.push_back(sp); }
+    void begin(int stage, uint32_t n = 0) { Span sp; sp.a = get(); sp.b = nullptr; sp.stage = stage; sp.n = n; cudaEventRecord(sp.a, st); spans.push_back(sp); }
     void end() { Span &sp = spans.back(); sp.b = get(); cudaEventRecord(sp.b, st); }
     void collect(float *out, int n_stage) {
-        for (int i = 0; i < n_stage; ++i) out[i] = 0;
         for (auto &sp : spans) { float ms = 0; if (sp.b && cudaEventElapsedTime(&ms, sp.a, sp.b) == cudaSuccess) out[sp.stage] += ms; }
+        (void) n_stage;
+        if (getenv("MTSB_PROFILE")) {       // per-launch-group times of the first passes (diagnostics)
+            static const char *names[] = {"raygen", "closest", "shade", "any", "splat"};
+            size_t k = 0;
+            for (auto &sp : spans) { float ms = 0; if (sp.b) cudaEventElapsedTime(&ms, sp.a, sp.b); if (k++ < 60) fprintf(stderr, "[mtsb] %-8s n<=%9u %8.3f ms\n", names[sp.stage], sp.n, ms); }
+        }
     }
     ~StageTimer() { for (auto e : pool) cudaEventDestroy(e); }
 };
@@ -481,6 +527,77 @@ static int shade_grid(size_t n_upper, int sm_count) {
     size_t need = (n_upper + MTSB_SHADE_BLOCK - 1) / MTSB_SHADE_BLOCK;
     size_t cap = (size_t) sm_count * 16;
     return (int) std::max<size_t>(1, std::min(need, cap));
+}
+
+// One pass = a block of tiles x a block of samples, small enough for the path buffers of a lane.
+struct Pass { PassInfo ps; uint32_t n_slots; };
+
+// A lane is an independent wavefront pipeline (own stream, own path buffers).  Passes are handed to
+// lanes as they become free, so the thin late bounces of one pass -- launches with few rays that
+// cannot fill 148 SMs -- and the host round trip that reads the queue sizes overlap with the wide
+// early bounces of another pass.  The film is shared: k_splat adds with atomics.
+struct Lane {
+    cudaStream_t st = nullptr;
+    PathBuffers *pb = nullptr;
+    StageTimer *timer = nullptr;
+    cudaEvent_t ev = nullptr;      // queue sizes of the bounce in flight are on the host
+    bool busy = false;
+    Pass pass{};
+    uint32_t n_cur = 0;
+    int cur = 0;
+};
+
+static int lane_bounce(Scene *s, Lane &L, const RenderConst &rcst, int sm_count) {
+    PathBuffers &pb = *L.pb;
+    const SceneView &v = s->v;
+    L.timer->begin(ST_CLOSEST, L.n_cur);
+    int rc = launch_trace_kernel<false>(s, pb.rays[L.cur], &pb.ctr->n_rays[L.cur], L.n_cur, StoreHit{pb.hits}, L.st);
+    L.timer->end();
+    if (rc) return rc;
+    L.timer->begin(ST_SHADE, L.n_cur);
+    const int g = shade_grid(L.n_cur, sm_count);
+    k_bounce_prepare<<<1, 1, 0, L.st>>>(pb, L.cur);
+    k_sort<<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.cur);
+    k_shade<Q_DIFFUSE><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur);
+    k_shade<Q_CONDUCTOR><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur);
+    k_shade<Q_DIELECTRIC><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur);
+    k_shade<Q_NULL><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur);
+    k_shade<Q_GENERIC><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur);
+    k_miss<<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, rcst, L.cur);
+    s->launches += 8;
+    L.timer->end();
+    L.timer->begin(ST_ANY, L.n_cur);
+    rc = launch_trace_kernel<true>(s, pb.srays, &pb.ctr->n_shadow, L.n_cur, ShadowResolve{pb.scontrib, pb.L_bpdf}, L.st);
+    L.timer->end();
+    if (rc) return rc;
+    MTSB_CUDA(cudaMemcpyAsync(pb.h_ctr, pb.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, L.st));
+    MTSB_CUDA(cudaEventRecord(L.ev, L.st));
+    return MTSB_OK;
+}
+
+static int lane_start(Scene *s, Lane &L, const Pass &p, const RenderConst &rcst, int sm_count) {
+    L.pass = p; L.busy = true; L.cur = 0; L.n_cur = p.n_slots;      // upper bound for the first bounce
+    L.timer->begin(ST_RAYGEN);
+    k_pass_begin<<<1, 1, 0, L.st>>>(*L.pb);
+    k_raygen<<<shade_grid(p.n_slots, sm_count), MTSB_SHADE_BLOCK, 0, L.st>>>(s->v, *L.pb, p.ps, p.n_slots);
+    s->launches += 2;
+    L.timer->end();
+    return lane_bounce(s, L, rcst, sm_count);
+}
+
+static void lane_finish(Scene *s, Lane &L, size_t splat_smem) {
+    L.timer->begin(ST_SPLAT);
+    k_pass_end<<<1, 1, 0, L.st>>>(*L.pb);
+    k_splat<<<L.pass.ps.n_tiles, 256, splat_smem, L.st>>>(s->v, *L.pb, L.pass.ps, s->d_film_bad);
+    s->launches += 2;
+    L.timer->end();
+    L.busy = false;
+}
+
+static int lane_count() {
+    const char *e = getenv("MTSB_LANES");
+    int n = e ? atoi(e) : 1;
+    return std::max(1, std::min(n, MTSB_MAX_LANES));
 }
 
 }  // namespace mtsb
@@ -512,94 +629,114 @@ extern "C" int mtsb_render(mtsb_scene_t scene, const MtsbRenderParams *params, M
     if (stats) memset(stats, 0, sizeof(*stats));
     if (tiles.empty()) { MTSB_CUDA(cudaStreamSynchronize(s->stream)); return MTSB_OK; }
 
-    // pass shape: about 16M path slots in flight
-    const uint64_t target = 16ull << 20;
+    // pass shape: about 16M path slots in flight over all lanes
     const uint64_t px_per_tile = MTSB_TILE * MTSB_TILE;
+    const uint64_t total_slots = (uint64_t) tiles.size() * px_per_tile * (uint64_t) spp;
+    int n_lanes = lane_count();
+    if (total_slots <= (2ull << 20)) n_lanes = 1;                       // small jobs: one pass, nothing to overlap
+    // path slots in flight over all lanes: as many as fit in a fifth of the free device memory, at most 64M
+    // (a pass pays a fixed price for its thin late bounces, so fewer and larger passes are faster)
+    uint64_t slots_m = 64;
+    {
+        size_t free_b = 0, total_b = 0;
+        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
+            uint64_t have = 0;
+            for (int l = 0; l < MTSB_MAX_LANES; ++l) if (s->paths[l]) have += (uint64_t) s->paths[l]->capacity * 216ull;
+            const uint64_t fit = ((uint64_t) free_b + have) / 5ull / 216ull >> 20;
+            slots_m = std::max<uint64_t>(1, std::min<uint64_t>(slots_m, fit));
+        }
+        const char *tenv = getenv("MTSB_SLOTS_M");
+        if (tenv && atoi(tenv) > 0) slots_m = (uint64_t) atoi(tenv);
+    }
+    const uint64_t target = (slots_m << 20) / (uint64_t) n_lanes;
     uint32_t spp_pass = params->spp_per_pass > 0 ? (uint32_t) params->spp_per_pass
                                                  : (uint32_t) std::max<uint64_t>(1, std::min<uint64_t>((uint64_t) spp, target / (tiles.size() * px_per_tile)));
     spp_pass = std::min<uint32_t>(spp_pass, (uint32_t) spp);
     uint32_t tiles_per_pass = (uint32_t) std::max<uint64_t>(1, std::min<uint64_t>(tiles.size(), target / (px_per_tile * spp_pass)));
     const uint32_t capacity = (uint32_t) (tiles_per_pass * px_per_tile * spp_pass);
-    int rc = ensure_buffers(s, capacity, (uint32_t) tiles.size());
-    if (rc) return rc;
-    PathBuffers &pb = *s->paths;
-    MTSB_CUDA(cudaMemcpyAsync(pb.tiles, tiles.data(), tiles.size() * sizeof(int), cudaMemcpyHostToDevice, s->stream));
-    MTSB_CUDA(cudaMemsetAsync(pb.ctr, 0, sizeof(Counters), s->stream));
+    std::vector<Pass> passes;
+    for (uint32_t t0 = 0; t0 < tiles.size(); t0 += tiles_per_pass)
+        for (uint32_t s0 = 0; s0 < (uint32_t) spp; s0 += spp_pass) {
+            Pass p;
+            p.ps.tile_first = t0; p.ps.n_tiles = std::min<uint32_t>(tiles_per_pass, (uint32_t) tiles.size() - t0);
+            p.ps.spp_pass = std::min<uint32_t>(spp_pass, (uint32_t) spp - s0);
+            p.ps.s_first = (uint32_t) params->spp_offset + s0; p.ps.tiles_x = tiles_x; p.ps.seed = params->seed;
+            p.n_slots = (uint32_t) (p.ps.n_tiles * px_per_tile * p.ps.spp_pass);
+            passes.push_back(p);
+        }
+    n_lanes = std::min<int>(n_lanes, (int) passes.size());
 
     RenderConst rcst; rcst.max_depth = v.integrator.max_depth; rcst.rr_depth = v.integrator.rr_depth;
     rcst.strict_normals = v.integrator.strict_normals; rcst.hide_emitters = v.integrator.hide_emitters;
-    StageTimer timer(s->stream);
-    cudaEvent_t ev0, ev1; cudaEventCreate(&ev0); cudaEventCreate(&ev1);
-    cudaEventRecord(ev0, s->stream);
     const size_t splat_smem = (size_t) MTSB_SPLAT_CHUNK * MTSB_TILE * MTSB_TILE * (sizeof(float4) + sizeof(float2));
     MTSB_CUDA(cudaFuncSetAttribute(k_splat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) splat_smem));
-    uint32_t n_passes = 0;
-    uint64_t samples = 0;
-    int status = MTSB_OK;
-    ShadowResolve resolve{pb.scontrib, pb.L_bpdf};
 
-    for (uint32_t t0 = 0; t0 < tiles.size() && status == MTSB_OK; t0 += tiles_per_pass) {
-        const uint32_t nt = std::min<uint32_t>(tiles_per_pass, (uint32_t) tiles.size() - t0);
-        for (uint32_t s0 = 0; s0 < (uint32_t) spp && status == MTSB_OK; s0 += spp_pass) {
-            PassInfo ps; ps.tile_first = t0; ps.n_tiles = nt; ps.spp_pass = std::min<uint32_t>(spp_pass, (uint32_t) spp - s0);
-            ps.s_first = (uint32_t) params->spp_offset + s0; ps.tiles_x = tiles_x; ps.seed = params->seed;
-            const uint32_t n_slots = (uint32_t) (nt * px_per_tile * ps.spp_pass);
-            ++n_passes;
-            timer.begin(ST_RAYGEN);
-            k_pass_begin<<<1, 1, 0, s->stream>>>(pb);
-            k_raygen<<<shade_grid(n_slots, sm_count), MTSB_SHADE_BLOCK, 0, s->stream>>>(v, pb, ps, n_slots);
-            s->launches += 2;
-            timer.end();
-            uint32_t n_cur = n_slots;     // upper bound for the first bounce
-            int cur = 0;
-            for (int bounce = 0;; ++bounce) {
-                timer.begin(ST_CLOSEST);
-                rc = launch_trace_kernel<false>(s, pb.rays[cur], &pb.ctr->n_rays[cur], n_cur, StoreHit{pb.hits}, s->stream);
-                timer.end();
-                if (rc) { status = rc; break; }
-                timer.begin(ST_SHADE);
-                const int g = shade_grid(n_cur, sm_count);
-                k_bounce_prepare<<<1, 1, 0, s->stream>>>(pb, cur);
-                k_sort<<<g, MTSB_SHADE_BLOCK, 0, s->stream>>>(v, pb, cur);
-                k_shade<Q_DIFFUSE><<<g, MTSB_SHADE_BLOCK, 0, s->stream>>>(v, pb, ps, rcst, cur);
-                k_shade<Q_CONDUCTOR><<<g, MTSB_SHADE_BLOCK, 0, s->stream>>>(v, pb, ps, rcst, cur);
-                k_shade<Q_DIELECTRIC><<<g, MTSB_SHADE_BLOCK, 0, s->stream>>>(v, pb, ps, rcst, cur);
-                k_shade<Q_NULL><<<g, MTSB_SHADE_BLOCK, 0, s->stream>>>(v, pb, ps, rcst, cur);
-                k_shade<Q_GENERIC><<<g, MTSB_SHADE_BLOCK, 0, s->stream>>>(v, pb, ps, rcst, cur);
-                k_miss<<<g, MTSB_SHADE_BLOCK, 0, s->stream>>>(v, pb, rcst, cur);
-                s->launches += 8;
-                timer.end();
-                timer.begin(ST_ANY);
-                rc = launch_trace_kernel<true>(s, pb.srays, &pb.ctr->n_shadow, n_cur, resolve, s->stream);
-                timer.end();
-                if (rc) { status = rc; break; }
-                cudaError_t e = cudaMemcpyAsync(pb.h_ctr, pb.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, s->stream);
-                if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
-                if (e != cudaSuccess) { status = cuda_fail(e, "wavefront bounce", __FILE__, __LINE__); break; }
-                if (s->cancel.load()) { status = MTSB_ERR_CANCELLED; set_error("render cancelled"); break; }
-                n_cur = pb.h_ctr->n_rays[1 - cur];
-                cur ^= 1;
-                if (n_cur == 0) break;
+    cudaEvent_t ev0, ev1; cudaEventCreate(&ev0); cudaEventCreate(&ev1);
+    cudaEventRecord(ev0, s->stream);
+    std::vector<Lane> lanes((size_t) n_lanes);
+    int status = MTSB_OK;
+    for (int l = 0; l < n_lanes && status == MTSB_OK; ++l) {
+        Lane &L = lanes[(size_t) l];
+        status = ensure_buffers(s, l, capacity, (uint32_t) tiles.size());
+        if (status) break;
+        L.st = s->lane_stream[l]; L.pb = s->paths[l];
+        L.timer = new StageTimer(L.st);
+        cudaEventCreateWithFlags(&L.ev, cudaEventDisableTiming);
+        cudaStreamWaitEvent(L.st, ev0, 0);                               // after the film clear
+        cudaMemcpyAsync(L.pb->tiles, tiles.data(), tiles.size() * sizeof(int), cudaMemcpyHostToDevice, L.st);
+        cudaMemsetAsync(L.pb->ctr, 0, sizeof(Counters), L.st);
+    }
+
+    size_t next_pass = 0;
+    uint32_t n_passes = 0;
+    while (status == MTSB_OK) {
+        bool any_busy = false, progressed = false;
+        for (Lane &L : lanes) {
+            if (!L.busy) {
+                if (next_pass < passes.size()) {
+                    status = lane_start(s, L, passes[next_pass++], rcst, sm_count);
+                    ++n_passes; progressed = true; any_busy = true;
+                    if (status) break;
+                }
+                continue;
             }
-            if (status != MTSB_OK) break;
-            timer.begin(ST_SPLAT);
-            k_pass_end<<<1, 1, 0, s->stream>>>(pb);
-            k_splat<<<nt, 256, splat_smem, s->stream>>>(v, pb, ps, s->d_film_bad);
-            s->launches += 2;
-            timer.end();
-            samples += (uint64_t) n_slots;
+            any_busy = true;
+            cudaError_t q = cudaEventQuery(L.ev);
+            if (q == cudaErrorNotReady) continue;
+            if (q != cudaSuccess) { status = cuda_fail(q, "wavefront bounce", __FILE__, __LINE__); break; }
+            progressed = true;
+            if (s->cancel.load()) { status = MTSB_ERR_CANCELLED; set_error("render cancelled"); break; }
+            L.n_cur = L.pb->h_ctr->n_rays[1 - L.cur];
+            L.cur ^= 1;
+            if (L.n_cur == 0) lane_finish(s, L, splat_smem);
+            else status = lane_bounce(s, L, rcst, sm_count);
+            if (status) break;
         }
+        if (status != MTSB_OK || !any_busy) break;
+        if (!progressed) {
+            // nothing ready: block on one busy lane instead of spinning
+            for (Lane &L : lanes) if (L.busy) { cudaEventSynchronize(L.ev); break; }
+        }
+    }
+    for (Lane &L : lanes) if (L.st) {
+        cudaError_t e = cudaStreamSynchronize(L.st);
+        if (e != cudaSuccess && status == MTSB_OK) status = cuda_fail(e, "mtsb_render", __FILE__, __LINE__);
     }
     cudaEventRecord(ev1, s->stream);
     cudaError_t e = cudaStreamSynchronize(s->stream);
     if (e != cudaSuccess && status == MTSB_OK) status = cuda_fail(e, "mtsb_render", __FILE__, __LINE__);
     if (status == MTSB_OK) { e = cudaGetLastError(); if (e != cudaSuccess) status = cuda_fail(e, "mtsb_render kernels", __FILE__, __LINE__); }
     if (stats && status == MTSB_OK) {
-        Counters hc;
+        Counters hc; memset(&hc, 0, sizeof(hc));
+        float st[ST_N] = {0, 0, 0, 0, 0};
+        for (Lane &L : lanes) {
+            Counters c;
+            cudaMemcpy(&c, L.pb->ctr, sizeof(c), cudaMemcpyDeviceToHost);
+            hc.closest += c.closest; hc.shadow += c.shadow; hc.shade += c.shade; hc.path_len += c.path_len;
+            L.timer->collect(st, ST_N);
+        }
         unsigned long long bad = 0;
-        cudaMemcpy(&hc, pb.ctr, sizeof(hc), cudaMemcpyDeviceToHost);
         cudaMemcpy(&bad, s->d_film_bad, sizeof(bad), cudaMemcpyDeviceToHost);
-        float st[ST_N]; timer.collect(st, ST_N);
         float total = 0; cudaEventElapsedTime(&total, ev0, ev1);
         // samples counts slots of whole tiles; report the ones inside the crop window
         uint64_t px_in = 0;
@@ -610,10 +747,11 @@ extern "C" int mtsb_render(mtsb_scene_t scene, const MtsbRenderParams *params, M
         stats->samples = px_in * (uint64_t) spp;
         stats->closest_rays = hc.closest; stats->shadow_rays = hc.shadow; stats->shade_events = hc.shade;
         stats->path_length_sum = hc.path_len; stats->kernel_launches = s->launches - launches0; stats->bad_samples = bad;
+        // stage times are summed over lanes; lanes overlap, so the sum can exceed ms_total
         stats->ms_total = total; stats->ms_raygen = st[ST_RAYGEN]; stats->ms_trace_closest = st[ST_CLOSEST]; stats->ms_shade = st[ST_SHADE];
         stats->ms_trace_any = st[ST_ANY]; stats->ms_splat = st[ST_SPLAT]; stats->n_passes = n_passes;
-        (void) samples;
     }
+    for (Lane &L : lanes) { delete L.timer; if (L.ev) cudaEventDestroy(L.ev); }
     cudaEventDestroy(ev0); cudaEventDestroy(ev1);
     return status;
 }

@@ -11,6 +11,7 @@
 namespace mtsb {
 
 struct PathBuffers;   // render.cu
+#define MTSB_MAX_LANES 4
 
 struct Scene {
     int device = 0;
@@ -19,7 +20,8 @@ struct Scene {
     MtsbSceneInfo info{};
     std::atomic<int> cancel{0};
     unsigned long long *d_film_bad = nullptr;
-    PathBuffers *paths = nullptr;
+    PathBuffers *paths[MTSB_MAX_LANES] = {};       // one wavefront pipeline per lane (render.cu)
+    cudaStream_t lane_stream[MTSB_MAX_LANES] = {};
     uint64_t launches = 0;                  // kernels launched by this library for this scene
     cudaStream_t stream = nullptr;
 };

@@ -36,7 +36,6 @@ struct TraceArgs {
     const uint32_t *d_count;     // number of rays if non-null (device), else n_max
     uint32_t n_max;
     uint32_t *work_counter;      // zeroed before the launch
-    unsigned long long *stat_nodes;   // optional: total node visits
 };
 
 template <bool ANY, class Epilogue>
@@ -51,7 +50,6 @@ __global__ void __launch_bounds__(MTSB_TRACE_BLOCK) k_trace(TraceArgs a, Epilogu
     bool exhausted = false;
     uint32_t ray_idx = 0;
     RayIn ray;
-    unsigned long long visited = 0;
     while (true) {
         // ---- refill idle lanes ----
         const unsigned idle = __ballot_sync(0xFFFFFFFFu, !active);
@@ -94,17 +92,12 @@ __global__ void __launch_bounds__(MTSB_TRACE_BLOCK) k_trace(TraceArgs a, Epilogu
             bool done = false;
             if (active && tr.tg != 0) done = tr.template test_triangle<ANY>(a.tris);
             __syncwarp();
-            if (active && (done || tr.advance())) {
+            if (active && (done || tr.finished())) {
                 ep(ray_idx, ray, tr.hit);
-                visited += tr.steps;
                 active = false;
             }
             live = __ballot_sync(0xFFFFFFFFu, active);
         } while (live != 0 && (exhausted || __popc(live) >= MTSB_REFILL));
-    }
-    if (a.stat_nodes) {
-        for (int o = 16; o; o >>= 1) visited += __shfl_xor_sync(0xFFFFFFFFu, visited, o);
-        if (lane == 0 && visited) atomicAdd(a.stat_nodes, visited);
     }
 }
 
@@ -120,13 +113,12 @@ int device_sm_count();   // api.cu: zeroed counter for the next launch
 int trace_grid(Scene *s, const void *kernel);
 
 template <bool ANY, class Epilogue>
-int launch_trace_kernel(Scene *s, const RayIn *d_rays, const uint32_t *d_count, uint32_t n_max, Epilogue ep, cudaStream_t st,
-                        unsigned long long *stat_nodes = nullptr) {
+int launch_trace_kernel(Scene *s, const RayIn *d_rays, const uint32_t *d_count, uint32_t n_max, Epilogue ep, cudaStream_t st) {
     if (n_max == 0) return MTSB_OK;
     TraceArgs a;
     a.nodes = s->v.nodes; a.tris = s->v.tris; a.n_nodes = s->v.n_nodes;
     for (int k = 0; k < 3; ++k) { a.box_lo[k] = s->v.box_lo[k]; a.box_hi[k] = s->v.box_hi[k]; }
-    a.rays = d_rays; a.d_count = d_count; a.n_max = n_max; a.stat_nodes = stat_nodes;
+    a.rays = d_rays; a.d_count = d_count; a.n_max = n_max;
     a.work_counter = trace_work_counter(s, st);
     if (!a.work_counter) return MTSB_ERR_CUDA;
     int grid = trace_grid(s, (const void *) k_trace<ANY, Epilogue>);

@@ -114,9 +114,10 @@ template <class Stack> struct Traversal {
     uint32_t ng_x, ng_y;          // current node group: (child base, hit bits<<24 | imask)
     HitOut hit;
     Stack stack;
-    uint32_t steps;               // nodes visited (statistics)
 #if !MTSB_DEVICE_CODE
-    uint32_t tri_tests = 0;       // triangle tests (emulation statistics only)
+    uint32_t steps = 0;           // nodes visited      (emulation statistics only)
+    uint32_t tri_tests = 0;       // triangle tests
+    uint32_t last_batch = 0;      // triangles queued by the last node visit
 #endif
 
     MTSB_HD void begin(const RayIn &r, float mint, float maxt) {
@@ -129,21 +130,28 @@ template <class Stack> struct Traversal {
         ng_x = 0; ng_y = 0x80000000u;
         hit.prim = MTSB_NO_HIT_ID; hit.u = 0; hit.v = 0; hit.t = MTSB_INF;
         stack.reset();
-        steps = 0; tg = 0; tri_base = 0;
+        tg = 0; tri_base = 0; tg2 = 0; tri_base2 = 0;
+#if !MTSB_DEVICE_CODE
+        steps = 0; last_batch = 0;
+#endif
     }
 
-    // The query is a small state machine with three transitions, so that a warp can run its 32
-    // rays in lock step: every iteration each lane (a) visits one node if it has no triangle
-    // pending, (b) tests ONE pending triangle, (c) pops the next group or finishes.  Lanes with
-    // many triangles therefore never hold back lanes that are descending.
-    // Invariant between iterations: tg != 0 (triangles pending) or ng_y has child-hit bits.
-    uint32_t tg;                  // pending triangle bits of the current node
-    uint32_t tri_base;            // first triangle record of the current node
+    // The query is a small state machine, so that a warp can run its 32 rays in lock step.  Every
+    // iteration each lane (a) visits one node if it has node work and a free triangle-batch slot,
+    // (b) tests ONE pending triangle, (c) finishes when nothing is left.  A lane keeps up to two
+    // batches of leaf triangles (the one being tested and one deferred), so a lane that is working
+    // through a leaf keeps descending with the rest of the warp instead of idling through the
+    // (expensive) node phase; tools/warp_sim.py has the model behind this choice.
+    uint32_t tg, tri_base;        // triangle batch being tested: pending bits, first triangle record
+    uint32_t tg2, tri_base2;      // deferred batch (empty when tg2 == 0)
 
-    MTSB_HD bool wants_node() const { return tg == 0; }
+    MTSB_HD bool has_nodes() const { return ng_y > 0x00FFFFFFu || !stack.empty(); }
+    MTSB_HD bool wants_node() const { return tg2 == 0 && has_nodes(); }
+    MTSB_HD bool finished() const { return tg == 0 && !has_nodes(); }
 
     // (a) take the nearest pending child of the current group and intersect its 8 children
     MTSB_HD void visit_node(const U4 *nodes) {
+        if (ng_y <= 0x00FFFFFFu) stack.pop(ng_x, ng_y);
         const uint32_t hits_imask = ng_y;
         const int bit = bfind(hits_imask);
         const uint32_t base = ng_x;
@@ -153,13 +161,22 @@ template <class Stack> struct Traversal {
         const uint32_t rel = (uint32_t) popc(hits_imask & ~(0xFFFFFFFFu << slot) & 0xFFu);
         const U4 *np = nodes + 5 * (size_t) (base + rel);
         const U4 n0 = ld16(np), n1 = ld16(np + 1), n2 = ld16(np + 2), n3 = ld16(np + 3), n4 = ld16(np + 4);
+#if !MTSB_DEVICE_CODE
         ++steps;
+#endif
 
         const uint32_t e_imask = n0.w;
         const float sdx = u2f((e_imask & 0xffu) << 23) * idx;
         const float sdy = u2f(((e_imask >> 8) & 0xffu) << 23) * idy;
         const float sdz = u2f(((e_imask >> 16) & 0xffu) << 23) * idz;
         const float ax = (u2f(n0.x) - ox) * idx, ay = (u2f(n0.y) - oy) * idy, az = (u2f(n0.z) - oz) * idz;
+        // Plane bytes are turned into floats by a byte permute: byte_bias_float() = 32768 + q, so the plane
+        // parameter is (32768 + q) * sd + (a - 32768 * sd).  Rounding the biased offset costs at most 2^-9 |sd|
+        // (1/512 of a quantisation step); near planes are pulled in and far planes pushed out by 2^-8 |sd| so the
+        // box test stays conservative (it only ever decides which nodes are visited, never a hit record).
+        const float bx = ax - 32768.0f * sdx, by = ay - 32768.0f * sdy, bz = az - 32768.0f * sdz;
+        const float gx = fabsf(sdx) * 0.00390625f, gy = fabsf(sdy) * 0.00390625f, gz = fabsf(sdz) * 0.00390625f;
+        const float anx = bx - gx, any_ = by - gy, anz = bz - gz, afx = bx + gx, afy = by + gy, afz = bz + gz;
         // near / far planes by ray direction sign
         const bool nx = dx < 0.0f, ny = dy < 0.0f, nz = dz < 0.0f;
         const uint32_t lox0 = n2.x, lox1 = n2.y, loy0 = n2.z, loy1 = n2.w, loz0 = n3.x, loz1 = n3.y;
@@ -192,12 +209,12 @@ template <class Stack> struct Traversal {
 #endif
             for (int j = 0; j < 4; ++j) {
                 const int sh = 8 * j;
-                const float tnx = (float) ((nearx[h] >> sh) & 0xffu) * sdx + ax;
-                const float tny = (float) ((neary[h] >> sh) & 0xffu) * sdy + ay;
-                const float tnz = (float) ((nearz[h] >> sh) & 0xffu) * sdz + az;
-                const float tfx = (float) ((farx[h] >> sh) & 0xffu) * sdx + ax;
-                const float tfy = (float) ((fary[h] >> sh) & 0xffu) * sdy + ay;
-                const float tfz = (float) ((farz[h] >> sh) & 0xffu) * sdz + az;
+                const float tnx = byte_bias_float(nearx[h], j) * sdx + anx;
+                const float tny = byte_bias_float(neary[h], j) * sdy + any_;
+                const float tnz = byte_bias_float(nearz[h], j) * sdz + anz;
+                const float tfx = byte_bias_float(farx[h], j) * sdx + afx;
+                const float tfy = byte_bias_float(fary[h], j) * sdy + afy;
+                const float tfz = byte_bias_float(farz[h], j) * sdz + afz;
                 const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
                 const float cmax = fminf(fminf(tfx, tfy), fminf(tfz, tmax));
                 const uint32_t bits = ((child_bits4[h] >> sh) & 0xffu) << ((bit_index4[h] >> sh) & 0xffu);
@@ -206,8 +223,11 @@ template <class Stack> struct Traversal {
         }
         ng_x = n1.x;
         ng_y = (hitmask & 0xFF000000u) | (e_imask >> 24);
-        tg = hitmask & 0x00FFFFFFu;
-        tri_base = n1.y;
+        const uint32_t batch = hitmask & 0x00FFFFFFu;
+        if (tg == 0) { tg = batch; tri_base = n1.y; } else { tg2 = batch; tri_base2 = n1.y; }
+#if !MTSB_DEVICE_CODE
+        last_batch = batch;
+#endif
     }
 
     // (b) test one pending triangle; returns true when an any-hit query is satisfied
@@ -218,6 +238,7 @@ template <class Stack> struct Traversal {
         ++tri_tests;
 #endif
         const U4 *tp = tris + 3 * ((size_t) tri_base + (size_t) i);
+        if (tg == 0) { tg = tg2; tri_base = tri_base2; tg2 = 0; }      // promote the deferred batch
         const U4 q0 = ld16(tp), q1 = ld16(tp + 1), q2 = ld16(tp + 2);
         float u, v, t;
         if (tri_test(q0, q1, q2, ox, oy, oz, dx, dy, dz, tmin, tmax, u, v, t)) {
@@ -228,19 +249,11 @@ template <class Stack> struct Traversal {
         return false;
     }
 
-    // (c) next group: returns true when the query is finished
-    MTSB_HD bool advance() {
-        if (tg != 0 || ng_y > 0x00FFFFFFu) return false;
-        if (stack.empty()) return true;
-        stack.pop(ng_x, ng_y);
-        return false;
-    }
-
     // one lock-step iteration for a single ray
     template <bool ANY> MTSB_HD bool step(const U4 *nodes, const U4 *tris) {
         if (wants_node()) visit_node(nodes);
         if (tg != 0 && test_triangle<ANY>(tris)) return true;
-        return advance();
+        return finished();
     }
 };
 

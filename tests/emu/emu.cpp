@@ -224,3 +224,29 @@ extern "C" void *emu_build_sah(const float *positions, const uint32_t *indices, 
     s->nodes.swap(nodes); s->tris.swap(tri_out);
     return s;
 }
+
+// Per-ray traversal profile for the warp-scheduling model in tools/warp_sim.py: seq[i*max_len + k] is the
+// number of triangle tests that followed node visit k of ray i (lens[i] = number of node visits, capped).
+extern "C" void emu_trace_profile(void *h, const RayIn *rays, size_t n, int mode, uint8_t *seq, uint32_t max_len, uint32_t *lens) {
+    EmuScene *s = static_cast<EmuScene *>(h);
+    const U4 *nodes = reinterpret_cast<const U4 *>(s->nodes.data()), *tris = reinterpret_cast<const U4 *>(s->tris.data());
+    for (size_t i = 0; i < n; ++i) {
+        uint32_t len = 0;
+        float mint, maxt;
+        if (!s->nodes.empty() && ray_interval(rays[i], s->box_lo, s->box_hi, mode == 1, mint, maxt)) {
+            Traversal<LocalStack<64>> tr;
+            tr.begin(rays[i], mint, maxt);
+            for (;;) {
+                if (tr.wants_node()) {
+                    tr.visit_node(nodes);
+                    if (len < max_len) seq[i * (size_t) max_len + len] = (uint8_t) __builtin_popcount(tr.last_batch);
+                    ++len;
+                }
+                bool done = false;
+                if (tr.tg != 0) done = mode == 1 ? tr.test_triangle<true>(tris) : tr.test_triangle<false>(tris);
+                if (done || tr.finished()) break;
+            }
+        }
+        lens[i] = len < max_len ? len : max_len;
+    }
+}
