@@ -244,17 +244,25 @@ def run_b200_arm(args):
     e2e_t0 = time.time()
     e2e_samples = 0.0
     d2h = 0
+    e2e_split = {"create": 0.0, "render": 0.0, "develop": 0.0, "destroy": 0.0}
     for i in range(args.steps):
+        t0 = time.time()
         sc = lib.Scene(desc_pair)                                   # H2D of the scene arrays + BVH build
+        t1 = time.time()
         st = sc.render(spp=total_spp, seed=300 + i, tile_index=rank, tile_count=world)
+        t2 = time.time()
         if world > 1:
             mdist.reduce_film(mdist.film_tensor(sc), dst=0)
             torch.cuda.synchronize()
         if rank == 0:
             img = sc.film_develop()                                 # D2H of the developed image
             d2h = int(img.nbytes)
+        t3 = time.time()
         e2e_samples += st.samples
         sc.close()
+        t4 = time.time()
+        for k, dt in zip(("create", "render", "develop", "destroy"), (t1 - t0, t2 - t1, t3 - t2, t4 - t3)):
+            e2e_split[k] += dt * 1e3 / args.steps
     barrier()
     e2e_s = time.time() - e2e_t0
     e2e_all = torch.tensor([e2e_samples], dtype=torch.float64, device="cuda")
@@ -292,7 +300,8 @@ def run_b200_arm(args):
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
                          "bytes_per_ray": b_c},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": host_bytes(builder), "d2h_bytes_per_step": d2h,
-                    "includes": "mtsb_scene_create (H2D + GPU BVH build) + mtsb_render + film reduce + mtsb_film_develop (D2H) per step"},
+                    "includes": "mtsb_scene_create (H2D + GPU BVH build) + mtsb_render + film reduce + mtsb_film_develop (D2H) per step",
+                    "wall_ms_per_step": {k: round(v, 2) for k, v in e2e_split.items()}},
             "gpu_launches": launches_all, "clocks": clk,
         }
         if not args.no_cpu_baseline and world == 1:

@@ -74,9 +74,9 @@ __device__ __forceinline__ SampleStream slot_stream(const SceneView &sc, const P
     return SampleStream(ps.seed, (pixel << 24) | (uint64_t) (ps.s_first + s_local));
 }
 
-__global__ void k_pass_begin(PathBuffers pb) {
+__global__ void k_pass_begin(PathBuffers pb, uint32_t n_slots) {
     Counters *c = pb.ctr;
-    c->n_rays[0] = c->n_rays[1] = 0; c->n_shadow = 0;
+    c->n_rays[0] = n_slots; c->n_rays[1] = 0; c->n_shadow = 0;          // k_raygen fills queue entry `slot` for every slot
     for (int i = 0; i < Q_COUNT; ++i) c->n_q[i] = 0;
 }
 
@@ -85,7 +85,15 @@ __global__ void k_raygen(SceneView sc, PathBuffers pb, PassInfo ps, uint32_t n_s
     for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n_slots; slot += gridDim.x * blockDim.x) {
         int px, py; uint32_t s_local;
         const bool valid = slot_pixel(sc, pb, ps, slot, px, py, s_local);
-        if (!valid) { pb.refn_flags[slot] = make_float4(0, 0, 0, __uint_as_float(0u)); continue; }
+        pb.ray_slot[0][slot] = slot;
+        if (!valid) {
+            // pixel of an edge tile outside the film: an empty-interval ray (reported as a miss, ignored by k_miss / k_splat).
+            // The primary queue is indexed by slot, so no queue atomics are needed here.
+            pb.refn_flags[slot] = make_float4(0, 0, 0, __uint_as_float(0u));
+            RayIn dead; dead.ox = dead.oy = dead.oz = 0.0f; dead.dx = dead.dy = 0.0f; dead.dz = 1.0f; dead.mint = 0.0f; dead.maxt = -1.0f;
+            store_ray(pb.rays[0], slot, dead);
+            continue;
+        }
         float u[4];
         slot_stream(sc, ps, px, py, s_local).block4(0, 0, u);
         const float sx = (float) px + u[0], sy = (float) py + u[1];
@@ -95,44 +103,57 @@ __global__ void k_raygen(SceneView sc, PathBuffers pb, PassInfo ps, uint32_t n_s
         pb.thr_eta[slot] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
         pb.L_bpdf[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         pb.refn_flags[slot] = make_float4(0, 0, 0, __uint_as_float(1u | PF_FIRST | PF_VALID));
-        const uint32_t q = queue_push(&pb.ctr->n_rays[0]);
-        store_ray(pb.rays[0], q, ray);
-        pb.ray_slot[0][q] = slot;
+        store_ray(pb.rays[0], slot, ray);
     }
 }
 
-__global__ void k_bounce_prepare(PathBuffers pb, int cur) {
+// n_count: rays of this bounce that count as traced (the primary queue also holds the dead rays of edge tiles)
+__global__ void k_bounce_prepare(PathBuffers pb, int cur, uint32_t n_count) {
     Counters *c = pb.ctr;
-    c->closest += c->n_rays[cur];
+    c->closest += n_count ? n_count : c->n_rays[cur];
     c->shadow += c->n_shadow;
     c->n_shadow = 0; c->n_rays[1 - cur] = 0;
     for (int i = 0; i < Q_COUNT; ++i) c->n_q[i] = 0;
 }
 __global__ void k_pass_end(PathBuffers pb) { Counters *c = pb.ctr; c->shadow += c->n_shadow; c->n_shadow = 0; }
 
-// bins the hits of this bounce by scattering model
-__global__ void k_sort(SceneView sc, PathBuffers pb, int cur) {
+// bins the hits of this bounce by scattering model.  Queue space is reserved once per BLOCK and queue
+// (shared-memory counts, one global atomic per non-empty queue): per-warp atomics on a single counter
+// run at ~1 G/s on this part and were a visible share of the stage.
+#define MTSB_SORT_BLOCK 512
+__global__ void __launch_bounds__(MTSB_SORT_BLOCK) k_sort(SceneView sc, PathBuffers pb, int cur) {
+    __shared__ uint32_t s_cnt[Q_COUNT], s_base[Q_COUNT];
     const uint32_t n = pb.ctr->n_rays[cur];
-    for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < n; q += gridDim.x * blockDim.x) {
-        const uint32_t prim = pb.hits[q].prim;
-        int which = Q_MISS;
-        if (prim != MTSB_NO_HIT_ID) {
-            const int mat = sc.shapes[sc.tri_shape[prim]].material;
-            if (mat < 0) which = Q_NULL;
-            else {
-                const MtsbMaterial &m = sc.materials[mat];
-                which = m.type == MTSB_BSDF_DIFFUSE ? Q_DIFFUSE : m.type == MTSB_BSDF_ROUGHCONDUCTOR ? Q_CONDUCTOR
-                      : m.type == MTSB_BSDF_ROUGHDIELECTRIC ? Q_DIELECTRIC : Q_NULL;
-                if ((m.flags & MTSB_MAT_TWOSIDED) && m.back >= 0 && sc.materials[m.back].type != m.type) which = Q_GENERIC;
+    for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
+        const uint32_t q = base + threadIdx.x;
+        if (threadIdx.x < Q_COUNT) s_cnt[threadIdx.x] = 0;
+        __syncthreads();
+        int which = -1;
+        if (q < n) {
+            const uint32_t prim = pb.hits[q].prim;
+            which = Q_MISS;
+            if (prim != MTSB_NO_HIT_ID) {
+                const int mat = sc.shapes[sc.tri_shape[prim]].material;
+                if (mat < 0) which = Q_NULL;
+                else {
+                    const MtsbMaterial &m = sc.materials[mat];
+                    which = m.type == MTSB_BSDF_DIFFUSE ? Q_DIFFUSE : m.type == MTSB_BSDF_ROUGHCONDUCTOR ? Q_CONDUCTOR
+                          : m.type == MTSB_BSDF_ROUGHDIELECTRIC ? Q_DIELECTRIC : Q_NULL;
+                    if ((m.flags & MTSB_MAT_TWOSIDED) && m.back >= 0 && sc.materials[m.back].type != m.type) which = Q_GENERIC;
+                }
             }
         }
-        const unsigned active = __activemask();
-        const unsigned peers = __match_any_sync(active, which);
+        // rank inside the block: warp-aggregated shared-memory atomic
+        const unsigned peers = __match_any_sync(0xFFFFFFFFu, which);
         const int leader = __ffs(peers) - 1;
-        uint32_t base = 0;
-        if ((int) (threadIdx.x & 31) == leader) base = atomicAdd(&pb.ctr->n_q[which], (uint32_t) __popc(peers));
-        base = __shfl_sync(peers, base, leader);
-        pb.q[which][base + (uint32_t) __popc(peers & ((1u << (threadIdx.x & 31)) - 1u))] = q;
+        uint32_t wbase = 0;
+        if (which >= 0 && (int) (threadIdx.x & 31) == leader) wbase = atomicAdd(&s_cnt[which], (uint32_t) __popc(peers));
+        wbase = __shfl_sync(0xFFFFFFFFu, wbase, leader);
+        const uint32_t rank = wbase + (uint32_t) __popc(peers & ((1u << (threadIdx.x & 31)) - 1u));
+        __syncthreads();
+        if (threadIdx.x < Q_COUNT) s_base[threadIdx.x] = s_cnt[threadIdx.x] ? atomicAdd(&pb.ctr->n_q[threadIdx.x], s_cnt[threadIdx.x]) : 0u;
+        __syncthreads();
+        if (which >= 0) pb.q[which][s_base[which] + rank] = q;
     }
 }
 
@@ -170,9 +191,18 @@ template <int Q> __device__ __forceinline__ bool sample_q(const MtsbMaterial *ma
 
 template <int Q>
 __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBuffers pb, PassInfo ps, RenderConst rc, int cur) {
+    // Outputs (shadow ray + pending contribution, continuation ray) are staged in shared memory and queue space is
+    // reserved once per block and queue at the end of the iteration: one global atomic per block instead of one per warp.
+    __shared__ float4 s_sray[2 * MTSB_SHADE_BLOCK], s_contrib[MTSB_SHADE_BLOCK], s_nray[2 * MTSB_SHADE_BLOCK];
+    __shared__ uint32_t s_wcnt[2][MTSB_SHADE_BLOCK / 32], s_qbase[2];
     const uint32_t n = pb.ctr->n_q[Q];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned long long shade_events = 0, path_len = 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    for (uint32_t i0 = blockIdx.x * blockDim.x; i0 < n; i0 += gridDim.x * blockDim.x) {
+        const uint32_t i = i0 + threadIdx.x;
+        bool have_shadow = false;
+        uint32_t spawn_slot = 0xFFFFFFFFu;
+        if (i < n) {
         const uint32_t q = pb.q[Q][i];
         const uint32_t slot = pb.ray_slot[cur][q];
         const RayIn ray = load_ray(pb.rays[cur], q);
@@ -249,9 +279,10 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBu
                         // shadow segment of Scene::sampleEmitterDirect (scene.cpp:840-846)
                         RayIn sr; sr.ox = dRec.ref.x; sr.oy = dRec.ref.y; sr.oz = dRec.ref.z; sr.dx = dRec.d.x; sr.dy = dRec.d.y; sr.dz = dRec.d.z;
                         sr.mint = MTSB_EPSILON; sr.maxt = dRec.dist * (1 - MTSB_SHADOW_EPSILON);
-                        const uint32_t sq = queue_push(&pb.ctr->n_shadow);
-                        store_ray(pb.srays, sq, sr);
-                        pb.scontrib[sq] = make_float4(contrib.x, contrib.y, contrib.z, __uint_as_float(slot));
+                        s_sray[2 * threadIdx.x] = make_float4(sr.ox, sr.oy, sr.oz, sr.mint);
+                        s_sray[2 * threadIdx.x + 1] = make_float4(sr.dx, sr.dy, sr.dz, sr.maxt);
+                        s_contrib[threadIdx.x] = make_float4(contrib.x, contrib.y, contrib.z, __uint_as_float(slot));
+                        have_shadow = true;
                     }
                 }
                 // ---- BSDF sampling (path.cpp:208-221) ----
@@ -270,9 +301,9 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBu
                     if (!(rc.strict_normals && dot(its.geoN, wo) * cosTheta(bs.wo) <= 0)) {
                         RayIn nr; nr.ox = its.p.x; nr.oy = its.p.y; nr.oz = its.p.z; nr.dx = wo.x; nr.dy = wo.y; nr.dz = wo.z;
                         nr.mint = MTSB_EPSILON; nr.maxt = MTSB_INF;
-                        const uint32_t nq = queue_push(&pb.ctr->n_rays[1 - cur]);
-                        store_ray(pb.rays[1 - cur], nq, nr);
-                        pb.ray_slot[1 - cur][nq] = slot;
+                        s_nray[2 * threadIdx.x] = make_float4(nr.ox, nr.oy, nr.oz, nr.mint);
+                        s_nray[2 * threadIdx.x + 1] = make_float4(nr.dx, nr.dy, nr.dz, nr.maxt);
+                        spawn_slot = slot;
                         thr *= bs.weight; eta *= bs.eta;
                         pb.thr_eta[slot] = make_float4(thr.x, thr.y, thr.z, eta);
                         pb.L_bpdf[slot] = make_float4(L.x, L.y, L.z, bs.pdf);
@@ -289,6 +320,31 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBu
             fl = (fl & ~PF_DEPTH_MASK) | ((uint32_t) depth & PF_DEPTH_MASK);
             pb.refn_flags[slot] = make_float4(0, 0, 0, __uint_as_float(fl));
         }
+        }   // i < n
+        // ---- reserve queue space for the whole block, then copy the staged records out ----
+        const unsigned b_s = __ballot_sync(0xFFFFFFFFu, have_shadow), b_r = __ballot_sync(0xFFFFFFFFu, spawn_slot != 0xFFFFFFFFu);
+        if (lane == 0) { s_wcnt[0][warp] = (uint32_t) __popc(b_s); s_wcnt[1][warp] = (uint32_t) __popc(b_r); }
+        __syncthreads();
+        if (threadIdx.x < 2) {
+            uint32_t tot = 0;
+            for (int w = 0; w < MTSB_SHADE_BLOCK / 32; ++w) { const uint32_t c = s_wcnt[threadIdx.x][w]; s_wcnt[threadIdx.x][w] = tot; tot += c; }
+            s_qbase[threadIdx.x] = tot ? atomicAdd(threadIdx.x == 0 ? &pb.ctr->n_shadow : &pb.ctr->n_rays[1 - cur], tot) : 0u;
+        }
+        __syncthreads();
+        const uint32_t lt = (1u << lane) - 1u;
+        if (have_shadow) {
+            const uint32_t sq = s_qbase[0] + s_wcnt[0][warp] + (uint32_t) __popc(b_s & lt);
+            reinterpret_cast<float4 *>(pb.srays)[2 * (size_t) sq] = s_sray[2 * threadIdx.x];
+            reinterpret_cast<float4 *>(pb.srays)[2 * (size_t) sq + 1] = s_sray[2 * threadIdx.x + 1];
+            pb.scontrib[sq] = s_contrib[threadIdx.x];
+        }
+        if (spawn_slot != 0xFFFFFFFFu) {
+            const uint32_t nq = s_qbase[1] + s_wcnt[1][warp] + (uint32_t) __popc(b_r & lt);
+            reinterpret_cast<float4 *>(pb.rays[1 - cur])[2 * (size_t) nq] = s_nray[2 * threadIdx.x];
+            reinterpret_cast<float4 *>(pb.rays[1 - cur])[2 * (size_t) nq + 1] = s_nray[2 * threadIdx.x + 1];
+            pb.ray_slot[1 - cur][nq] = spawn_slot;
+        }
+        __syncthreads();
     }
     for (int o = 16; o; o >>= 1) { shade_events += __shfl_xor_sync(0xFFFFFFFFu, shade_events, o); path_len += __shfl_xor_sync(0xFFFFFFFFu, path_len, o); }
     if ((threadIdx.x & 31) == 0) {
@@ -307,6 +363,7 @@ __global__ void k_miss(SceneView sc, PathBuffers pb, RenderConst rc, int cur) {
         float4 lb = pb.L_bpdf[slot];
         const float4 rf = pb.refn_flags[slot];
         const uint32_t fl = __float_as_uint(rf.w);
+        if (!(fl & PF_VALID)) continue;                                        // dead ray of an edge tile
         path_len += (unsigned long long) (fl & PF_DEPTH_MASK);
         if (sc.env_emitter >= 0) {
             const float4 te = pb.thr_eta[slot];
@@ -355,7 +412,7 @@ struct ShadowResolve {
 // summation order inside the tile.  Only the final add into the film is atomic (tile borders overlap).
 #define MTSB_SPLAT_CHUNK 4
 __global__ void __launch_bounds__(256) k_splat(SceneView sc, PathBuffers pb, PassInfo ps, unsigned long long *bad) {
-    extern __shared__ float4 s_stage[];                 // [chunk][1024] value (rgb, alpha or -1 = skip), then [chunk][1024] float2 positions
+    extern __shared__ float4 s_stage[];                 // [chunk][1024] value (rgb, alpha), then [chunk][1024] float2 positions
     __shared__ float s_filter[32];                      // the discretised filter (a per-thread index into kernel parameters would serialise)
     if (threadIdx.x < 32) s_filter[threadIdx.x] = sc.filter_table[threadIdx.x];
     const float f_scale = sc.filter_scale;
@@ -380,8 +437,8 @@ __global__ void __launch_bounds__(256) k_splat(SceneView sc, PathBuffers pb, Pas
             const uint32_t slot = slot0 + pix * ps.spp_pass + c0 + sl;
             const uint32_t fl = __float_as_uint(pb.refn_flags[slot].w);
             const int x = (int) compact1by1(pix), y = (int) compact1by1(pix >> 1);
-            float4 val = make_float4(0, 0, 0, -1.0f);
-            float2 pos = make_float2(0, 0);
+            float4 val = make_float4(0, 0, 0, 0);
+            float2 pos = make_float2(1e30f, 1e30f);       // skipped slots sit outside every footprint
             if (fl & PF_VALID) {
                 const float4 lb = pb.L_bpdf[slot];
                 if (isfinite(lb.x) && isfinite(lb.y) && isfinite(lb.z)) {               // imageblock.h:147-153
@@ -398,6 +455,7 @@ __global__ void __launch_bounds__(256) k_splat(SceneView sc, PathBuffers pb, Pas
         // ---- gather: one bordered pixel per thread iteration ----
         for (int p = threadIdx.x; p < sx * sy; p += blockDim.x) {
             const int X = p % sx, Y = p / sx;
+            const float Xf = (float) X, Yf = (float) Y;
             // tile pixels whose samples can reach (X, Y): |X - px| <= r with px in [x' + b - 0.5, x' + b + 0.5)
             const int x_lo = max(0, (int) ceilf((float) (X - b) - r - 0.5f)), x_hi = min(bw - 1, (int) floorf((float) (X - b) + r + 0.5f));
             const int y_lo = max(0, (int) ceilf((float) (Y - b) - r - 0.5f)), y_hi = min(bh - 1, (int) floorf((float) (Y - b) + r + 0.5f));
@@ -406,14 +464,13 @@ __global__ void __launch_bounds__(256) k_splat(SceneView sc, PathBuffers pb, Pas
                 for (int yy = y_lo; yy <= y_hi; ++yy)
                     for (int xx = x_lo; xx <= x_hi; ++xx) {
                         const int j = sl * MTSB_TILE * MTSB_TILE + yy * MTSB_TILE + xx;
-                        const float4 val = s_val[j];
-                        if (val.w < 0.0f) continue;
                         const float2 pos = s_pos[j];
-                        // ImageBlock::put pixel range of this sample, clipped to the block
-                        if ((float) X < ceilf(pos.x - r) || (float) X > floorf(pos.x + r) ||
-                            (float) Y < ceilf(pos.y - r) || (float) Y > floorf(pos.y + r)) continue;
-                        const float w = s_filter[min((int) fabsf(((float) X - pos.x) * f_scale), 31)] *
-                                        s_filter[min((int) fabsf(((float) Y - pos.y) * f_scale), 31)];
+                        // ImageBlock::put pixel range of this sample, ceil(pos - r) .. floor(pos + r): for an integer X,
+                        // X >= ceil(y) <=> X >= y and X <= floor(z) <=> X <= z, so no rounding instruction is needed
+                        if (Xf < pos.x - r || Xf > pos.x + r || Yf < pos.y - r || Yf > pos.y + r) continue;
+                        const float4 val = s_val[j];
+                        const float w = s_filter[min((int) fabsf((Xf - pos.x) * f_scale), 31)] *
+                                        s_filter[min((int) fabsf((Yf - pos.y) * f_scale), 31)];
                         acc[0] += w * val.x; acc[1] += w * val.y; acc[2] += w * val.z; acc[3] += w * val.w; acc[4] += w;
                     }
             float *dest = sc.film + ((size_t) (oy + Y) * fsx + (ox + X)) * 5;
@@ -530,7 +587,7 @@ static int shade_grid(size_t n_upper, int sm_count) {
 }
 
 // One pass = a block of tiles x a block of samples, small enough for the path buffers of a lane.
-struct Pass { PassInfo ps; uint32_t n_slots; };
+struct Pass { PassInfo ps; uint32_t n_slots, n_valid; };
 
 // A lane is an independent wavefront pipeline (own stream, own path buffers).  Passes are handed to
 // lanes as they become free, so the thin late bounces of one pass -- launches with few rays that
@@ -545,6 +602,7 @@ struct Lane {
     Pass pass{};
     uint32_t n_cur = 0;
     int cur = 0;
+    bool first = false;            // the bounce in flight is the primary one
 };
 
 static int lane_bounce(Scene *s, Lane &L, const RenderConst &rcst, int sm_count) {
@@ -556,8 +614,9 @@ static int lane_bounce(Scene *s, Lane &L, const RenderConst &rcst, int sm_count)
     if (rc) return rc;
     L.timer->begin(ST_SHADE, L.n_cur);
     const int g = shade_grid(L.n_cur, sm_count);
-    k_bounce_prepare<<<1, 1, 0, L.st>>>(pb, L.cur);
-    k_sort<<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.cur);
+    k_bounce_prepare<<<1, 1, 0, L.st>>>(pb, L.cur, L.first ? L.pass.n_valid : 0u);
+    L.first = false;
+    k_sort<<<std::max(1, std::min((int) ((L.n_cur + MTSB_SORT_BLOCK - 1) / MTSB_SORT_BLOCK), sm_count * 4)), MTSB_SORT_BLOCK, 0, L.st>>>(v, pb, L.cur);
     k_shade<Q_DIFFUSE><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur);
     k_shade<Q_CONDUCTOR><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur);
     k_shade<Q_DIELECTRIC><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur);
@@ -576,9 +635,9 @@ static int lane_bounce(Scene *s, Lane &L, const RenderConst &rcst, int sm_count)
 }
 
 static int lane_start(Scene *s, Lane &L, const Pass &p, const RenderConst &rcst, int sm_count) {
-    L.pass = p; L.busy = true; L.cur = 0; L.n_cur = p.n_slots;      // upper bound for the first bounce
+    L.pass = p; L.busy = true; L.cur = 0; L.n_cur = p.n_slots; L.first = true;
     L.timer->begin(ST_RAYGEN);
-    k_pass_begin<<<1, 1, 0, L.st>>>(*L.pb);
+    k_pass_begin<<<1, 1, 0, L.st>>>(*L.pb, p.n_slots);
     k_raygen<<<shade_grid(p.n_slots, sm_count), MTSB_SHADE_BLOCK, 0, L.st>>>(s->v, *L.pb, p.ps, p.n_slots);
     s->launches += 2;
     L.timer->end();
@@ -662,6 +721,12 @@ extern "C" int mtsb_render(mtsb_scene_t scene, const MtsbRenderParams *params, M
             p.ps.spp_pass = std::min<uint32_t>(spp_pass, (uint32_t) spp - s0);
             p.ps.s_first = (uint32_t) params->spp_offset + s0; p.ps.tiles_x = tiles_x; p.ps.seed = params->seed;
             p.n_slots = (uint32_t) (p.ps.n_tiles * px_per_tile * p.ps.spp_pass);
+            uint64_t px_valid = 0;
+            for (uint32_t t = t0; t < t0 + p.ps.n_tiles; ++t) {
+                const int ox = (tiles[t] % (int) tiles_x) * MTSB_TILE, oy = (tiles[t] / (int) tiles_x) * MTSB_TILE;
+                px_valid += (uint64_t) std::min(MTSB_TILE, v.film_w - ox) * (uint64_t) std::min(MTSB_TILE, v.film_h - oy);
+            }
+            p.n_valid = (uint32_t) (px_valid * p.ps.spp_pass);
             passes.push_back(p);
         }
     n_lanes = std::min<int>(n_lanes, (int) passes.size());
