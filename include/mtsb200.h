@@ -211,7 +211,9 @@ void mtsb_scene_destroy(mtsb_scene_t scene);
 
 /* Host-buffer ray query: copies rays in, traces, copies hits out. */
 int  mtsb_trace(mtsb_scene_t scene, const MtsbRay *rays, size_t n, int mode, MtsbHit *hits);
-/* Device-resident variant: d_rays/d_hits are device pointers; `stream` is a cudaStream_t (or NULL).
+/* Device-resident variant: d_rays/d_hits are device pointers; `stream` is a cudaStream_t. The kernel is ordered after
+ * the work already queued on that stream (pass the stream that produced d_rays). NULL selects the scene's own
+ * non-blocking stream: then the caller must have synchronised the producer of d_rays itself.
  * ms_kernel (optional) receives the kernel time measured with CUDA events on that stream. */
 int  mtsb_trace_device(mtsb_scene_t scene, const void *d_rays, size_t n, int mode, void *d_hits,
                        void *stream, float *ms_kernel);

@@ -410,7 +410,7 @@ struct ShadowResolve {
 // time, row-major), then every thread owns bordered pixels and sums the samples whose footprint
 // covers them -- same weights as the scatter form, no shared-memory atomics, and a fixed
 // summation order inside the tile.  Only the final add into the film is atomic (tile borders overlap).
-#define MTSB_SPLAT_CHUNK 4
+#define MTSB_SPLAT_CHUNK 1
 __global__ void __launch_bounds__(256) k_splat(SceneView sc, PathBuffers pb, PassInfo ps, unsigned long long *bad) {
     extern __shared__ float4 s_stage[];                 // [chunk][1024] value (rgb, alpha), then [chunk][1024] float2 positions
     __shared__ float s_filter[32];                      // the discretised filter (a per-thread index into kernel parameters would serialise)

@@ -36,6 +36,7 @@ struct TraceArgs {
     const uint32_t *d_count;     // number of rays if non-null (device), else n_max
     uint32_t n_max;
     uint32_t *work_counter;      // zeroed before the launch
+    int refill;                  // refill a warp when fewer lanes than this are busy
 };
 
 template <bool ANY, class Epilogue>
@@ -97,7 +98,7 @@ __global__ void __launch_bounds__(MTSB_TRACE_BLOCK) k_trace(TraceArgs a, Epilogu
                 active = false;
             }
             live = __ballot_sync(0xFFFFFFFFu, active);
-        } while (live != 0 && (exhausted || __popc(live) >= MTSB_REFILL));
+        } while (live != 0 && (exhausted || __popc(live) >= a.refill));
     }
 }
 
@@ -119,6 +120,7 @@ int launch_trace_kernel(Scene *s, const RayIn *d_rays, const uint32_t *d_count, 
     a.nodes = s->v.nodes; a.tris = s->v.tris; a.n_nodes = s->v.n_nodes;
     for (int k = 0; k < 3; ++k) { a.box_lo[k] = s->v.box_lo[k]; a.box_hi[k] = s->v.box_hi[k]; }
     a.rays = d_rays; a.d_count = d_count; a.n_max = n_max;
+    { static int r = 0; if (!r) { const char *e = getenv("MTSB_REFILL"); r = e ? atoi(e) : MTSB_REFILL; } a.refill = r; }
     a.work_counter = trace_work_counter(s, st);
     if (!a.work_counter) return MTSB_ERR_CUDA;
     int grid = trace_grid(s, (const void *) k_trace<ANY, Epilogue>);
