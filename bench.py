@@ -282,6 +282,16 @@ def run_b200_arm(args):
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         achieved = closest * b_c / (ms_closest * 1e-3) / 1e9 if ms_closest > 0 else 0.0
+        # measured DRAM traffic of the same kernel (one ncu --set full capture, profiles/r01_traffic.json), per launch
+        traffic, n_closest_launches = None, 0
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+            bpr = tj.get(args.workload, {}).get("dram_bytes_per_ray_closest")
+            n_closest_launches = max(1, (launches_all // world) // 11)        # 11 kernels per bounce, one of them k_trace<closest>
+            if bpr:
+                traffic = bpr * closest / n_closest_launches
+        except Exception:
+            pass
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": max_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -296,7 +306,9 @@ def run_b200_arm(args):
             "stage_ms_last_step": {"raygen": s0.ms_raygen, "trace_closest": s0.ms_trace_closest, "shade": s0.ms_shade,
                                    "trace_any": s0.ms_trace_any, "splat": s0.ms_splat, "total": s0.ms_total, "passes": s0.n_passes},
             "roofline": {"bound": "hbm", "kernel": "k_trace<closest>", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None,
+                         "frac": achieved / peak, "traffic": traffic,
+                         "traffic_note": "DRAM bytes per k_trace<closest> launch = measured bytes/ray (ncu, profiles/r01_traffic.json) x mean rays per launch; "
+                                         "algorithmic bytes/ray = %d, so the BVH is served by L2 and the kernel is issue/L1-bound, not HBM-bound" % b_c,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
                          "bytes_per_ray": b_c},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": host_bytes(builder), "d2h_bytes_per_step": d2h,

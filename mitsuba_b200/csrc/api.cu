@@ -60,6 +60,7 @@ int trace_grid(Scene *s, const void *kernel) {
         set_error("occupancy query failed"); cudaGetLastError(); return -1;
     }
     int grid = per_sm * (g_sm_count > 0 ? g_sm_count : 148);
+    { const char *e = getenv("MTSB_GRID_DIV"); if (e && atoi(e) > 1) grid = std::max(1, grid / atoi(e)); }     // experiments: share the SMs between lanes
     cache[kernel] = grid;
     return grid;
 }

@@ -208,14 +208,13 @@ extern "C" int mtsb_film_develop(mtsb_scene_t scene, float *rgb) {
     if (!s || !rgb) { set_error("mtsb_film_develop: bad argument"); return MTSB_ERR_INVALID; }
     MTSB_CUDA(cudaSetDevice(s->device));
     size_t n = (size_t) s->v.film_w * s->v.film_h;
-    float *d = nullptr;
-    MTSB_CUDA(cudaMalloc((void **) &d, 3 * n * sizeof(float)));
+    if (!s->d_rgb) { int rc = dev_alloc(s, &s->d_rgb, 3 * n); if (rc) return rc; }      // kept for the life of the scene
+    float *d = s->d_rgb;
     k_develop<<<grid_for(n, 256), 256, 0, s->stream>>>(s->v, d);
     s->launches++;
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaMemcpyAsync(rgb, d, 3 * n * sizeof(float), cudaMemcpyDeviceToHost, s->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
-    cudaFree(d);
     if (e != cudaSuccess) return cuda_fail(e, "mtsb_film_develop", __FILE__, __LINE__);
     return MTSB_OK;
 }

@@ -20,6 +20,7 @@ struct Scene {
     MtsbSceneInfo info{};
     std::atomic<int> cancel{0};
     unsigned long long *d_film_bad = nullptr;
+    float *d_rgb = nullptr;                 // developed image staging (mtsb_film_develop)
     PathBuffers *paths[MTSB_MAX_LANES] = {};       // one wavefront pipeline per lane (render.cu)
     cudaStream_t lane_stream[MTSB_MAX_LANES] = {};
     uint64_t launches = 0;                  // kernels launched by this library for this scene
