@@ -54,7 +54,9 @@ enum {
 
 /* ---- material table (reference: src/bsdfs) --------------------------- */
 enum { MTSB_BSDF_DIFFUSE = 0, MTSB_BSDF_ROUGHCONDUCTOR = 1, MTSB_BSDF_ROUGHDIELECTRIC = 2,
-       MTSB_BSDF_NULL = 3 /* shape without a BSDF: absorbs (emitter-only quads) */ };
+       MTSB_BSDF_NULL = 3 /* shape without a BSDF: absorbs (emitter-only quads) */,
+       MTSB_BSDF_DIELECTRIC = 4 /* smooth: dielectric.cpp, both lobes Dirac deltas */,
+       MTSB_BSDF_CONDUCTOR = 5  /* smooth: conductor.cpp, one delta reflection lobe */ };
 enum { MTSB_DISTR_BECKMANN = 0, MTSB_DISTR_GGX = 1 };           /* microfacet.h:48-57 */
 enum { MTSB_MAT_TWOSIDED = 1u, MTSB_MAT_SAMPLE_VISIBLE = 2u };
 

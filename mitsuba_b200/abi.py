@@ -11,7 +11,7 @@ import numpy as np
 ABI_VERSION = 1
 
 OK, ERR_INVALID, ERR_NO_DEVICE, ERR_CUDA, ERR_CANCELLED, ERR_IO, ERR_PARSE = range(7)
-BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_ROUGHDIELECTRIC, BSDF_NULL = range(4)
+BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_ROUGHDIELECTRIC, BSDF_NULL, BSDF_DIELECTRIC, BSDF_CONDUCTOR = range(6)
 DISTR_BECKMANN, DISTR_GGX = 0, 1
 MAT_TWOSIDED, MAT_SAMPLE_VISIBLE = 1, 2
 EMITTER_AREA, EMITTER_POINT, EMITTER_CONSTANT = 0, 1, 2

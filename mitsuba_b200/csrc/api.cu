@@ -49,6 +49,74 @@ uint32_t *trace_work_counter(Scene *s, cudaStream_t st) {
 
 int device_sm_count() { return g_sm_count > 0 ? g_sm_count : 148; }
 
+// ---- device block cache -------------------------------------------------------------------------
+// cudaMalloc / cudaFree cost tens to hundreds of milliseconds per scene once the process holds a few
+// GB (every call updates the page tables of the whole context and cudaFree synchronises the device).
+// A frame loop that re-creates its scene per frame (the e2e path of bench.py, an animation) would pay
+// that every frame, so blocks freed by mtsb_scene_destroy and the build / query temporaries are kept
+// per device and size class and handed out again.  Callers synchronise their streams before dfree().
+namespace {
+struct BlockCache {
+    std::mutex m;
+    std::multimap<size_t, void *> free_blocks;       // size class -> block
+    std::map<void *, size_t> live;                   // block -> size class
+    size_t cached_bytes = 0;
+};
+std::map<int, BlockCache> g_block_cache;
+std::mutex g_block_cache_mutex;
+size_t cache_limit_bytes() {
+    static const size_t v = [] { const char *e = getenv("MTSB_CACHE_MB"); return (size_t) (e ? std::max(0, atoi(e)) : 8192) << 20; }();
+    return v;
+}
+size_t size_class(size_t bytes) {
+    if (bytes < 16) bytes = 16;
+    const size_t g = bytes <= (1u << 20) ? 512 : (size_t) 2 << 20;       // cudaMalloc granularity above 1 MiB is 2 MiB
+    return (bytes + g - 1) / g * g;
+}
+BlockCache &cache_of_current_device() {
+    int dev = 0; cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> g(g_block_cache_mutex);
+    return g_block_cache[dev];
+}
+}  // namespace
+
+cudaError_t dmalloc(void **p, size_t bytes) {
+    BlockCache &c = cache_of_current_device();
+    const size_t sc = size_class(bytes);
+    std::lock_guard<std::mutex> g(c.m);
+    auto it = c.free_blocks.find(sc);
+    if (it != c.free_blocks.end()) {
+        *p = it->second; c.free_blocks.erase(it); c.cached_bytes -= sc; c.live[*p] = sc;
+        return cudaSuccess;
+    }
+    cudaError_t e = cudaMalloc(p, sc);
+    if (e != cudaSuccess && !c.free_blocks.empty()) {                     // out of memory: give the cache back and retry
+        cudaGetLastError();
+        for (auto &b : c.free_blocks) cudaFree(b.second);
+        c.free_blocks.clear(); c.cached_bytes = 0;
+        e = cudaMalloc(p, sc);
+    }
+    if (e == cudaSuccess) c.live[*p] = sc;
+    return e;
+}
+void dfree(void *p) {
+    if (!p) return;
+    BlockCache &c = cache_of_current_device();
+    std::lock_guard<std::mutex> g(c.m);
+    auto it = c.live.find(p);
+    if (it == c.live.end()) { cudaFree(p); return; }
+    const size_t sc = it->second;
+    c.live.erase(it);
+    if (c.cached_bytes + sc > cache_limit_bytes()) { cudaFree(p); return; }
+    c.free_blocks.emplace(sc, p); c.cached_bytes += sc;
+}
+void dcache_release() {
+    BlockCache &c = cache_of_current_device();
+    std::lock_guard<std::mutex> g(c.m);
+    for (auto &b : c.free_blocks) cudaFree(b.second);
+    c.free_blocks.clear(); c.cached_bytes = 0;
+}
+
 int trace_grid(Scene *s, const void *kernel) {
     static std::mutex m;
     static std::map<const void *, int> cache;
@@ -112,7 +180,7 @@ static int validate(const MtsbSceneDesc *d) {
     if (tri_sum != d->n_tris) { set_error("shape triangle counts do not add up to n_tris"); return MTSB_ERR_INVALID; }
     for (uint32_t i = 0; i < d->n_materials; ++i) {
         const MtsbMaterial &m = d->materials[i];
-        if (m.type > MTSB_BSDF_NULL || m.distribution > MTSB_DISTR_GGX || m.back >= (int32_t) d->n_materials) { set_error("bad material record"); return MTSB_ERR_INVALID; }
+        if (m.type > MTSB_BSDF_CONDUCTOR || m.distribution > MTSB_DISTR_GGX || m.back >= (int32_t) d->n_materials) { set_error("bad material record"); return MTSB_ERR_INVALID; }
     }
     int n_env = 0;
     for (uint32_t i = 0; i < d->n_emitters; ++i) {
@@ -158,6 +226,9 @@ extern "C" int mtsb_scene_create(const MtsbSceneDesc *d, mtsb_scene_t *out) {
     if ((rc = dev_upload(s, &v.indices, d->indices, 3 * (size_t) d->n_tris))) return fail(rc);
     if ((rc = dev_upload(s, &v.shapes, d->shapes, (size_t) d->n_shapes))) return fail(rc);
     if ((rc = dev_upload(s, &v.materials, d->materials, (size_t) d->n_materials))) return fail(rc);
+    s->h_materials.assign(d->materials, d->materials + d->n_materials);
+    s->h_shape_material.resize(d->n_shapes);
+    for (uint32_t i = 0; i < d->n_shapes; ++i) s->h_shape_material[i] = d->shapes[i].material;
     if ((rc = dev_upload(s, &v.emitters, d->emitters, (size_t) d->n_emitters))) return fail(rc);
     {   // primitive -> shape map (ShapeKDTree::findShape, skdtree.h:205-210, as a table)
         std::vector<uint32_t> ts((size_t) d->n_tris);
@@ -261,7 +332,8 @@ extern "C" void mtsb_scene_destroy(mtsb_scene_t scene) {
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
     render_free(s);
-    for (void *p : s->allocs) cudaFree(p);
+    cudaDeviceSynchronize();                 // what cudaFree did implicitly: nothing may still read a block that goes back to the cache
+    for (void *p : s->allocs) dfree(p);
     if (s->stream) cudaStreamDestroy(s->stream);
     delete s;
 }

@@ -279,7 +279,7 @@ struct Microfacet {
     MTSB_HD float pdf(V3 wi, V3 m) const { return visible ? pdfVisible(wi, m) : pdfAll(m); }            // :270-275
 };
 
-struct BsdfSample { V3 wo; V3 weight; float pdf; float eta; };
+struct BsdfSample { V3 wo; V3 weight; float pdf; float eta; bool delta; };
 
 MTSB_HD Microfacet distr_of(const MtsbMaterial &m) {
     return Microfacet((int) m.distribution, m.alpha_u, m.alpha_v, (m.flags & MTSB_MAT_SAMPLE_VISIBLE) != 0);
@@ -297,7 +297,7 @@ MTSB_HD float diffuse_pdf(V3 wi, V3 wo) {
 MTSB_HD bool diffuse_sample(const MtsbMaterial &m, V3 wi, P2 u, BsdfSample &s) {
     if (cosTheta(wi) <= 0) return false;
     s.wo = squareToCosineHemisphere(u);
-    s.eta = 1.0f;
+    s.eta = 1.0f; s.delta = false;
     s.pdf = squareToCosineHemispherePdf(s.wo);
     s.weight = ld3(m.reflectance);
     return true;
@@ -329,7 +329,7 @@ MTSB_HD bool roughconductor_sample(const MtsbMaterial &m, V3 wi, P2 u, BsdfSampl
     V3 mm = distr.sample(wi, u, pdf);
     if (pdf == 0) return false;
     s.wo = reflect(wi, mm);
-    s.eta = 1.0f;
+    s.eta = 1.0f; s.delta = false;
     if (cosTheta(s.wo) <= 0) return false;
     V3 F = fresnelConductorExact(dot(wi, mm), ld3(m.cond_eta), ld3(m.cond_k)) * ld3(m.reflectance);
     float weight;
@@ -404,6 +404,7 @@ MTSB_HD bool roughdielectric_sample(const MtsbMaterial &m, V3 wi, P2 u, float u1
     bool sampleReflection = true;
     if (u1 > F) { sampleReflection = false; pdf *= 1 - F; } else pdf *= F;
     float dwh_dwo;
+    s.delta = false;
     if (sampleReflection) {
         s.wo = reflect(wi, mm);
         s.eta = 1.0f;
@@ -425,6 +426,40 @@ MTSB_HD bool roughdielectric_sample(const MtsbMaterial &m, V3 wi, P2 u, float u1
     pdf *= fabsf(dwh_dwo);
     s.pdf = pdf;
     s.weight = weight;
+    return true;
+}
+
+// ---- SmoothDielectric (src/bsdfs/dielectric.cpp, mode == ERadiance) ----------------------------
+// Both lobes are Dirac deltas: eval()/pdf() under the solid-angle measure of `path` are zero
+// (:224-226, :256-259), so only sample() exists here.
+MTSB_HD bool dielectric_sample(const MtsbMaterial &m, V3 wi, P2 u, BsdfSample &s) {           // :277-301
+    const float m_eta = m.eta, m_invEta = 1 / m.eta;
+    float cosThetaT;
+    const float F = fresnelDielectricExt(cosTheta(wi), cosThetaT, m_eta);
+    s.delta = true;
+    if (u.x <= F) {
+        s.wo = V3(-wi.x, -wi.y, wi.z);                                                        // :206-208
+        s.eta = 1.0f;
+        s.pdf = F;
+        s.weight = ld3(m.reflectance);
+    } else {
+        const float scale = -(cosThetaT < 0 ? m_invEta : m_eta);                              // :211-214
+        s.wo = V3(scale * wi.x, scale * wi.y, cosThetaT);
+        s.eta = cosThetaT < 0 ? m_eta : m_invEta;
+        s.pdf = 1 - F;
+        const float factor = cosThetaT < 0 ? m_invEta : m_eta;
+        s.weight = ld3(m.transmittance) * (factor * factor);
+    }
+    return true;
+}
+// ---- SmoothConductor (src/bsdfs/conductor.cpp:268-285) ----------------------------------------
+MTSB_HD bool conductor_sample(const MtsbMaterial &m, V3 wi, BsdfSample &s) {
+    if (cosTheta(wi) <= 0) return false;
+    s.delta = true;
+    s.wo = V3(-wi.x, -wi.y, wi.z);
+    s.eta = 1.0f;
+    s.pdf = 1.0f;
+    s.weight = ld3(m.reflectance) * fresnelConductorExact(cosTheta(wi), ld3(m.cond_eta), ld3(m.cond_k));
     return true;
 }
 
@@ -452,6 +487,8 @@ MTSB_HD bool bsdf_sample_one(const MtsbMaterial &m, V3 wi, P2 u, float u1, BsdfS
         case MTSB_BSDF_DIFFUSE: return diffuse_sample(m, wi, u, s);
         case MTSB_BSDF_ROUGHCONDUCTOR: return roughconductor_sample(m, wi, u, s);
         case MTSB_BSDF_ROUGHDIELECTRIC: return roughdielectric_sample(m, wi, u, u1, s);
+        case MTSB_BSDF_DIELECTRIC: return dielectric_sample(m, wi, u, s);
+        case MTSB_BSDF_CONDUCTOR: return conductor_sample(m, wi, s);
         default: return false;
     }
 }
@@ -489,9 +526,17 @@ MTSB_HD int bsdf_effective_material(const MtsbMaterial *mats, int id, float wi_z
     return id;
 }
 // BSDF::getType() bits that path.cpp reads: ESmooth (path.cpp:177); ETransmission|EBackSide (records.inl:175-179)
-MTSB_HD bool bsdf_is_smooth(const MtsbMaterial &m) { return m.type != MTSB_BSDF_NULL; }
+// (a twosided wrapper reports the union of both nested types, twosided.cpp:72-99)
+MTSB_HD bool bsdf_type_is_smooth(uint32_t t) {
+    return t == MTSB_BSDF_DIFFUSE || t == MTSB_BSDF_ROUGHCONDUCTOR || t == MTSB_BSDF_ROUGHDIELECTRIC;
+}
+MTSB_HD bool bsdf_type_is_delta(uint32_t t) { return t == MTSB_BSDF_DIELECTRIC || t == MTSB_BSDF_CONDUCTOR; }
+MTSB_HD bool bsdf_is_smooth(const MtsbMaterial *mats, const MtsbMaterial &m) {
+    if (bsdf_type_is_smooth(m.type)) return true;
+    return (m.flags & MTSB_MAT_TWOSIDED) && m.back >= 0 && bsdf_type_is_smooth(mats[m.back].type);
+}
 MTSB_HD bool bsdf_has_back_or_transmission(const MtsbMaterial &m) {
-    return m.type == MTSB_BSDF_ROUGHDIELECTRIC || (m.flags & MTSB_MAT_TWOSIDED);
+    return m.type == MTSB_BSDF_ROUGHDIELECTRIC || m.type == MTSB_BSDF_DIELECTRIC || (m.flags & MTSB_MAT_TWOSIDED);
 }
 
 }  // namespace mtsb

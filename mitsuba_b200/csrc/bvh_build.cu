@@ -63,7 +63,7 @@ int build_bvh(Scene *s, const float *d_positions, const uint32_t *d_indices, uin
     std::vector<void *> tmp;
     auto talloc = [&](size_t bytes) -> void * {
         void *p = nullptr;
-        if (cudaMalloc(&p, bytes ? bytes : 16) != cudaSuccess) return nullptr;
+        if (dmalloc(&p, bytes ? bytes : 16) != cudaSuccess) return nullptr;
         tmp.push_back(p);
         return p;
     };
@@ -175,7 +175,7 @@ int build_bvh(Scene *s, const float *d_positions, const uint32_t *d_indices, uin
         s->info.tri_bytes = (uint64_t) n * sizeof(TriRec); s->info.build_ms = ms;
     }
 done:
-    for (void *p : tmp) cudaFree(p);
+    for (void *p : tmp) dfree(p);            // the stream was synchronised above (or the build failed)
     if (ev0) cudaEventDestroy(ev0);
     if (ev1) cudaEventDestroy(ev1);
     return rc;

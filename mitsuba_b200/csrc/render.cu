@@ -120,6 +120,17 @@ __global__ void k_pass_end(PathBuffers pb) { Counters *c = pb.ctr; c->shadow += 
 // bins the hits of this bounce by scattering model.  Queue space is reserved once per BLOCK and queue
 // (shared-memory counts, one global atomic per non-empty queue): per-warp atomics on a single counter
 // run at ~1 G/s on this part and were a visible share of the stage.
+__host__ __device__ inline int queue_of_type(uint32_t t) {
+    return t == MTSB_BSDF_DIFFUSE ? Q_DIFFUSE : t == MTSB_BSDF_ROUGHCONDUCTOR ? Q_CONDUCTOR : t == MTSB_BSDF_ROUGHDIELECTRIC ? Q_DIELECTRIC
+         : (t == MTSB_BSDF_DIELECTRIC || t == MTSB_BSDF_CONDUCTOR) ? Q_DELTA : Q_NULL;
+}
+__host__ __device__ inline int queue_of_material(const MtsbMaterial *mats, int mat) {
+    if (mat < 0) return Q_NULL;
+    const MtsbMaterial &m = mats[mat];
+    const int q = queue_of_type(m.type);
+    if ((m.flags & MTSB_MAT_TWOSIDED) && m.back >= 0 && queue_of_type(mats[m.back].type) != q) return Q_GENERIC;
+    return q;
+}
 #define MTSB_SORT_BLOCK 512
 __global__ void __launch_bounds__(MTSB_SORT_BLOCK) k_sort(SceneView sc, PathBuffers pb, int cur) {
     __shared__ uint32_t s_cnt[Q_COUNT], s_base[Q_COUNT];
@@ -131,17 +142,7 @@ __global__ void __launch_bounds__(MTSB_SORT_BLOCK) k_sort(SceneView sc, PathBuff
         int which = -1;
         if (q < n) {
             const uint32_t prim = pb.hits[q].prim;
-            which = Q_MISS;
-            if (prim != MTSB_NO_HIT_ID) {
-                const int mat = sc.shapes[sc.tri_shape[prim]].material;
-                if (mat < 0) which = Q_NULL;
-                else {
-                    const MtsbMaterial &m = sc.materials[mat];
-                    which = m.type == MTSB_BSDF_DIFFUSE ? Q_DIFFUSE : m.type == MTSB_BSDF_ROUGHCONDUCTOR ? Q_CONDUCTOR
-                          : m.type == MTSB_BSDF_ROUGHDIELECTRIC ? Q_DIELECTRIC : Q_NULL;
-                    if ((m.flags & MTSB_MAT_TWOSIDED) && m.back >= 0 && sc.materials[m.back].type != m.type) which = Q_GENERIC;
-                }
-            }
+            which = prim != MTSB_NO_HIT_ID ? queue_of_material(sc.materials, sc.shapes[sc.tri_shape[prim]].material) : (int) Q_MISS;
         }
         // rank inside the block: warp-aggregated shared-memory atomic
         const unsigned peers = __match_any_sync(0xFFFFFFFFu, which);
@@ -184,6 +185,7 @@ template <int Q> __device__ __forceinline__ bool sample_q(const MtsbMaterial *ma
     if (Q == Q_DIFFUSE) ok = diffuse_sample(*m, wi, u, s);
     else if (Q == Q_CONDUCTOR) ok = roughconductor_sample(*m, wi, u, s);
     else if (Q == Q_DIELECTRIC) ok = roughdielectric_sample(*m, wi, u, u1, s);
+    else if (Q == Q_DELTA) ok = m->type == MTSB_BSDF_DIELECTRIC ? dielectric_sample(*m, wi, u, s) : conductor_sample(*m, wi, s);
     else ok = false;
     if (flip && ok && !isZero(s.weight) && s.pdf != 0) s.wo.z *= -1;
     return ok;
@@ -234,7 +236,8 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBu
                 DRec dRec;
                 dRec.ref = V3(ray.ox, ray.oy, ray.oz); dRec.refN = prevRefN; dRec.p = its.p; dRec.n = its.sh.n;
                 dRec.d = rd; dRec.dist = ht; dRec.measure = MTSB_MEASURE_SOLID_ANGLE; dRec.emitter = shape.emitter;
-                const float lumPdf = pdf_emitter_direct(sc, dRec);
+                // a negative stored pdf marks a Dirac lobe: lumPdf = 0 (path.cpp:263-264)
+                const float lumPdf = bsdfPdfPrev < 0 ? 0.0f : pdf_emitter_direct(sc, dRec);
                 L += thr * value * mi_weight(bsdfPdfPrev, lumPdf);
             }
             // Russian roulette (path.cpp:278-288)
@@ -265,9 +268,12 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBu
                 ss.block4((uint32_t) depth, 0, u);
                 const MtsbMaterial &m0 = sc.materials[mat];
                 if (!bsdf_has_back_or_transmission(m0)) dRec.refN = its.sh.n;              // records.inl:175-179
-                // ---- direct illumination (path.cpp:174-202) ----
+                // ---- direct illumination (path.cpp:174-202): only for BSDFs with a smooth component (:176-177) ----
+                const bool smooth = Q == Q_DELTA ? false : Q == Q_GENERIC ? bsdf_is_smooth(sc.materials, m0) : true;
                 P2 ue; ue.x = u[0]; ue.y = u[1];
-                const V3 value = sample_emitter_direct(sc, dRec, ue);
+                V3 value(0.0f);
+                dRec.pdf = 0;
+                if (smooth) value = sample_emitter_direct(sc, dRec, ue);
                 if (dRec.pdf != 0 && !isZero(value)) {
                     const V3 wo = its.sh.toLocal(dRec.d);
                     const V3 bsdfVal = eval_q<Q>(sc.materials, mat, its.wi, wo);
@@ -306,7 +312,8 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBu
                         spawn_slot = slot;
                         thr *= bs.weight; eta *= bs.eta;
                         pb.thr_eta[slot] = make_float4(thr.x, thr.y, thr.z, eta);
-                        pb.L_bpdf[slot] = make_float4(L.x, L.y, L.z, bs.pdf);
+                        const bool delta = (Q == Q_DELTA || Q == Q_GENERIC) && bs.delta;
+                        pb.L_bpdf[slot] = make_float4(L.x, L.y, L.z, delta ? -bs.pdf : bs.pdf);
                         fl = (fl & ~(PF_DEPTH_MASK | PF_FIRST)) | ((uint32_t) depth & PF_DEPTH_MASK);
                         pb.refn_flags[slot] = make_float4(dRec.refN.x, dRec.refN.y, dRec.refN.z, __uint_as_float(fl));
                         spawned = true;
@@ -379,7 +386,7 @@ __global__ void k_miss(SceneView sc, PathBuffers pb, RenderConst rc, int cur) {
                 if (bsphere_intersect(sc.bsphere_c, sc.bsphere_r, o, d, nearT, farT) && !(nearT > 0 || farT < 0)) {
                     DRec dRec; dRec.ref = o; dRec.refN = V3(rf.x, rf.y, rf.z); dRec.p = o; dRec.n = V3(0.0f); dRec.d = d; dRec.dist = farT;
                     dRec.measure = MTSB_MEASURE_SOLID_ANGLE; dRec.emitter = sc.env_emitter;
-                    const float w = mi_weight(lb.w, pdf_emitter_direct(sc, dRec));
+                    const float w = mi_weight(lb.w, lb.w < 0 ? 0.0f : pdf_emitter_direct(sc, dRec));
                     lb.x += thr.x * value.x * w; lb.y += thr.y * value.y * w; lb.z += thr.z * value.z * w;
                 }
             }
@@ -603,6 +610,7 @@ struct Lane {
     uint32_t n_cur = 0;
     int cur = 0;
     bool first = false;            // the bounce in flight is the primary one
+    uint32_t queue_mask = 0;       // shading queues this scene can feed
 };
 
 static int lane_bounce(Scene *s, Lane &L, const RenderConst &rcst, int sm_count) {
@@ -617,13 +625,16 @@ static int lane_bounce(Scene *s, Lane &L, const RenderConst &rcst, int sm_count)
     k_bounce_prepare<<<1, 1, 0, L.st>>>(pb, L.cur, L.first ? L.pass.n_valid : 0u);
     L.first = false;
     k_sort<<<std::max(1, std::min((int) ((L.n_cur + MTSB_SORT_BLOCK - 1) / MTSB_SORT_BLOCK), sm_count * 4)), MTSB_SORT_BLOCK, 0, L.st>>>(v, pb, L.cur);
-    k_shade<Q_DIFFUSE><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur);
-    k_shade<Q_CONDUCTOR><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur);
-    k_shade<Q_DIELECTRIC><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur);
-    k_shade<Q_NULL><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur);
-    k_shade<Q_GENERIC><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur);
+    // only the queues some material of this scene can feed are launched
+    const uint32_t qm = L.queue_mask;
+    if (qm & (1u << Q_DIFFUSE))    { k_shade<Q_DIFFUSE><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
+    if (qm & (1u << Q_CONDUCTOR))  { k_shade<Q_CONDUCTOR><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
+    if (qm & (1u << Q_DIELECTRIC)) { k_shade<Q_DIELECTRIC><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
+    if (qm & (1u << Q_NULL))       { k_shade<Q_NULL><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
+    if (qm & (1u << Q_GENERIC))    { k_shade<Q_GENERIC><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
+    if (qm & (1u << Q_DELTA))      { k_shade<Q_DELTA><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
     k_miss<<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, rcst, L.cur);
-    s->launches += 8;
+    s->launches += 3;
     L.timer->end();
     L.timer->begin(ST_ANY, L.n_cur);
     rc = launch_trace_kernel<true>(s, pb.srays, &pb.ctr->n_shadow, L.n_cur, ShadowResolve{pb.scontrib, pb.L_bpdf}, L.st);
@@ -739,12 +750,14 @@ extern "C" int mtsb_render(mtsb_scene_t scene, const MtsbRenderParams *params, M
     cudaEvent_t ev0, ev1; cudaEventCreate(&ev0); cudaEventCreate(&ev1);
     cudaEventRecord(ev0, s->stream);
     std::vector<Lane> lanes((size_t) n_lanes);
+    uint32_t queue_mask = 0;
+    for (int32_t m : s->h_shape_material) queue_mask |= 1u << queue_of_material(s->h_materials.data(), m);
     int status = MTSB_OK;
     for (int l = 0; l < n_lanes && status == MTSB_OK; ++l) {
         Lane &L = lanes[(size_t) l];
         status = ensure_buffers(s, l, capacity, (uint32_t) tiles.size());
         if (status) break;
-        L.st = s->lane_stream[l]; L.pb = s->paths[l];
+        L.st = s->lane_stream[l]; L.pb = s->paths[l]; L.queue_mask = queue_mask;
         L.timer = new StageTimer(L.st);
         cudaEventCreateWithFlags(&L.ev, cudaEventDisableTiming);
         cudaStreamWaitEvent(L.st, ev0, 0);                               // after the film clear

@@ -5,7 +5,10 @@
 
 namespace mtsb {
 
-enum { Q_DIFFUSE = 0, Q_CONDUCTOR = 1, Q_DIELECTRIC = 2, Q_NULL = 3, Q_GENERIC = 4, Q_MISS = 5, Q_COUNT = 6 };
+// Shading queues: one per scattering model so that every k_shade instance runs one code path.
+// Q_CONDUCTOR / Q_DIELECTRIC are the rough (microfacet) models, Q_DELTA the smooth `dielectric` and
+// `conductor` (Dirac lobes: no emitter sampling), Q_GENERIC twosided wrappers that mix two models.
+enum { Q_DIFFUSE = 0, Q_CONDUCTOR = 1, Q_DIELECTRIC = 2, Q_NULL = 3, Q_GENERIC = 4, Q_DELTA = 5, Q_MISS = 6, Q_COUNT = 7 };
 
 // path flags (stored as float bits in refn_flags.w)
 #define PF_DEPTH_MASK 0xFFFFu
@@ -18,7 +21,7 @@ struct Counters {
     uint32_t n_rays[2];        // closest-ray queue sizes (double buffered)
     uint32_t n_shadow;
     uint32_t n_q[Q_COUNT];
-    uint32_t pad[3];
+    uint32_t pad[2];
     unsigned long long closest, shadow, shade, path_len, bad, samples;
 };
 

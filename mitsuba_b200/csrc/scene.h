@@ -23,6 +23,8 @@ struct Scene {
     float *d_rgb = nullptr;                 // developed image staging (mtsb_film_develop)
     PathBuffers *paths[MTSB_MAX_LANES] = {};       // one wavefront pipeline per lane (render.cu)
     cudaStream_t lane_stream[MTSB_MAX_LANES] = {};
+    std::vector<MtsbMaterial> h_materials;  // host copies for launch decisions (which shading queues can be non-empty)
+    std::vector<int32_t> h_shape_material;
     uint64_t launches = 0;                  // kernels launched by this library for this scene
     cudaStream_t stream = nullptr;
 };
@@ -31,9 +33,14 @@ void set_error(const std::string &s);
 int cuda_fail(cudaError_t e, const char *what, const char *file, int line);
 #define MTSB_CUDA(x) do { cudaError_t e__ = (x); if (e__ != cudaSuccess) return mtsb::cuda_fail(e__, #x, __FILE__, __LINE__); } while (0)
 
+// cached device blocks (api.cu): dfree() keeps a block for the next dmalloc() of the same size class
+cudaError_t dmalloc(void **p, size_t bytes);
+void dfree(void *p);
+void dcache_release();
+
 template <class T> int dev_alloc(Scene *s, T **p, size_t count) {
     void *q = nullptr;
-    cudaError_t e = cudaMalloc(&q, count ? count * sizeof(T) : sizeof(T));
+    cudaError_t e = dmalloc(&q, count ? count * sizeof(T) : sizeof(T));
     if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc", __FILE__, __LINE__);
     if (s) s->allocs.push_back(q);
     *p = static_cast<T *>(q);

@@ -75,15 +75,16 @@ extern "C" int mtsb_trace(mtsb_scene_t scene, const MtsbRay *rays, size_t n, int
     if (n == 0) return MTSB_OK;
     MTSB_CUDA(cudaSetDevice(s->device));
     void *d_rays = nullptr, *d_hits = nullptr;
-    MTSB_CUDA(cudaMalloc(&d_rays, n * sizeof(MtsbRay)));
-    cudaError_t e = cudaMalloc(&d_hits, n * sizeof(MtsbHit));
-    if (e != cudaSuccess) { cudaFree(d_rays); return cuda_fail(e, "cudaMalloc", __FILE__, __LINE__); }
+    MTSB_CUDA(dmalloc(&d_rays, n * sizeof(MtsbRay)));
+    cudaError_t e = dmalloc(&d_hits, n * sizeof(MtsbHit));
+    if (e != cudaSuccess) { dfree(d_rays); return cuda_fail(e, "cudaMalloc", __FILE__, __LINE__); }
     int rc = MTSB_OK;
     e = cudaMemcpyAsync(d_rays, rays, n * sizeof(MtsbRay), cudaMemcpyHostToDevice, s->stream);
     if (e == cudaSuccess) rc = mtsb_trace_device(scene, d_rays, n, mode, d_hits, s->stream, nullptr);
     if (e == cudaSuccess && rc == MTSB_OK) e = cudaMemcpyAsync(hits, d_hits, n * sizeof(MtsbHit), cudaMemcpyDeviceToHost, s->stream);
     if (e == cudaSuccess && rc == MTSB_OK) e = cudaStreamSynchronize(s->stream);
-    cudaFree(d_rays); cudaFree(d_hits);
+    if (e != cudaSuccess || rc != MTSB_OK) cudaStreamSynchronize(s->stream);       // nothing in flight when the blocks go back to the cache
+    dfree(d_rays); dfree(d_hits);
     if (e != cudaSuccess) return cuda_fail(e, "mtsb_trace", __FILE__, __LINE__);
     return rc;
 }

@@ -70,6 +70,43 @@ static void microfacetProps(const Properties &p, MtsbMaterial &m) {
 
 static void set3(float *dst, const Vec3 &v) { dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; }
 
+// eta / k of a conductor (conductor.cpp:146-174, roughconductor.cpp:168-189): material table or explicit values, over extEta
+static void conductorProps(const Properties &p, MtsbMaterial &m, const std::string &plugin) {
+    std::string mat = p.getString("material", "Cu");
+    Vec3 eta{0, 0, 0}, k{1, 1, 1};
+    bool haveTable = true;
+    if (lower(mat) != "none") {
+        // The reference converts data/ior/<material>.{eta,k}.spd to RGB.  Those measured spectra are data files of
+        // the reference distribution; RGB values for the three metals the benchmark scenes use are kept here and
+        // everything else must come as explicit eta / k.
+        static const struct { const char *n; float e[3], k[3]; } metals[] = {
+            {"cu", {0.200438f, 0.924033f, 1.102212f}, {3.912949f, 2.452848f, 2.142188f}},
+            {"au", {0.143119f, 0.374957f, 1.442479f}, {3.983160f, 2.385721f, 1.603215f}},
+            {"al", {1.657460f, 0.880369f, 0.521229f}, {9.223869f, 6.269523f, 4.837001f}}};
+        haveTable = false;
+        for (auto &e : metals)
+            if (lower(mat) == e.n) { eta = Vec3{e.e[0], e.e[1], e.e[2]}; k = Vec3{e.k[0], e.k[1], e.k[2]}; haveTable = true; }
+    }
+    if (!haveTable && !(p.hasProperty("eta") && p.hasProperty("k")))
+        error(plugin + ": no RGB data for material \"" + mat + "\" -- specify 'eta' and 'k' explicitly.");
+    float ext = lookupIOR(p, "extEta", "air");
+    eta = p.getSpectrum("eta", eta);
+    k = p.getSpectrum("k", k);
+    set3(m.cond_eta, Vec3{eta.x / ext, eta.y / ext, eta.z / ext});
+    set3(m.cond_k, Vec3{k.x / ext, k.y / ext, k.z / ext});
+}
+
+// ensureEnergyConservation (bsdf.cpp:96-113) on a constant texture
+static Vec3 conserveEnergy(const std::string &plugin, const char *name, Vec3 r, float maxV) {
+    float mx = std::max(r.x, std::max(r.y, r.z));
+    if (mx > maxV) {
+        warn("BSDF " + plugin + ": " + name + " > " + (maxV == 1.0f ? std::string("1") : std::to_string(maxV)) + " -- scaled to conserve energy");
+        float sc = 0.99f * (maxV / mx);
+        r = Vec3{r.x * sc, r.y * sc, r.z * sc};
+    }
+    return r;
+}
+
 Bsdf::Bsdf(const Properties &p) : ConfigurableObject(p) {
     std::memset(&m_rec, 0, sizeof(m_rec));
     m_rec.back = -1;
@@ -95,28 +132,7 @@ Bsdf::Bsdf(const Properties &p) : ConfigurableObject(p) {
         // roughconductor.cpp:168-201
         m_rec.type = MTSB_BSDF_ROUGHCONDUCTOR;
         set3(m_rec.reflectance, p.getSpectrum("specularReflectance", Vec3{1, 1, 1}));
-        std::string mat = p.getString("material", "Cu");
-        Vec3 eta{0, 0, 0}, k{1, 1, 1};
-        bool haveTable = true;
-        if (lower(mat) != "none") {
-            // The reference converts data/ior/<material>.{eta,k}.spd to RGB.  Those measured spectra are data files of
-            // the reference distribution; RGB values for the three metals the benchmark scenes use are kept here and
-            // everything else must come as explicit eta / k.
-            static const struct { const char *n; float e[3], k[3]; } metals[] = {
-                {"cu", {0.200438f, 0.924033f, 1.102212f}, {3.912949f, 2.452848f, 2.142188f}},
-                {"au", {0.143119f, 0.374957f, 1.442479f}, {3.983160f, 2.385721f, 1.603215f}},
-                {"al", {1.657460f, 0.880369f, 0.521229f}, {9.223869f, 6.269523f, 4.837001f}}};
-            haveTable = false;
-            for (auto &e : metals)
-                if (lower(mat) == e.n) { eta = Vec3{e.e[0], e.e[1], e.e[2]}; k = Vec3{e.k[0], e.k[1], e.k[2]}; haveTable = true; }
-        }
-        if (!haveTable && !(p.hasProperty("eta") && p.hasProperty("k")))
-            error("roughconductor: no RGB data for material \"" + mat + "\" -- specify 'eta' and 'k' explicitly.");
-        float ext = lookupIOR(p, "extEta", "air");
-        eta = p.getSpectrum("eta", eta);
-        k = p.getSpectrum("k", k);
-        set3(m_rec.cond_eta, Vec3{eta.x / ext, eta.y / ext, eta.z / ext});
-        set3(m_rec.cond_k, Vec3{k.x / ext, k.y / ext, k.z / ext});
+        conductorProps(p, m_rec, type);
         microfacetProps(p, m_rec);
     } else if (type == "roughdielectric") {
         // roughdielectric.cpp:183-211
@@ -127,10 +143,23 @@ Bsdf::Bsdf(const Properties &p) : ConfigurableObject(p) {
         if (in < 0 || ex < 0 || in == ex) error("The interior and exterior indices of refraction must be positive and differ!");
         m_rec.eta = in / ex;
         microfacetProps(p, m_rec);
+    } else if (type == "dielectric") {
+        // dielectric.cpp:141-168, 192-197
+        m_rec.type = MTSB_BSDF_DIELECTRIC;
+        float in = lookupIOR(p, "intIOR", "bk7"), ex = lookupIOR(p, "extIOR", "air");
+        if (in < 0 || ex < 0) error("The interior and exterior indices of refraction must be positive!");
+        m_rec.eta = in / ex;
+        set3(m_rec.reflectance, conserveEnergy(type, "specularReflectance", p.getSpectrum("specularReflectance", Vec3{1, 1, 1}), 1.0f));
+        set3(m_rec.transmittance, conserveEnergy(type, "specularTransmittance", p.getSpectrum("specularTransmittance", Vec3{1, 1, 1}), 1.0f));
+    } else if (type == "conductor") {
+        // conductor.cpp:146-174, 189-193
+        m_rec.type = MTSB_BSDF_CONDUCTOR;
+        set3(m_rec.reflectance, conserveEnergy(type, "specularReflectance", p.getSpectrum("specularReflectance", Vec3{1, 1, 1}), 1.0f));
+        conductorProps(p, m_rec, type);
     } else if (type == "twosided") {
         m_twosided = true;
     } else {
-        error("Plugin \"" + type + "\" not found -- the B200 path implements the BSDFs diffuse, roughconductor, roughdielectric and twosided.");
+        error("Plugin \"" + type + "\" not found -- the B200 path implements the BSDFs diffuse, dielectric, conductor, roughconductor, roughdielectric and twosided.");
     }
 }
 

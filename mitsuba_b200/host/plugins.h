@@ -50,7 +50,7 @@ public:
     EClass getClass() const override { return CBsdf; }
     void addChild(const std::string &name, const ObjRef &child) override;   // twosided.cpp:186-196
     void configure() override;
-    bool hasTransmission() const { return m_rec.type == MTSB_BSDF_ROUGHDIELECTRIC; }
+    bool hasTransmission() const { return m_rec.type == MTSB_BSDF_ROUGHDIELECTRIC || m_rec.type == MTSB_BSDF_DIELECTRIC; }
     bool isTwosided() const { return m_twosided; }
     // appends this BSDF's record(s) to `out` (twosided with two children: back first), returns its index
     int flatten(std::vector<MtsbMaterial> &out) const;

@@ -91,6 +91,53 @@ def roughdielectric(int_ior=1.5046, ext_ior=1.000277, alpha=0.1, distribution="b
     return m
 
 
+def _conserve(v, max_value=1.0):
+    """ensureEnergyConservation on a constant texture (src/librender/bsdf.cpp:96-113)."""
+    r = np.asarray(v, dtype=np.float32).reshape(-1)
+    if r.size == 1:
+        r = np.repeat(r, 3)
+    mx = float(r.max())
+    if mx > max_value:
+        r = r * np.float32(0.99 * (max_value / mx))
+    return r
+
+
+def dielectric(int_ior=1.5046, ext_ior=1.000277, specular_reflectance=1.0, specular_transmittance=1.0):
+    """Smooth `dielectric` record (src/bsdfs/dielectric.cpp:141-168, 192-197)."""
+    m = abi.Material()
+    m.type = abi.BSDF_DIELECTRIC
+    m.flags = 0
+    m.back = -1
+    m.alpha_u = m.alpha_v = 0.1
+    m.eta = float(np.float32(int_ior) / np.float32(ext_ior))
+    m.reflectance = _f3(_conserve(specular_reflectance))
+    m.transmittance = _f3(_conserve(specular_transmittance))
+    m.cond_eta = _f3(0.0)
+    m.cond_k = _f3(1.0)
+    return m
+
+
+def conductor(eta, k, specular_reflectance=1.0, ext_eta=1.000277, twosided=False):
+    """Smooth `conductor` record (src/bsdfs/conductor.cpp:146-174, 189-193): eta, k are divided by extEta."""
+    m = abi.Material()
+    m.type = abi.BSDF_CONDUCTOR
+    m.flags = abi.MAT_TWOSIDED if twosided else 0
+    m.back = -1
+    m.alpha_u = m.alpha_v = 0.1
+    e = np.asarray(eta, dtype=np.float32).reshape(-1)
+    kk = np.asarray(k, dtype=np.float32).reshape(-1)
+    if e.size == 1:
+        e = np.repeat(e, 3)
+    if kk.size == 1:
+        kk = np.repeat(kk, 3)
+    m.cond_eta = _f3(e / np.float32(ext_eta))
+    m.cond_k = _f3(kk / np.float32(ext_eta))
+    m.reflectance = _f3(_conserve(specular_reflectance))
+    m.transmittance = _f3(1.0)
+    m.eta = 1.0
+    return m
+
+
 def look_at(origin, target, up):
     """Transform::lookAt (src/libcore/transform.cpp:191-214): row-major camera-to-world."""
     p = np.asarray(origin, dtype=np.float64)

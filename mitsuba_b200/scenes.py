@@ -27,8 +27,9 @@ def _quad(p):
     return np.asarray(p, np.float32), np.array([[0, 1, 2], [0, 2, 3]], np.uint32)
 
 
-def cbox(width=512, height=512, spp=64, max_depth=8, rr_depth=5, twosided=False):
-    """Cornell box, `path` integrator, 512x512, 64 spp, maxDepth 8 (BASELINE.json configs[0])."""
+def cbox(width=512, height=512, spp=64, max_depth=8, rr_depth=5, twosided=False, short_material=None, tall_material=None):
+    """Cornell box, `path` integrator, 512x512, 64 spp, maxDepth 8 (BASELINE.json configs[0]).
+    short_material / tall_material: material records for the two blocks (default: the white diffuse)."""
     b = SceneBuilder()
     b.set_integrator(max_depth=max_depth, rr_depth=rr_depth, sample_count=spp)
     b.set_sensor(look_at([278, 273, -800], [278, 273, -799], [0, 1, 0]), 39.3077, width, height,
@@ -61,10 +62,14 @@ def cbox(width=512, height=512, spp=64, max_depth=8, rr_depth=5, twosided=False)
         [(314, 0, 456), (314, 330, 456), (265, 330, 296), (265, 0, 296)],
         [(265, 0, 296), (265, 330, 296), (423, 330, 247), (423, 0, 247)],
     ]
-    for block in (short, tall):
+    def block_material(m):
+        if m is None:
+            return white
+        return b.add_twosided(*m) if isinstance(m, tuple) else b.add_material(m)
+    for block, m in ((short, block_material(short_material)), (tall, block_material(tall_material))):
         pos = np.concatenate([np.asarray(f, np.float32) for f in block])
         idx = np.concatenate([np.array([[0, 1, 2], [0, 2, 3]], np.uint32) + 4 * k for k in range(5)])
-        b.add_mesh(pos, idx, white)
+        b.add_mesh(pos, idx, m)
     p, i = _quad([(343, 548.75, 227), (343, 548.75, 332), (213, 548.75, 332), (213, 548.75, 227)])
     b.add_mesh(p, i, light, area_radiance=[18.4, 15.6, 8.0])
     return b

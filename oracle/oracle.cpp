@@ -129,7 +129,7 @@ V3 Li(const Scene &sc, const MtsbRay &primary, Rng &rng, Counters &cnt, float &a
         const bool haveMat = mat >= 0;
         if (haveMat && !bsdf_has_back_or_transmission(sc.materials[mat])) dRec.refN = its.sh.n;   // records.inl:175-179
         dRec.emitter = -1;
-        if (haveMat && bsdf_is_smooth(sc.materials[mat])) {
+        if (haveMat && bsdf_is_smooth(sc.materials.data(), sc.materials[mat])) {
             V3 value = sampleEmitterDirectNoVis(sc, dRec, rng.emitter2D(depth));
             if (dRec.pdf != 0) {
                 // scene.cpp:840-846

@@ -316,6 +316,41 @@ inline bool roughdielectric_sample(const MtsbMaterial &m, V3 wi, P2 u, float u1,
     return true;
 }
 
+// ---- SmoothDielectric: src/bsdfs/dielectric.cpp:216-330 (mode == ERadiance) --------
+// Both lobes are Dirac deltas: eval()/pdf() under the solid-angle measure that `path`
+// uses are zero (:224-226, :256-259); only sample() does work.
+inline bool dielectric_sample(const MtsbMaterial &m, V3 wi, P2 u, BsdfSample &s) {      // :277-301
+    const float m_eta = m.eta, m_invEta = 1 / m.eta;
+    float cosThetaT;
+    float F = fresnelDielectricExt(cosTheta(wi), cosThetaT, m_eta);
+    s.delta = true;
+    if (u.x <= F) {
+        s.wo = V3(-wi.x, -wi.y, wi.z);                                                  // reflect(wi) :206-208
+        s.eta = 1.0f;
+        s.pdf = F;
+        s.weight = rgb(m.reflectance);
+    } else {
+        float scale = -(cosThetaT < 0 ? m_invEta : m_eta);                              // refract(wi, cosThetaT) :211-214
+        s.wo = V3(scale * wi.x, scale * wi.y, cosThetaT);
+        s.eta = cosThetaT < 0 ? m_eta : m_invEta;
+        s.pdf = 1 - F;
+        float factor = cosThetaT < 0 ? m_invEta : m_eta;
+        s.weight = rgb(m.transmittance) * (factor * factor);
+    }
+    return true;
+}
+
+// ---- SmoothConductor: src/bsdfs/conductor.cpp:224-285 --------------------------------
+inline bool conductor_sample(const MtsbMaterial &m, V3 wi, P2, BsdfSample &s) {          // :268-285
+    if (cosTheta(wi) <= 0) return false;
+    s.delta = true;
+    s.wo = V3(-wi.x, -wi.y, wi.z);
+    s.eta = 1.0f;
+    s.pdf = 1.0f;
+    s.weight = rgb(m.reflectance) * fresnelConductorExact(cosTheta(wi), rgb(m.cond_eta), rgb(m.cond_k));
+    return true;
+}
+
 // ---- dispatch incl. TwoSided (src/bsdfs/twosided.cpp:108-184) -------------------
 inline V3 bsdf_eval_one(const MtsbMaterial &m, V3 wi, V3 wo) {
     switch (m.type) {
@@ -338,6 +373,8 @@ inline bool bsdf_sample_one(const MtsbMaterial &m, V3 wi, P2 u, float u1, BsdfSa
         case MTSB_BSDF_DIFFUSE: return diffuse_sample(m, wi, u, s);
         case MTSB_BSDF_ROUGHCONDUCTOR: return roughconductor_sample(m, wi, u, s);
         case MTSB_BSDF_ROUGHDIELECTRIC: return roughdielectric_sample(m, wi, u, u1, s);
+        case MTSB_BSDF_DIELECTRIC: return dielectric_sample(m, wi, u, s);
+        case MTSB_BSDF_CONDUCTOR: return conductor_sample(m, wi, u, s);
         default: return false;
     }
 }
@@ -373,9 +410,16 @@ inline bool bsdf_sample(const MtsbMaterial *mats, int id, V3 wi, P2 u, float u1,
 }
 // BSDF::getType() bits that path.cpp looks at: ESmooth (path.cpp:177) and
 // ETransmission|EBackSide (records.inl:175-179).
-inline bool bsdf_is_smooth(const MtsbMaterial &m) { return m.type != MTSB_BSDF_NULL; }
+// A twosided wrapper reports the union of both nested types (twosided.cpp:72-99).
+inline bool bsdf_type_is_smooth(uint32_t t) {
+    return t == MTSB_BSDF_DIFFUSE || t == MTSB_BSDF_ROUGHCONDUCTOR || t == MTSB_BSDF_ROUGHDIELECTRIC;
+}
+inline bool bsdf_is_smooth(const MtsbMaterial *mats, const MtsbMaterial &m) {
+    if (bsdf_type_is_smooth(m.type)) return true;
+    return (m.flags & MTSB_MAT_TWOSIDED) && m.back >= 0 && bsdf_type_is_smooth(mats[m.back].type);
+}
 inline bool bsdf_has_back_or_transmission(const MtsbMaterial &m) {
-    return m.type == MTSB_BSDF_ROUGHDIELECTRIC || (m.flags & MTSB_MAT_TWOSIDED);
+    return m.type == MTSB_BSDF_ROUGHDIELECTRIC || m.type == MTSB_BSDF_DIELECTRIC || (m.flags & MTSB_MAT_TWOSIDED);
 }
 
 }  // namespace orc

@@ -3,7 +3,7 @@ import numpy as np
 import pytest
 
 from mitsuba_b200 import abi, scenes
-from mitsuba_b200.scenedesc import SceneBuilder, diffuse, look_at, roughconductor, roughdielectric
+from mitsuba_b200.scenedesc import SceneBuilder, conductor, dielectric, diffuse, look_at, roughconductor, roughdielectric
 from tests import util
 
 pytestmark = pytest.mark.gpu
@@ -26,6 +26,12 @@ def material_scene():
         "rd_ggx": b.add_material(roughdielectric(1.5, 1.0, alpha=0.3, distribution="ggx")),
         "rd_ggx_all": b.add_material(roughdielectric(1.5, 1.0, alpha=0.2, distribution="ggx", sample_visible=False)),
     }
+    # smooth (Dirac) models, SURVEY 8(f) N3
+    mats["glass"] = b.add_material(dielectric(1.5046, 1.000277, [0.9, 0.8, 0.7], [0.6, 0.5, 0.4]))
+    mats["glass_inv"] = b.add_material(dielectric(1.0, 1.33))
+    mats["mirror"] = b.add_material(conductor(eta, k, specular_reflectance=[1.0, 0.5, 0.25]))
+    mats["mirror2s"] = b.add_material(conductor(0.0, 1.0, twosided=True))
+    mats["mirror_over_diffuse"] = b.add_twosided(conductor(eta, k), diffuse([0.2, 0.4, 0.6]))
     mats["mixed2s"] = b.add_twosided(roughconductor(eta, k, alpha=0.2, distribution="ggx"), diffuse([0.2, 0.4, 0.6]))
     b.add_quad((-1, 0, -1), (-1, 0, 1), (1, 0, 1), (1, 0, -1), mats["diffuse"])
     b.add_quad((-0.3, 2, -0.3), (0.3, 2, -0.3), (0.3, 2, 0.3), (-0.3, 2, 0.3), mats["diffuse"], area_radiance=[5, 4, 3])

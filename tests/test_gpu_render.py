@@ -94,6 +94,35 @@ def test_same_stream_ggx_conductors_1m_family(gpu_lib, oracle_mod):
     check_same_stream(gpu_lib, oracle_mod, b, 4, "1m-small")
 
 
+def _glass_mirror_cbox(**kw):
+    from mitsuba_b200.scenedesc import conductor, dielectric, diffuse
+    eta, k = scenes.METALS["Al"]
+    return scenes.cbox(short_material=dielectric(1.5046, 1.000277), tall_material=conductor(eta, k), **kw)
+
+
+@pytest.mark.parametrize("max_depth", [2, 5, -1])
+def test_same_stream_glass_and_mirror_blocks(gpu_lib, oracle_mod, max_depth):
+    """smooth dielectric + conductor (Dirac lobes: no emitter sampling at the hit, MIS weight 1
+    on the next emitter hit -- path.cpp:176-177, 263-264)."""
+    b = _glass_mirror_cbox(width=64, height=64, spp=4, max_depth=max_depth)
+    check_same_stream(gpu_lib, oracle_mod, b, 4, "cbox glass+mirror maxDepth=%d" % max_depth)
+
+
+def test_same_stream_delta_lobes_in_twosided_wrappers_and_env(gpu_lib, oracle_mod):
+    from mitsuba_b200.scenedesc import conductor, diffuse, roughconductor
+    eta, k = scenes.METALS["Cu"]
+    b = scenes.cbox(width=60, height=44, spp=4, max_depth=6,
+                    short_material=(conductor(eta, k), diffuse([0.2, 0.4, 0.6])),         # mirror outside, diffuse inside
+                    tall_material=(roughconductor(eta, k, alpha=0.2, distribution="ggx"), conductor(0.0, 1.0)))
+    b.add_constant_env([0.3, 0.4, 0.5])
+    check_same_stream(gpu_lib, oracle_mod, b, 4, "cbox twosided delta + env")
+
+
+def test_glass_and_mirror_blocks_independent_streams(gpu_lib, oracle_mod):
+    b = _glass_mirror_cbox(width=48, height=48, spp=32, max_depth=8)
+    check_render(gpu_lib, oracle_mod, b, 32, 256, "cbox glass+mirror")
+
+
 def test_same_stream_point_light_hide_emitters_strict_normals(gpu_lib, oracle_mod):
     b = scenes.cbox(width=48, height=48, spp=4)
     b.add_point_light([278, 400, 279], [4e5, 4e5, 4e5])

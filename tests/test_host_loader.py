@@ -201,6 +201,34 @@ def test_bsdf_records_match_python_builder():
         load('<shape type="rectangle"><bsdf type="roughdielectric"><string name="intIOR" value="unobtainium"/></bsdf></shape>')
 
 
+def test_smooth_dielectric_and_conductor_records():
+    """dielectric.cpp:141-168 / conductor.cpp:146-174 property surface."""
+    hs = load('<shape type="rectangle"><bsdf type="dielectric"/></shape>'
+              '<shape type="rectangle"><bsdf type="dielectric"><string name="intIOR" value="water"/><float name="extIOR" value="1.0"/>'
+              '<rgb name="specularReflectance" value="2,1,1"/><rgb name="specularTransmittance" value="0.5,0.25,0.125"/></bsdf></shape>'
+              '<shape type="rectangle"><bsdf type="conductor"><string name="material" value="Au"/></bsdf></shape>'
+              '<shape type="rectangle"><bsdf type="conductor"><string name="material" value="none"/></bsdf></shape>'
+              '<shape type="rectangle"><bsdf type="twosided"><bsdf type="conductor"><rgb name="eta" value="1,2,3"/><rgb name="k" value="4,5,6"/>'
+              '<float name="extEta" value="2"/></bsdf></bsdf></shape>')
+    m = hs.materials()
+    eta, k = scenes.METALS["Au"]
+    assert bytes(m[0]) == bytes(scenedesc.dielectric())                                    # bk7 / air defaults
+    assert bytes(m[1]) == bytes(scenedesc.dielectric(1.3330, 1.0, [2, 1, 1], [0.5, 0.25, 0.125]))
+    assert list(m[1].reflectance) == pytest.approx([0.99, 0.495, 0.495])                  # ensureEnergyConservation
+    assert any("specularReflectance" in w and "conserve energy" in w for w in hs.warnings)
+    assert bytes(m[2]) == bytes(scenedesc.conductor(eta, k))
+    assert bytes(m[3]) == bytes(scenedesc.conductor(0.0, 1.0))
+    assert bytes(m[4]) == bytes(scenedesc.conductor([1, 2, 3], [4, 5, 6], ext_eta=2.0, twosided=True))
+    with pytest.raises(MtsbError, match="without a transmission component"):
+        load('<shape type="rectangle"><bsdf type="twosided"><bsdf type="dielectric"/></bsdf></shape>')
+    with pytest.raises(MtsbError, match="must be positive"):
+        load('<shape type="rectangle"><bsdf type="dielectric"><float name="intIOR" value="-1"/></bsdf></shape>')
+    with pytest.raises(MtsbError, match="specify 'eta' and 'k'"):
+        load('<shape type="rectangle"><bsdf type="conductor"><string name="material" value="W"/></bsdf></shape>')
+    with pytest.raises(MtsbError, match="not found"):
+        load('<shape type="rectangle"><bsdf type="plastic"/></shape>')
+
+
 def test_twosided_and_shared_references():
     hs = load('<bsdf type="twosided" id="two"><bsdf type="diffuse"><rgb name="reflectance" value="0.1"/></bsdf>'
               '<bsdf type="roughconductor"><string name="material" value="Al"/></bsdf></bsdf>'
