@@ -39,7 +39,7 @@
 extern "C" {
 #endif
 
-#define MTSB_ABI_VERSION 1
+#define MTSB_ABI_VERSION 2
 
 /* ---- status codes ---------------------------------------------------- */
 enum {
@@ -56,9 +56,10 @@ enum {
 enum { MTSB_BSDF_DIFFUSE = 0, MTSB_BSDF_ROUGHCONDUCTOR = 1, MTSB_BSDF_ROUGHDIELECTRIC = 2,
        MTSB_BSDF_NULL = 3 /* shape without a BSDF: absorbs (emitter-only quads) */,
        MTSB_BSDF_DIELECTRIC = 4 /* smooth: dielectric.cpp, both lobes Dirac deltas */,
-       MTSB_BSDF_CONDUCTOR = 5  /* smooth: conductor.cpp, one delta reflection lobe */ };
+       MTSB_BSDF_CONDUCTOR = 5  /* smooth: conductor.cpp, one delta reflection lobe */,
+       MTSB_BSDF_PLASTIC = 6    /* smooth: plastic.cpp, delta reflection over a diffuse base */ };
 enum { MTSB_DISTR_BECKMANN = 0, MTSB_DISTR_GGX = 1 };           /* microfacet.h:48-57 */
-enum { MTSB_MAT_TWOSIDED = 1u, MTSB_MAT_SAMPLE_VISIBLE = 2u };
+enum { MTSB_MAT_TWOSIDED = 1u, MTSB_MAT_SAMPLE_VISIBLE = 2u, MTSB_MAT_NONLINEAR = 4u /* plastic `nonlinear` */ };
 
 typedef struct MtsbMaterial {
     uint32_t type;            /* MTSB_BSDF_*                                          */
@@ -67,12 +68,14 @@ typedef struct MtsbMaterial {
     int32_t  back;            /* twosided: material used when wi.z<0 (twosided.cpp:111-121); -1 = same */
     float    alpha_u, alpha_v;/* already clamped to >= 1e-4 (microfacet.h:135-136)     */
     float    eta;             /* roughdielectric: intIOR/extIOR (roughdielectric.cpp:199) */
-    float    _pad0;
-    float    reflectance[3];  /* diffuse `reflectance` / `specularReflectance`        */
-    float    transmittance[3];/* roughdielectric `specularTransmittance`              */
+    float    fdr_int;         /* plastic: fresnelDiffuseReflectance(1/eta) (plastic.cpp:196) */
+    float    reflectance[3];  /* diffuse `reflectance` / `specularReflectance`; plastic: `diffuseReflectance` */
+    float    transmittance[3];/* (rough)dielectric `specularTransmittance`; plastic: `specularReflectance`   */
     float    cond_eta[3];     /* roughconductor eta/extEta (roughconductor.cpp:189)   */
     float    cond_k[3];       /* roughconductor k/extEta                              */
-} MtsbMaterial;              /* 80 bytes */
+    float    spec_weight;     /* plastic: m_specularSamplingWeight (plastic.cpp:199-204) */
+    float    _pad1[3];
+} MtsbMaterial;              /* 96 bytes */
 
 /* ---- shapes: every shape is a triangle mesh (createTriMesh'd on the host) */
 typedef struct MtsbShape {

@@ -8,12 +8,12 @@ import ctypes as C
 
 import numpy as np
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 OK, ERR_INVALID, ERR_NO_DEVICE, ERR_CUDA, ERR_CANCELLED, ERR_IO, ERR_PARSE = range(7)
-BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_ROUGHDIELECTRIC, BSDF_NULL, BSDF_DIELECTRIC, BSDF_CONDUCTOR = range(6)
+BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_ROUGHDIELECTRIC, BSDF_NULL, BSDF_DIELECTRIC, BSDF_CONDUCTOR, BSDF_PLASTIC = range(7)
 DISTR_BECKMANN, DISTR_GGX = 0, 1
-MAT_TWOSIDED, MAT_SAMPLE_VISIBLE = 1, 2
+MAT_TWOSIDED, MAT_SAMPLE_VISIBLE, MAT_NONLINEAR = 1, 2, 4
 EMITTER_AREA, EMITTER_POINT, EMITTER_CONSTANT = 0, 1, 2
 RFILTER_GAUSSIAN, RFILTER_BOX = 0, 1
 TRACE_CLOSEST, TRACE_ANY = 0, 1
@@ -23,9 +23,9 @@ RENDER_KEEP_FILM = 1
 
 class Material(C.Structure):
     _fields_ = [("type", C.c_uint32), ("flags", C.c_uint32), ("distribution", C.c_uint32), ("back", C.c_int32),
-                ("alpha_u", C.c_float), ("alpha_v", C.c_float), ("eta", C.c_float), ("_pad0", C.c_float),
+                ("alpha_u", C.c_float), ("alpha_v", C.c_float), ("eta", C.c_float), ("fdr_int", C.c_float),
                 ("reflectance", C.c_float * 3), ("transmittance", C.c_float * 3),
-                ("cond_eta", C.c_float * 3), ("cond_k", C.c_float * 3)]
+                ("cond_eta", C.c_float * 3), ("cond_k", C.c_float * 3), ("spec_weight", C.c_float), ("_pad1", C.c_float * 3)]
 
 
 class Shape(C.Structure):
@@ -93,7 +93,7 @@ DIRECT_RESULT_DTYPE = np.dtype([("value", np.float32, 3), ("pdf", np.float32), (
 assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 16
 assert BSDF_QUERY_DTYPE.itemsize == 36 and BSDF_RESULT_DTYPE.itemsize == 48
 assert DIRECT_QUERY_DTYPE.itemsize == 32 and DIRECT_RESULT_DTYPE.itemsize == 64
-assert C.sizeof(Material) == 80 and C.sizeof(Shape) == 32 and C.sizeof(Emitter) == 48
+assert C.sizeof(Material) == 96 and C.sizeof(Shape) == 32 and C.sizeof(Emitter) == 48
 
 
 def ptr(arr, ctype):

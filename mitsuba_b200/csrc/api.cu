@@ -180,7 +180,7 @@ static int validate(const MtsbSceneDesc *d) {
     if (tri_sum != d->n_tris) { set_error("shape triangle counts do not add up to n_tris"); return MTSB_ERR_INVALID; }
     for (uint32_t i = 0; i < d->n_materials; ++i) {
         const MtsbMaterial &m = d->materials[i];
-        if (m.type > MTSB_BSDF_CONDUCTOR || m.distribution > MTSB_DISTR_GGX || m.back >= (int32_t) d->n_materials) { set_error("bad material record"); return MTSB_ERR_INVALID; }
+        if (m.type > MTSB_BSDF_PLASTIC || m.distribution > MTSB_DISTR_GGX || m.back >= (int32_t) d->n_materials) { set_error("bad material record"); return MTSB_ERR_INVALID; }
     }
     int n_env = 0;
     for (uint32_t i = 0; i < d->n_emitters; ++i) {

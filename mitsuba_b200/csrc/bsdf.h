@@ -463,6 +463,55 @@ MTSB_HD bool conductor_sample(const MtsbMaterial &m, V3 wi, BsdfSample &s) {
     return true;
 }
 
+// ---- SmoothPlastic (src/bsdfs/plastic.cpp:245-440) -----------------------------------------------
+// Dirac reflection lobe (specularReflectance in `transmittance`) over a diffuse base (diffuseReflectance in
+// `reflectance`).  Under the solid-angle measure eval()/pdf() see only the diffuse component.
+MTSB_HD float plastic_prob_specular(const MtsbMaterial &m, float Fi) {                          // :288-291
+    return (Fi * m.spec_weight) / (Fi * m.spec_weight + (1 - Fi) * (1 - m.spec_weight));
+}
+MTSB_HD V3 plastic_diffuse_term(const MtsbMaterial &m) {                                        // :270-275
+    V3 diff = ld3(m.reflectance);
+    if (m.flags & MTSB_MAT_NONLINEAR) diff = diff / (V3(1.0f) - diff * m.fdr_int);
+    else diff = diff / (1 - m.fdr_int);
+    return diff;
+}
+MTSB_HD V3 plastic_eval(const MtsbMaterial &m, V3 wi, V3 wo) {                                  // :245-280
+    if (cosTheta(wo) <= 0 || cosTheta(wi) <= 0) return V3(0.0f);
+    float t;
+    const float Fi = fresnelDielectricExt(cosTheta(wi), t, m.eta);
+    const float Fo = fresnelDielectricExt(cosTheta(wo), t, m.eta);
+    const float invEta2 = 1 / (m.eta * m.eta);
+    return plastic_diffuse_term(m) * (squareToCosineHemispherePdf(wo) * invEta2 * (1 - Fi) * (1 - Fo));
+}
+MTSB_HD float plastic_pdf(const MtsbMaterial &m, V3 wi, V3 wo) {                                // :282-310
+    if (cosTheta(wo) <= 0 || cosTheta(wi) <= 0) return 0.0f;
+    float t;
+    const float Fi = fresnelDielectricExt(cosTheta(wi), t, m.eta);
+    return squareToCosineHemispherePdf(wo) * (1 - plastic_prob_specular(m, Fi));
+}
+MTSB_HD bool plastic_sample(const MtsbMaterial &m, V3 wi, P2 u, BsdfSample &s) {                // :373-412
+    if (cosTheta(wi) <= 0) return false;
+    float t;
+    const float Fi = fresnelDielectricExt(cosTheta(wi), t, m.eta);
+    s.eta = 1.0f;
+    const float probSpecular = plastic_prob_specular(m, Fi);
+    if (u.x < probSpecular) {
+        s.delta = true;
+        s.wo = V3(-wi.x, -wi.y, wi.z);
+        s.pdf = probSpecular;
+        s.weight = ld3(m.transmittance) * Fi / probSpecular;
+    } else {
+        s.delta = false;
+        P2 v; v.x = (u.x - probSpecular) / (1 - probSpecular); v.y = u.y;
+        s.wo = squareToCosineHemisphere(v);
+        const float Fo = fresnelDielectricExt(cosTheta(s.wo), t, m.eta);
+        const float invEta2 = 1 / (m.eta * m.eta);
+        s.pdf = (1 - probSpecular) * squareToCosineHemispherePdf(s.wo);
+        s.weight = plastic_diffuse_term(m) * (invEta2 * (1 - Fi) * (1 - Fo) / (1 - probSpecular));
+    }
+    return true;
+}
+
 // ---- dispatch + TwoSided ---------------------------------------------------------------------
 // The per-material shading kernels call the *_one functions with a compile-time TYPE; the
 // generic switch is used by the query entry point (mtsb_bsdf_query).
@@ -471,6 +520,7 @@ MTSB_HD V3 bsdf_eval_one(const MtsbMaterial &m, V3 wi, V3 wo) {
         case MTSB_BSDF_DIFFUSE: return diffuse_eval(m, wi, wo);
         case MTSB_BSDF_ROUGHCONDUCTOR: return roughconductor_eval(m, wi, wo);
         case MTSB_BSDF_ROUGHDIELECTRIC: return roughdielectric_eval(m, wi, wo);
+        case MTSB_BSDF_PLASTIC: return plastic_eval(m, wi, wo);
         default: return V3(0.0f);
     }
 }
@@ -479,6 +529,7 @@ MTSB_HD float bsdf_pdf_one(const MtsbMaterial &m, V3 wi, V3 wo) {
         case MTSB_BSDF_DIFFUSE: return diffuse_pdf(wi, wo);
         case MTSB_BSDF_ROUGHCONDUCTOR: return roughconductor_pdf(m, wi, wo);
         case MTSB_BSDF_ROUGHDIELECTRIC: return roughdielectric_pdf(m, wi, wo);
+        case MTSB_BSDF_PLASTIC: return plastic_pdf(m, wi, wo);
         default: return 0.0f;
     }
 }
@@ -489,6 +540,7 @@ MTSB_HD bool bsdf_sample_one(const MtsbMaterial &m, V3 wi, P2 u, float u1, BsdfS
         case MTSB_BSDF_ROUGHDIELECTRIC: return roughdielectric_sample(m, wi, u, u1, s);
         case MTSB_BSDF_DIELECTRIC: return dielectric_sample(m, wi, u, s);
         case MTSB_BSDF_CONDUCTOR: return conductor_sample(m, wi, s);
+        case MTSB_BSDF_PLASTIC: return plastic_sample(m, wi, u, s);
         default: return false;
     }
 }
@@ -528,7 +580,7 @@ MTSB_HD int bsdf_effective_material(const MtsbMaterial *mats, int id, float wi_z
 // BSDF::getType() bits that path.cpp reads: ESmooth (path.cpp:177); ETransmission|EBackSide (records.inl:175-179)
 // (a twosided wrapper reports the union of both nested types, twosided.cpp:72-99)
 MTSB_HD bool bsdf_type_is_smooth(uint32_t t) {
-    return t == MTSB_BSDF_DIFFUSE || t == MTSB_BSDF_ROUGHCONDUCTOR || t == MTSB_BSDF_ROUGHDIELECTRIC;
+    return t == MTSB_BSDF_DIFFUSE || t == MTSB_BSDF_ROUGHCONDUCTOR || t == MTSB_BSDF_ROUGHDIELECTRIC || t == MTSB_BSDF_PLASTIC;
 }
 MTSB_HD bool bsdf_type_is_delta(uint32_t t) { return t == MTSB_BSDF_DIELECTRIC || t == MTSB_BSDF_CONDUCTOR; }
 MTSB_HD bool bsdf_is_smooth(const MtsbMaterial *mats, const MtsbMaterial &m) {

@@ -82,6 +82,7 @@ MTSB_HD V3 operator*(float s, V3 a) { return V3(a.x * s, a.y * s, a.z * s); }
 MTSB_HD V3 operator*(V3 a, V3 b) { return V3(a.x * b.x, a.y * b.y, a.z * b.z); }
 // TVector3::operator/(Float) multiplies by the reciprocal (include/mitsuba/core/vector.h)
 MTSB_HD V3 operator/(V3 a, float s) { float r = fdiv(1.0f, s); return V3(a.x * r, a.y * r, a.z * r); }
+MTSB_HD V3 operator/(V3 a, V3 b) { return V3(fdiv(a.x, b.x), fdiv(a.y, b.y), fdiv(a.z, b.z)); }
 MTSB_HD V3 &operator+=(V3 &a, V3 b) { a = a + b; return a; }
 MTSB_HD V3 &operator*=(V3 &a, V3 b) { a = a * b; return a; }
 MTSB_HD V3 &operator*=(V3 &a, float s) { a = a * s; return a; }

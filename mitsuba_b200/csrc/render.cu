@@ -122,7 +122,7 @@ __global__ void k_pass_end(PathBuffers pb) { Counters *c = pb.ctr; c->shadow += 
 // run at ~1 G/s on this part and were a visible share of the stage.
 __host__ __device__ inline int queue_of_type(uint32_t t) {
     return t == MTSB_BSDF_DIFFUSE ? Q_DIFFUSE : t == MTSB_BSDF_ROUGHCONDUCTOR ? Q_CONDUCTOR : t == MTSB_BSDF_ROUGHDIELECTRIC ? Q_DIELECTRIC
-         : (t == MTSB_BSDF_DIELECTRIC || t == MTSB_BSDF_CONDUCTOR) ? Q_DELTA : Q_NULL;
+         : (t == MTSB_BSDF_DIELECTRIC || t == MTSB_BSDF_CONDUCTOR) ? Q_DELTA : t == MTSB_BSDF_PLASTIC ? Q_GENERIC : Q_NULL;
 }
 __host__ __device__ inline int queue_of_material(const MtsbMaterial *mats, int mat) {
     if (mat < 0) return Q_NULL;

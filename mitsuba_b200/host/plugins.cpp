@@ -107,6 +107,26 @@ static Vec3 conserveEnergy(const std::string &plugin, const char *name, Vec3 r, 
     return r;
 }
 
+// fresnelDiffuseReflectance(eta, false) (util.cpp:814-860): integral over xi in [0,1] of fresnelDielectricExt(sqrt(xi), eta).
+// The reference integrates adaptively in single precision (relative tolerance 1e-5); a double-precision midpoint rule
+// here, equal to that tolerance.
+static float fresnelDiffuseReflectance(float etaF) {
+    const double eta = etaF;
+    if (eta == 1.0) return 0.0f;
+    const int n = 65536;
+    double sum = 0;
+    for (int i = 0; i < n; ++i) {
+        const double xi = (i + 0.5) / n, cosI = std::sqrt(xi), scale = 1.0 / eta;
+        const double cosTSqr = 1.0 - (1.0 - cosI * cosI) * (scale * scale);
+        if (cosTSqr <= 0.0) { sum += 1.0; continue; }
+        const double cosT = std::sqrt(cosTSqr);
+        const double Rs = (cosI - eta * cosT) / (cosI + eta * cosT), Rp = (eta * cosI - cosT) / (eta * cosI + cosT);
+        sum += 0.5 * (Rs * Rs + Rp * Rp);
+    }
+    return (float) (sum / n);
+}
+static float luminance(const Vec3 &c) { return c.x * 0.212671f + c.y * 0.715160f + c.z * 0.072169f; }
+
 Bsdf::Bsdf(const Properties &p) : ConfigurableObject(p) {
     std::memset(&m_rec, 0, sizeof(m_rec));
     m_rec.back = -1;
@@ -156,10 +176,24 @@ Bsdf::Bsdf(const Properties &p) : ConfigurableObject(p) {
         m_rec.type = MTSB_BSDF_CONDUCTOR;
         set3(m_rec.reflectance, conserveEnergy(type, "specularReflectance", p.getSpectrum("specularReflectance", Vec3{1, 1, 1}), 1.0f));
         conductorProps(p, m_rec, type);
+    } else if (type == "plastic") {
+        // plastic.cpp:141-165, 185-206
+        m_rec.type = MTSB_BSDF_PLASTIC;
+        float in = lookupIOR(p, "intIOR", "polypropylene"), ex = lookupIOR(p, "extIOR", "air");
+        if (in < 0 || ex < 0) error("The interior and exterior indices of refraction must be positive!");
+        m_rec.eta = in / ex;
+        Vec3 sp = conserveEnergy(type, "specularReflectance", p.getSpectrum("specularReflectance", Vec3{1, 1, 1}), 1.0f);
+        Vec3 df = conserveEnergy(type, "diffuseReflectance", p.getSpectrum("diffuseReflectance", Vec3{0.5f, 0.5f, 0.5f}), 1.0f);
+        set3(m_rec.reflectance, df);
+        set3(m_rec.transmittance, sp);
+        if (p.getBoolean("nonlinear", false)) m_rec.flags |= MTSB_MAT_NONLINEAR;
+        m_rec.fdr_int = fresnelDiffuseReflectance(1 / m_rec.eta);
+        const float dAvg = luminance(df), sAvg = luminance(sp);
+        m_rec.spec_weight = sAvg / (dAvg + sAvg);
     } else if (type == "twosided") {
         m_twosided = true;
     } else {
-        error("Plugin \"" + type + "\" not found -- the B200 path implements the BSDFs diffuse, dielectric, conductor, roughconductor, roughdielectric and twosided.");
+        error("Plugin \"" + type + "\" not found -- the B200 path implements the BSDFs diffuse, dielectric, conductor, plastic, roughconductor, roughdielectric and twosided.");
     }
 }
 

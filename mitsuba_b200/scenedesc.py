@@ -138,6 +138,51 @@ def conductor(eta, k, specular_reflectance=1.0, ext_eta=1.000277, twosided=False
     return m
 
 
+def fresnel_diffuse_reflectance(eta, n=65536):
+    """fresnelDiffuseReflectance(eta, false) (src/libcore/util.cpp:814-860): the integral over xi in [0,1] of
+    fresnelDielectricExt(sqrt(xi), eta).  The reference integrates adaptively in single precision to a relative
+    tolerance of 1e-5; this is a double-precision midpoint rule, so the two agree to that tolerance."""
+    eta = float(eta)
+    xi = (np.arange(n, dtype=np.float64) + 0.5) / n
+    cos_i = np.sqrt(xi)
+    if eta == 1.0:
+        return np.float32(0.0)
+    scale = 1.0 / eta                                         # cos_i > 0
+    cos_t_sqr = 1.0 - (1.0 - cos_i * cos_i) * (scale * scale)
+    tir = cos_t_sqr <= 0.0
+    cos_t = np.sqrt(np.where(tir, 0.0, cos_t_sqr))
+    rs = (cos_i - eta * cos_t) / (cos_i + eta * cos_t)
+    rp = (eta * cos_i - cos_t) / (eta * cos_i + cos_t)
+    f = np.where(tir, 1.0, 0.5 * (rs * rs + rp * rp))
+    return np.float32(f.sum() / n)
+
+
+def _luminance(rgb):
+    r = np.asarray(rgb, dtype=np.float32)
+    return np.float32(np.float32(r[0] * np.float32(0.212671) + r[1] * np.float32(0.715160)) + r[2] * np.float32(0.072169))
+
+
+def plastic(int_ior=1.49, ext_ior=1.000277, diffuse_reflectance=0.5, specular_reflectance=1.0, nonlinear=False,
+            twosided=False):
+    """Smooth `plastic` record (src/bsdfs/plastic.cpp:141-165, 185-206): polypropylene / air by default."""
+    m = abi.Material()
+    m.type = abi.BSDF_PLASTIC
+    m.flags = (abi.MAT_TWOSIDED if twosided else 0) | (abi.MAT_NONLINEAR if nonlinear else 0)
+    m.back = -1
+    m.alpha_u = m.alpha_v = 0.1
+    eta = np.float32(int_ior) / np.float32(ext_ior)
+    m.eta = float(eta)
+    d, sp = _conserve(diffuse_reflectance), _conserve(specular_reflectance)
+    m.reflectance = _f3(d)
+    m.transmittance = _f3(sp)
+    m.cond_eta = _f3(0.0)
+    m.cond_k = _f3(1.0)
+    m.fdr_int = float(fresnel_diffuse_reflectance(np.float32(1.0) / eta))
+    d_avg, s_avg = _luminance(d), _luminance(sp)
+    m.spec_weight = float(s_avg / np.float32(d_avg + s_avg))
+    return m
+
+
 def look_at(origin, target, up):
     """Transform::lookAt (src/libcore/transform.cpp:191-214): row-major camera-to-world."""
     p = np.asarray(origin, dtype=np.float64)

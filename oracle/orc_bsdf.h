@@ -351,12 +351,60 @@ inline bool conductor_sample(const MtsbMaterial &m, V3 wi, P2, BsdfSample &s) { 
     return true;
 }
 
+// ---- SmoothPlastic: src/bsdfs/plastic.cpp:245-440 ---------------------------------------
+// A Dirac reflection lobe (specularReflectance, stored in `transmittance`) over a diffuse base
+// (diffuseReflectance, stored in `reflectance`).  Under the solid-angle measure eval()/pdf() see only
+// the diffuse component (:250-252, :300-302).
+inline float plastic_prob_specular(const MtsbMaterial &m, float Fi) {                  // :288-291
+    return (Fi * m.spec_weight) / (Fi * m.spec_weight + (1 - Fi) * (1 - m.spec_weight));
+}
+inline V3 plastic_diffuse_term(const MtsbMaterial &m) {                                  // :270-275
+    V3 diff = rgb(m.reflectance);
+    if (m.flags & MTSB_MAT_NONLINEAR) diff = diff / (V3(1.0f) - diff * m.fdr_int);
+    else diff = diff / (1 - m.fdr_int);
+    return diff;
+}
+inline V3 plastic_eval(const MtsbMaterial &m, V3 wi, V3 wo) {                            // :245-280
+    if (cosTheta(wo) <= 0 || cosTheta(wi) <= 0) return V3(0.0f);
+    float Fi = fresnelDielectricExt(cosTheta(wi), m.eta);
+    float Fo = fresnelDielectricExt(cosTheta(wo), m.eta);
+    const float invEta2 = 1 / (m.eta * m.eta);
+    return plastic_diffuse_term(m) * (squareToCosineHemispherePdf(wo) * invEta2 * (1 - Fi) * (1 - Fo));
+}
+inline float plastic_pdf(const MtsbMaterial &m, V3 wi, V3 wo) {                          // :282-310
+    if (cosTheta(wo) <= 0 || cosTheta(wi) <= 0) return 0.0f;
+    float Fi = fresnelDielectricExt(cosTheta(wi), m.eta);
+    float probSpecular = plastic_prob_specular(m, Fi);
+    return squareToCosineHemispherePdf(wo) * (1 - probSpecular);
+}
+inline bool plastic_sample(const MtsbMaterial &m, V3 wi, P2 u, BsdfSample &s) {          // :373-412
+    if (cosTheta(wi) <= 0) return false;
+    float Fi = fresnelDielectricExt(cosTheta(wi), m.eta);
+    s.eta = 1.0f;
+    float probSpecular = plastic_prob_specular(m, Fi);
+    if (u.x < probSpecular) {
+        s.delta = true;
+        s.wo = V3(-wi.x, -wi.y, wi.z);
+        s.pdf = probSpecular;
+        s.weight = rgb(m.transmittance) * Fi / probSpecular;
+    } else {
+        s.delta = false;
+        s.wo = squareToCosineHemisphere(P2{(u.x - probSpecular) / (1 - probSpecular), u.y});
+        float Fo = fresnelDielectricExt(cosTheta(s.wo), m.eta);
+        const float invEta2 = 1 / (m.eta * m.eta);
+        s.pdf = (1 - probSpecular) * squareToCosineHemispherePdf(s.wo);
+        s.weight = plastic_diffuse_term(m) * (invEta2 * (1 - Fi) * (1 - Fo) / (1 - probSpecular));
+    }
+    return true;
+}
+
 // ---- dispatch incl. TwoSided (src/bsdfs/twosided.cpp:108-184) -------------------
 inline V3 bsdf_eval_one(const MtsbMaterial &m, V3 wi, V3 wo) {
     switch (m.type) {
         case MTSB_BSDF_DIFFUSE: return diffuse_eval(m, wi, wo);
         case MTSB_BSDF_ROUGHCONDUCTOR: return roughconductor_eval(m, wi, wo);
         case MTSB_BSDF_ROUGHDIELECTRIC: return roughdielectric_eval(m, wi, wo);
+        case MTSB_BSDF_PLASTIC: return plastic_eval(m, wi, wo);
         default: return V3(0.0f);
     }
 }
@@ -365,6 +413,7 @@ inline float bsdf_pdf_one(const MtsbMaterial &m, V3 wi, V3 wo) {
         case MTSB_BSDF_DIFFUSE: return diffuse_pdf(m, wi, wo);
         case MTSB_BSDF_ROUGHCONDUCTOR: return roughconductor_pdf(m, wi, wo);
         case MTSB_BSDF_ROUGHDIELECTRIC: return roughdielectric_pdf(m, wi, wo);
+        case MTSB_BSDF_PLASTIC: return plastic_pdf(m, wi, wo);
         default: return 0.0f;
     }
 }
@@ -375,6 +424,7 @@ inline bool bsdf_sample_one(const MtsbMaterial &m, V3 wi, P2 u, float u1, BsdfSa
         case MTSB_BSDF_ROUGHDIELECTRIC: return roughdielectric_sample(m, wi, u, u1, s);
         case MTSB_BSDF_DIELECTRIC: return dielectric_sample(m, wi, u, s);
         case MTSB_BSDF_CONDUCTOR: return conductor_sample(m, wi, u, s);
+        case MTSB_BSDF_PLASTIC: return plastic_sample(m, wi, u, s);
         default: return false;
     }
 }
@@ -412,7 +462,7 @@ inline bool bsdf_sample(const MtsbMaterial *mats, int id, V3 wi, P2 u, float u1,
 // ETransmission|EBackSide (records.inl:175-179).
 // A twosided wrapper reports the union of both nested types (twosided.cpp:72-99).
 inline bool bsdf_type_is_smooth(uint32_t t) {
-    return t == MTSB_BSDF_DIFFUSE || t == MTSB_BSDF_ROUGHCONDUCTOR || t == MTSB_BSDF_ROUGHDIELECTRIC;
+    return t == MTSB_BSDF_DIFFUSE || t == MTSB_BSDF_ROUGHCONDUCTOR || t == MTSB_BSDF_ROUGHDIELECTRIC || t == MTSB_BSDF_PLASTIC;
 }
 inline bool bsdf_is_smooth(const MtsbMaterial *mats, const MtsbMaterial &m) {
     if (bsdf_type_is_smooth(m.type)) return true;

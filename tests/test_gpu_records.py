@@ -3,7 +3,7 @@ import numpy as np
 import pytest
 
 from mitsuba_b200 import abi, scenes
-from mitsuba_b200.scenedesc import SceneBuilder, conductor, dielectric, diffuse, look_at, roughconductor, roughdielectric
+from mitsuba_b200.scenedesc import SceneBuilder, conductor, dielectric, diffuse, look_at, plastic, roughconductor, roughdielectric
 from tests import util
 
 pytestmark = pytest.mark.gpu
@@ -32,6 +32,9 @@ def material_scene():
     mats["mirror"] = b.add_material(conductor(eta, k, specular_reflectance=[1.0, 0.5, 0.25]))
     mats["mirror2s"] = b.add_material(conductor(0.0, 1.0, twosided=True))
     mats["mirror_over_diffuse"] = b.add_twosided(conductor(eta, k), diffuse([0.2, 0.4, 0.6]))
+    mats["plastic"] = b.add_material(plastic(1.49, 1.000277, [0.6, 0.3, 0.1], [1.0, 0.9, 0.8]))
+    mats["plastic_nonlinear2s"] = b.add_material(plastic(1.9, 1.33, [0.1, 0.2, 0.9], 0.5, nonlinear=True, twosided=True))
+    mats["plastic_over_mirror"] = b.add_twosided(plastic(), conductor(eta, k))
     mats["mixed2s"] = b.add_twosided(roughconductor(eta, k, alpha=0.2, distribution="ggx"), diffuse([0.2, 0.4, 0.6]))
     b.add_quad((-1, 0, -1), (-1, 0, 1), (1, 0, 1), (1, 0, -1), mats["diffuse"])
     b.add_quad((-0.3, 2, -0.3), (0.3, 2, -0.3), (0.3, 2, 0.3), (-0.3, 2, 0.3), mats["diffuse"], area_radiance=[5, 4, 3])

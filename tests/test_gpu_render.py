@@ -118,6 +118,17 @@ def test_same_stream_delta_lobes_in_twosided_wrappers_and_env(gpu_lib, oracle_mo
     check_same_stream(gpu_lib, oracle_mod, b, 4, "cbox twosided delta + env")
 
 
+def test_same_stream_plastic_blocks(gpu_lib, oracle_mod):
+    """plastic: a Dirac lobe over a diffuse base -- emitter sampling sees the diffuse part only, a sampled specular
+    bounce reaches emitters with MIS weight 1."""
+    from mitsuba_b200.scenedesc import conductor, plastic
+    eta, k = scenes.METALS["Au"]
+    b = scenes.cbox(width=64, height=64, spp=4, max_depth=6,
+                    short_material=plastic(1.49, 1.000277, [0.1, 0.27, 0.36], 1.0),
+                    tall_material=(plastic(1.9, 1.0, [0.6, 0.3, 0.1], 0.7, nonlinear=True), conductor(eta, k)))
+    check_same_stream(gpu_lib, oracle_mod, b, 4, "cbox plastic")
+
+
 def test_glass_and_mirror_blocks_independent_streams(gpu_lib, oracle_mod):
     b = _glass_mirror_cbox(width=48, height=48, spp=32, max_depth=8)
     check_render(gpu_lib, oracle_mod, b, 32, 256, "cbox glass+mirror")

@@ -226,7 +226,22 @@ def test_smooth_dielectric_and_conductor_records():
     with pytest.raises(MtsbError, match="specify 'eta' and 'k'"):
         load('<shape type="rectangle"><bsdf type="conductor"><string name="material" value="W"/></bsdf></shape>')
     with pytest.raises(MtsbError, match="not found"):
-        load('<shape type="rectangle"><bsdf type="plastic"/></shape>')
+        load('<shape type="rectangle"><bsdf type="phong"/></shape>')
+
+
+def test_plastic_records():
+    """plastic.cpp:141-165, 185-206: IOR defaults, energy clamp, fdrInt, specular sampling weight, nonlinear."""
+    hs = load('<shape type="rectangle"><bsdf type="plastic"/></shape>'
+              '<shape type="rectangle"><bsdf type="twosided"><bsdf type="plastic"><float name="intIOR" value="1.9"/><string name="extIOR" value="water"/>'
+              '<rgb name="diffuseReflectance" value="0.1,0.2,0.9"/><rgb name="specularReflectance" value="0.5"/>'
+              '<boolean name="nonlinear" value="true"/></bsdf></bsdf></shape>')
+    m = hs.materials()
+    for got, want in ((m[0], scenedesc.plastic()),
+                      (m[1], scenedesc.plastic(1.9, 1.3330, [0.1, 0.2, 0.9], 0.5, nonlinear=True, twosided=True))):
+        assert got.fdr_int == pytest.approx(want.fdr_int, rel=1e-6) and 0.3 < got.fdr_int < 0.7
+        got.fdr_int = want.fdr_int                      # two double-precision sums in different order: equal to rounding
+        assert bytes(got) == bytes(want)
+    assert m[1].flags == abi.MAT_TWOSIDED | abi.MAT_NONLINEAR and m[0].eta == np.float32(np.float32(1.49) / np.float32(1.000277))
 
 
 def test_twosided_and_shared_references():

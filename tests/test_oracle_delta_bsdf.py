@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 from mitsuba_b200 import abi
-from mitsuba_b200.scenedesc import SceneBuilder, conductor, dielectric, diffuse, look_at
+from mitsuba_b200.scenedesc import SceneBuilder, conductor, dielectric, diffuse, fresnel_diffuse_reflectance, look_at, plastic
 
 
 def _scene():
@@ -138,3 +138,86 @@ def test_delta_materials_in_the_li_loop(oracle_mod):
     img = orc.film_develop()
     assert np.allclose(img, [2, 3, 4], rtol=1e-5)
     assert st.shadow_rays == 0 and st.closest_rays == 2 * st.samples
+
+
+def test_fresnel_diffuse_reflectance_known_values():
+    # util.cpp:814-853 quotes fits with <= 0.1 % error for 1 <= eta <= 2: d'Eon & Irving (eta > 1), Egan & Hilgeman (eta < 1)
+    for eta in (1.1, 1.33, 1.49, 1.5, 2.0):
+        inv = 1.0 / eta
+        fit = 0.919317 - 3.4793 * inv + 6.75335 * inv ** 2 - 7.80989 * inv ** 3 + 4.98554 * inv ** 4 - 1.36881 * inv ** 5
+        assert float(fresnel_diffuse_reflectance(eta)) == pytest.approx(fit, rel=2e-3)
+        fit_int = -1.4399 * inv * inv + 0.7099 * inv + 0.6681 + 0.0636 / inv
+        assert float(fresnel_diffuse_reflectance(inv)) == pytest.approx(fit_int, rel=7e-3)
+        # the two are tied by 1 - Fdr(1/eta) = (1 - Fdr(eta)) / eta^2 (reciprocity of the interface)
+        assert 1 - float(fresnel_diffuse_reflectance(inv)) == pytest.approx((1 - float(fresnel_diffuse_reflectance(eta))) / eta ** 2, rel=1e-4)
+    assert float(fresnel_diffuse_reflectance(1.0)) == 0.0
+
+
+def test_plastic_lobes_energy_and_sampling(oracle_mod):
+    b = SceneBuilder()
+    mats = {
+        "lin": b.add_material(plastic(1.5, 1.0, [0.6, 0.3, 0.1], [1.0, 0.9, 0.8])),
+        "nonlin": b.add_material(plastic(1.5, 1.0, [0.6, 0.3, 0.1], 1.0, nonlinear=True)),
+    }
+    b.add_quad((-1, 0, -1), (-1, 0, 1), (1, 0, 1), (1, 0, -1), mats["lin"])
+    b.add_quad((-0.3, 2, -0.3), (0.3, 2, -0.3), (0.3, 2, 0.3), (-0.3, 2, 0.3), mats["lin"], area_radiance=[5, 4, 3])
+    b.set_sensor(look_at([0, 1, -4], [0, 0.5, 0], [0, 1, 0]), 40.0, 16, 16)
+    orc = oracle_mod.Oracle(b)
+    m = b.materials[mats["lin"]]
+    assert m.fdr_int == pytest.approx(0.59635, rel=1e-4)
+    lum = lambda c: 0.212671 * c[0] + 0.715160 * c[1] + 0.072169 * c[2]
+    assert m.spec_weight == pytest.approx(lum([1.0, 0.9, 0.8]) / (lum([0.6, 0.3, 0.1]) + lum([1.0, 0.9, 0.8])), rel=1e-6)
+
+    n = 40000
+    wi = np.tile(np.array([[0.6, 0.0, 0.8]], np.float32), (n, 1))
+    rng = np.random.default_rng(4)
+    q = _q(wi, 0.0)
+    q["u"][:, :2] = rng.random((n, 2)).astype(np.float32)
+    wo = _dirs(n, 8, front=True)
+    q["wo"] = wo
+    r = orc.bsdf_query(mats["lin"], q)
+    F = 0.5 * (((0.8 - 1.5 * np.sqrt(1 - 0.36 / 2.25)) / (0.8 + 1.5 * np.sqrt(1 - 0.36 / 2.25))) ** 2 +
+               ((1.5 * 0.8 - np.sqrt(1 - 0.36 / 2.25)) / (1.5 * 0.8 + np.sqrt(1 - 0.36 / 2.25))) ** 2)
+    p_spec = F * m.spec_weight / (F * m.spec_weight + (1 - F) * (1 - m.spec_weight))
+    spec = q["u"][:, 0] < p_spec
+    assert spec.mean() == pytest.approx(p_spec, abs=0.01)
+    # delta lobe: mirror direction, pdf = probSpecular, weight = specularReflectance * F / probSpecular
+    assert np.array_equal(r["swo"][spec], wi[spec] * np.array([-1, -1, 1], np.float32))
+    assert np.allclose(r["spdf"][spec], p_spec, rtol=1e-5)
+    assert np.allclose(r["weight"][spec], np.array([1.0, 0.9, 0.8]) * F / p_spec, rtol=1e-5)
+    # diffuse lobe: cosine-distributed, pdf = (1 - probSpecular) cos / pi, and sample weight * pdf == eval
+    d = ~spec
+    assert np.all(r["swo"][d, 2] > 0)
+    assert np.allclose(r["spdf"][d], (1 - p_spec) * r["swo"][d, 2] / np.pi, rtol=1e-5)
+    q2 = q.copy()
+    q2["wo"] = r["swo"]
+    r2 = orc.bsdf_query(mats["lin"], q2)
+    assert np.allclose(r2["eval"][d], r["weight"][d] * r["spdf"][d, None], rtol=2e-5, atol=1e-8)
+    assert np.allclose(r2["pdf"][d], r["spdf"][d], rtol=1e-6)
+    # energy: delta albedo F * spec + Monte Carlo estimate of the diffuse albedo; never above one, and the diffuse part
+    # equals rho (1-Fi)/eta^2 * E[(1-Fo)] / (1 - fdrInt) with E over the cosine density = (1-FdrExt) ... checked numerically
+    albedo = (r["weight"] * 1.0).mean(0)          # E[weight] over the sampling density
+    assert np.all(albedo < 1.0) and np.all(albedo > np.array([1.0, 0.9, 0.8]) * F)
+    fdr_ext = float(fresnel_diffuse_reflectance(1.5))
+    expect_diffuse = np.array([0.6, 0.3, 0.1]) / (1 - m.fdr_int) * (1 - F) * (1 - fdr_ext) / 2.25
+    assert albedo - np.array([1.0, 0.9, 0.8]) * F == pytest.approx(expect_diffuse, rel=0.02)
+    # eval for arbitrary wo is the closed form of plastic.cpp:270-279
+    Fo = np.array([_fresnel(c, 1.5) for c in wo[:200, 2]])
+    want = (np.array([0.6, 0.3, 0.1]) / (1 - m.fdr_int))[None, :] * (wo[:200, 2] / np.pi / 2.25 * (1 - F) * (1 - Fo))[:, None]
+    assert np.allclose(r["eval"][:200], want, rtol=2e-5)
+    # nonlinear: diff / (1 - diff * fdrInt) per channel
+    rn = orc.bsdf_query(mats["nonlin"], q)
+    ratio = rn["eval"][:200] / r["eval"][:200]
+    assert np.allclose(ratio, ((1 - m.fdr_int) / (1 - np.array([0.6, 0.3, 0.1]) * m.fdr_int))[None, :], rtol=1e-5)
+    # back side: nothing
+    qb = _q(_dirs(100, 9, front=False), 0.5)
+    rb = orc.bsdf_query(mats["lin"], qb)
+    assert not rb["spdf"].any() and not rb["eval"].any() and not rb["pdf"].any()
+
+
+def _fresnel(cos_i, eta):
+    s2 = (1 - cos_i * cos_i) / eta ** 2
+    ct = np.sqrt(1 - s2)
+    rs = (cos_i - eta * ct) / (cos_i + eta * ct)
+    rp = (eta * cos_i - ct) / (eta * cos_i + ct)
+    return 0.5 * (rs * rs + rp * rp)
