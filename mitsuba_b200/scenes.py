@@ -15,11 +15,12 @@ from .scenedesc import SceneBuilder, diffuse, look_at, roughconductor, roughdiel
 
 SEED = 1004
 
-# RGB eta/k of three metals (given explicitly so that no SPD lookup is needed; cf. data/ior/*.spd)
+# RGB eta/k of three metals: what the reference's spectrum -> RGB conversion gives for data/ior/{Cu,Au,Al}.*.spd
+# (mitsuba_b200/host/ior_rgb.inc, tools/make_ior_table.py); passed explicitly so that no SPD lookup is needed
 METALS = {
-    "Cu": ([0.200438, 0.924033, 1.102212], [3.912949, 2.452848, 2.142188]),
-    "Au": ([0.143119, 0.374957, 1.442479], [3.983160, 2.385721, 1.603215]),
-    "Al": ([1.657460, 0.880369, 0.521229], [9.223869, 6.269523, 4.837001]),
+    "Cu": ([0.208209336, 0.919432044, 1.10242665], [3.92252636, 2.45611167, 2.14157939]),
+    "Au": ([0.143171251, 0.377493262, 1.43917966], [3.98517585, 2.38457704, 1.60435247]),
+    "Al": ([1.6603291, 0.881592274, 0.521452069], [9.22673416, 6.27122402, 4.83799553]),
 }
 
 

@@ -7,6 +7,10 @@
 //   - MicrofacetDistribution                                 src/bsdfs/microfacet.h
 //   - warp::*, math::{erf,erfinv,hypot2}                     src/libcore/{warp,math}.cpp
 //   - AABB::rayIntersect                                     include/mitsuba/core/aabb.h:308-338
+//   - fresnelDielectricExt / fresnelConductorExact / fresnelDiffuseReflectance / reflect / refract
+//                                                            src/libcore/util.cpp:651-860 (+ quad.cpp)
+//   - InterpolatedSpectrum + Spectrum::fromContinuousSpectrum (SPD file -> RGB)
+//                                                            src/libcore/spectrum.cpp:172-191, 575-600
 // The CRTP `RefTree` below supplies what ShapeKDTree supplies (skdtree.h:205-337): primitive
 // count, boxes, clipped boxes and the two TriAccel `intersect` callbacks.
 // Built by oracle/Makefile into oracle/_ref/libmtsref.so when /root/reference is present.
@@ -17,6 +21,11 @@
 #include <mitsuba/core/timer.h>
 #include <mitsuba/render/triaccel.h>
 #include <mitsuba/render/sahkdtree3.h>
+#include <mitsuba/core/spectrum.h>
+#include <mitsuba/core/util.h>
+#include <mitsuba/core/random.h>
+#include <boost/filesystem.hpp>
+#include <mutex>
 #include "src/bsdfs/microfacet.h"
 #include "../include/mtsb200.h"
 #include <vector>
@@ -238,6 +247,33 @@ void ref_warp(int kind, const float *u2, float *out3) {
     else if (kind == 1) { Vector v = warp::squareToUniformSphere(u); out3[0] = v.x; out3[1] = v.y; out3[2] = v.z; }
     else if (kind == 2) { Point2 p = warp::squareToUniformTriangle(u); out3[0] = p.x; out3[1] = p.y; out3[2] = 0; }
     else { Point2 p = warp::squareToUniformDiskConcentric(u); out3[0] = p.x; out3[1] = p.y; out3[2] = 0; }
+}
+
+// ---- Fresnel terms (util.cpp) -------------------------------------------------------------
+float ref_fresnel_dielectric_ext(float cosThetaI, float eta, float *cosThetaT) {
+    Float t; Float F = fresnelDielectricExt(cosThetaI, t, eta); *cosThetaT = t; return F;
+}
+void ref_fresnel_conductor_exact(float cosThetaI, const float *eta3, const float *k3, float *out3) {
+    Spectrum eta, k; eta.fromLinearRGB(eta3[0], eta3[1], eta3[2]); k.fromLinearRGB(k3[0], k3[1], k3[2]);
+    Spectrum r = fresnelConductorExact(cosThetaI, eta, k);
+    r.toLinearRGB(out3[0], out3[1], out3[2]);
+}
+float ref_fresnel_diffuse_reflectance(float eta, int fast) { return fresnelDiffuseReflectance(eta, fast != 0); }
+void ref_refract(const float *wi3, const float *n3, float eta, float *out3) {
+    Vector r = refract(Vector(wi3[0], wi3[1], wi3[2]), Normal(n3[0], n3[1], n3[2]), eta);
+    out3[0] = r.x; out3[1] = r.y; out3[2] = r.z;
+}
+
+// ---- SPD file -> RGB, the conversion behind `material=` names (roughconductor.cpp:174-185) ----
+int ref_spd_to_rgb(const char *path, float *out3) {
+    static std::once_flag once;
+    std::call_once(once, []() { Spectrum::staticInitialization(); });
+    try {
+        InterpolatedSpectrum spd((fs::path(path)));
+        Spectrum s; s.fromContinuousSpectrum(spd);
+        s.toLinearRGB(out3[0], out3[1], out3[2]);
+        return 0;
+    } catch (const std::exception &e) { return 1; }
 }
 
 }  // extern "C"

@@ -9,6 +9,7 @@
 #include <mitsuba/core/lock.h>
 #include <mitsuba/core/thread.h>
 #include <mitsuba/core/logger.h>
+#include <mitsuba/core/random.h>
 #include <mutex>
 #include <condition_variable>
 #include <thread>
@@ -114,6 +115,10 @@ void Thread::start() {
 }
 void Thread::join() { if (d->th.joinable()) d->th.join(); decRef(false); }
 std::string Thread::toString() const { return "Thread[" + d->name + "]"; }
+
+// util.cpp's stratified-sampling helpers take a Random; nothing on the paths used here calls them
+Float Random::nextFloat() { throw std::runtime_error("[reference] Random is not part of this build"); }
+size_t Random::nextSize(size_t) { throw std::runtime_error("[reference] Random is not part of this build"); }
 
 MTS_IMPLEMENT_CLASS(Mutex, false, Object)
 MTS_IMPLEMENT_CLASS(ConditionVariable, false, Object)

@@ -224,7 +224,7 @@ def test_smooth_dielectric_and_conductor_records():
     with pytest.raises(MtsbError, match="must be positive"):
         load('<shape type="rectangle"><bsdf type="dielectric"><float name="intIOR" value="-1"/></bsdf></shape>')
     with pytest.raises(MtsbError, match="specify 'eta' and 'k'"):
-        load('<shape type="rectangle"><bsdf type="conductor"><string name="material" value="W"/></bsdf></shape>')
+        load('<shape type="rectangle"><bsdf type="conductor"><string name="material" value="unobtainium"/></bsdf></shape>')
     with pytest.raises(MtsbError, match="not found"):
         load('<shape type="rectangle"><bsdf type="phong"/></shape>')
 
