@@ -46,7 +46,7 @@ MTSB_HD int clz64(uint64_t v) { return __clzll((long long) v); }
 MTSB_HD int clz32(uint32_t v) { return __clz(v); }
 // 32768 + byte J of w as a float, by one byte permute (PRMT, ALU pipe) instead of an integer->float
 // conversion (I2F, quarter-rate XU pipe): 0x4700bb00 has exponent 2^15 and the byte in mantissa bits 8..15.
-MTSB_HD float byte_bias_float(uint32_t w, int j) { return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7604u | ((uint32_t) j << 4))); }
+MTSB_HD float byte_bias_float(uint32_t w, int j, uint32_t bias) { return __uint_as_float(__byte_perm(w, bias, 0x7604u | ((uint32_t) j << 4))); }
 #else
 // g++ builds of this header are compiled with -ffp-contract=off
 MTSB_HD float fmul(float a, float b) { return a * b; }
@@ -62,7 +62,7 @@ MTSB_HD int bfind(uint32_t v) { return v ? 31 - __builtin_clz(v) : -1; }
 MTSB_HD int popc(uint32_t v) { return __builtin_popcount(v); }
 MTSB_HD int clz64(uint64_t v) { return v ? __builtin_clzll(v) : 64; }
 MTSB_HD int clz32(uint32_t v) { return v ? __builtin_clz(v) : 32; }
-MTSB_HD float byte_bias_float(uint32_t w, int j) { return u2f(0x47000000u | (((w >> (8 * j)) & 0xffu) << 8)); }
+MTSB_HD float byte_bias_float(uint32_t w, int j, uint32_t bias) { return u2f(bias | (((w >> (8 * j)) & 0xffu) << 8)); }
 #endif
 
 // ---- small vector type (kept independent of CUDA's float3 so g++ sees the same code) ----

@@ -6,6 +6,9 @@
 namespace mtsb {
 
 #define MTSB_TRACE_BLOCK 128
+#ifndef MTSB_TRACE_MIN_CTAS
+#define MTSB_TRACE_MIN_CTAS 8     /* resident CTAs per SM the register allocation is held to (64 registers) */
+#endif
 #define MTSB_SM_STACK 8        /* stack entries per thread kept in shared memory   */
 #define MTSB_LOCAL_STACK 56    /* overflow entries per thread in local memory      */
 #define MTSB_REFILL 26         /* refill a warp when fewer lanes than this are busy */
@@ -13,7 +16,7 @@ namespace mtsb {
 // Shared-memory short stack with local-memory overflow.
 struct SmemStack {
     uint2 *sm;                       // this thread's column: sm[i * MTSB_TRACE_BLOCK]
-    uint2 loc[MTSB_LOCAL_STACK];
+    uint2 *loc;                      // overflow array (kept outside the struct so the scalar state stays in registers)
     int sp;
     __device__ __forceinline__ void reset() { sp = 0; }
     __device__ __forceinline__ bool empty() const { return sp == 0; }
@@ -37,16 +40,20 @@ struct TraceArgs {
     uint32_t n_max;
     uint32_t *work_counter;      // zeroed before the launch
     int refill;                  // refill a warp when fewer lanes than this are busy
+    uint32_t prmt_bias;          // 0x47000000, passed as data so it stays a register operand of PRMT (the selector is then the immediate)
 };
 
 template <bool ANY, class Epilogue>
-__global__ void __launch_bounds__(MTSB_TRACE_BLOCK) k_trace(TraceArgs a, Epilogue ep) {
+__global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_MIN_CTAS) k_trace(TraceArgs a, Epilogue ep) {
     __shared__ uint2 s_stack[MTSB_SM_STACK * MTSB_TRACE_BLOCK];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t n = a.d_count ? min(*a.d_count, a.n_max) : a.n_max;
+    uint2 overflow[MTSB_LOCAL_STACK];
     Traversal<SmemStack> tr;
     tr.stack.sm = s_stack + threadIdx.x;
+    tr.stack.loc = overflow;
     tr.stack.sp = 0;
+    tr.bias = a.prmt_bias;
     bool active = false;
     bool exhausted = false;
     uint32_t ray_idx = 0;
@@ -121,6 +128,7 @@ int launch_trace_kernel(Scene *s, const RayIn *d_rays, const uint32_t *d_count, 
     for (int k = 0; k < 3; ++k) { a.box_lo[k] = s->v.box_lo[k]; a.box_hi[k] = s->v.box_hi[k]; }
     a.rays = d_rays; a.d_count = d_count; a.n_max = n_max;
     { static int r = 0; if (!r) { const char *e = getenv("MTSB_REFILL"); r = e ? atoi(e) : MTSB_REFILL; } a.refill = r; }
+    a.prmt_bias = 0x47000000u;
     a.work_counter = trace_work_counter(s, st);
     if (!a.work_counter) return MTSB_ERR_CUDA;
     int grid = trace_grid(s, (const void *) k_trace<ANY, Epilogue>);

@@ -111,6 +111,7 @@ template <class Stack> struct Traversal {
     float ox, oy, oz, dx, dy, dz, tmin, tmax;
     float idx, idy, idz;
     uint32_t octinv;
+    uint32_t bias;                // 0x47000000 (see byte_bias_float)
     uint32_t ng_x, ng_y;          // current node group: (child base, hit bits<<24 | imask)
     HitOut hit;
     Stack stack;
@@ -127,6 +128,9 @@ template <class Stack> struct Traversal {
         idy = 1.0f / (fabsf(dy) > ooeps ? dy : copysignf(ooeps, dy));
         idz = 1.0f / (fabsf(dz) > ooeps ? dz : copysignf(ooeps, dz));
         octinv = (dx >= 0.0f ? 1u : 0u) | (dy >= 0.0f ? 2u : 0u) | (dz >= 0.0f ? 4u : 0u);
+#if !MTSB_DEVICE_CODE
+        bias = 0x47000000u;
+#endif
         ng_x = 0; ng_y = 0x80000000u;
         hit.prim = MTSB_NO_HIT_ID; hit.u = 0; hit.v = 0; hit.t = MTSB_INF;
         stack.reset();
@@ -209,12 +213,12 @@ template <class Stack> struct Traversal {
 #endif
             for (int j = 0; j < 4; ++j) {
                 const int sh = 8 * j;
-                const float tnx = byte_bias_float(nearx[h], j) * sdx + anx;
-                const float tny = byte_bias_float(neary[h], j) * sdy + any_;
-                const float tnz = byte_bias_float(nearz[h], j) * sdz + anz;
-                const float tfx = byte_bias_float(farx[h], j) * sdx + afx;
-                const float tfy = byte_bias_float(fary[h], j) * sdy + afy;
-                const float tfz = byte_bias_float(farz[h], j) * sdz + afz;
+                const float tnx = byte_bias_float(nearx[h], j, bias) * sdx + anx;
+                const float tny = byte_bias_float(neary[h], j, bias) * sdy + any_;
+                const float tnz = byte_bias_float(nearz[h], j, bias) * sdz + anz;
+                const float tfx = byte_bias_float(farx[h], j, bias) * sdx + afx;
+                const float tfy = byte_bias_float(fary[h], j, bias) * sdy + afy;
+                const float tfz = byte_bias_float(farz[h], j, bias) * sdz + afz;
                 const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
                 const float cmax = fminf(fminf(tfx, tfy), fminf(tfz, tmax));
                 const uint32_t bits = ((child_bits4[h] >> sh) & 0xffu) << ((bit_index4[h] >> sh) & 0xffu);
