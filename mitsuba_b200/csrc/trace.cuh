@@ -5,11 +5,15 @@
 
 namespace mtsb {
 
+#ifndef MTSB_TRACE_BLOCK
 #define MTSB_TRACE_BLOCK 128
+#endif
 #ifndef MTSB_TRACE_MIN_CTAS
 #define MTSB_TRACE_MIN_CTAS 8     /* resident CTAs per SM the register allocation is held to (64 registers) */
 #endif
+#ifndef MTSB_SM_STACK
 #define MTSB_SM_STACK 8        /* stack entries per thread kept in shared memory   */
+#endif
 #define MTSB_LOCAL_STACK 56    /* overflow entries per thread in local memory      */
 #define MTSB_REFILL 26         /* refill a warp when fewer lanes than this are busy */
 

@@ -13,7 +13,8 @@ import numpy as np
 from . import abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmtsb200.so")
+# MTSB200_LIB: load another build of the same library (kernel experiments, tools/build_variant.sh)
+LIB_PATH = os.environ.get("MTSB200_LIB") or os.path.join(_HERE, "libmtsb200.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 # every symbol include/mtsb200.h declares (checked by tests/test_abi.py)
