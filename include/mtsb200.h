@@ -39,7 +39,7 @@
 extern "C" {
 #endif
 
-#define MTSB_ABI_VERSION 2
+#define MTSB_ABI_VERSION 3
 
 /* ---- status codes ---------------------------------------------------- */
 enum {
@@ -122,6 +122,22 @@ typedef struct MtsbIntegrator {
     uint32_t _pad;
 } MtsbIntegrator;
 
+/* ---- sample generator (reference: src/samplers/{independent,ldsampler,halton}.cpp) ----
+ * independent: i.i.d. uniforms (counter-based here, independent.cpp:97-105).
+ * ldsampler:   randomly scrambled (0,2)-sequences for the first `dimension` 1D and 2D draws of a
+ *              sample, shuffled per pixel, independent numbers afterwards (ldsampler.cpp:152-215);
+ *              sample_count must be a power of two (the host plugin rounds up, ldsampler.cpp:82-86).
+ * halton:      the Halton sequence enumerated per pixel (Gruenschloss et al., halton.cpp:240-330),
+ *              deterministic: scramble -1 = Faure permutations (default), 0 = none, any other value =
+ *              pseudorandom permutations seeded by it (faure.cpp:34-74).                             */
+enum { MTSB_SAMPLER_INDEPENDENT = 0, MTSB_SAMPLER_LDSAMPLER = 1, MTSB_SAMPLER_HALTON = 2 };
+typedef struct MtsbSampler {
+    uint32_t type;                  /* MTSB_SAMPLER_*                                  */
+    int32_t  dimension;             /* ldsampler `dimension`, default 4 (ldsampler.cpp:78) */
+    int32_t  scramble;              /* halton `scramble`, default -1 (halton.cpp:126)  */
+    uint32_t _pad;
+} MtsbSampler;
+
 typedef struct MtsbSceneDesc {
     uint32_t abi_version;           /* MTSB_ABI_VERSION                                */
     uint32_t n_shapes, n_materials, n_emitters;
@@ -135,6 +151,7 @@ typedef struct MtsbSceneDesc {
     const uint32_t *indices;        /* 3*n_tris, GLOBAL vertex indices                 */
     MtsbSensor      sensor;
     MtsbIntegrator  integrator;
+    MtsbSampler     sampler;        /* zero-initialised = independent                  */
 } MtsbSceneDesc;
 
 /* ---- rays and hit records (cfg 4 and the parity tests) ---------------- */

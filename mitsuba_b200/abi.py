@@ -8,7 +8,7 @@ import ctypes as C
 
 import numpy as np
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 OK, ERR_INVALID, ERR_NO_DEVICE, ERR_CUDA, ERR_CANCELLED, ERR_IO, ERR_PARSE = range(7)
 BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_ROUGHDIELECTRIC, BSDF_NULL, BSDF_DIELECTRIC, BSDF_CONDUCTOR, BSDF_PLASTIC = range(7)
@@ -19,6 +19,7 @@ RFILTER_GAUSSIAN, RFILTER_BOX = 0, 1
 TRACE_CLOSEST, TRACE_ANY = 0, 1
 NO_HIT = 0xFFFFFFFF
 RENDER_KEEP_FILM = 1
+SAMPLER_INDEPENDENT, SAMPLER_LDSAMPLER, SAMPLER_HALTON = 0, 1, 2
 
 
 class Material(C.Structure):
@@ -51,13 +52,17 @@ class Integrator(C.Structure):
                 ("hide_emitters", C.c_int32), ("sample_count", C.c_int32), ("_pad", C.c_uint32)]
 
 
+class Sampler(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("dimension", C.c_int32), ("scramble", C.c_int32), ("_pad", C.c_uint32)]
+
+
 class SceneDesc(C.Structure):
     _fields_ = [("abi_version", C.c_uint32), ("n_shapes", C.c_uint32), ("n_materials", C.c_uint32),
                 ("n_emitters", C.c_uint32), ("n_vertices", C.c_uint64), ("n_tris", C.c_uint64),
                 ("shapes", C.POINTER(Shape)), ("materials", C.POINTER(Material)), ("emitters", C.POINTER(Emitter)),
                 ("positions", C.POINTER(C.c_float)), ("normals", C.POINTER(C.c_float)),
                 ("texcoords", C.POINTER(C.c_float)), ("indices", C.POINTER(C.c_uint32)),
-                ("sensor", Sensor), ("integrator", Integrator)]
+                ("sensor", Sensor), ("integrator", Integrator), ("sampler", Sampler)]
 
 
 class RenderParams(C.Structure):

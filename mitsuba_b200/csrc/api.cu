@@ -5,6 +5,7 @@
 // src/librender/trimesh.cpp:388-403) and builds the BVH on the GPU.
 #include "scene.h"
 #include "trace.cuh"
+#include "qmc_host.h"
 #include <map>
 #include <mutex>
 #include <cmath>
@@ -193,6 +194,7 @@ static int validate(const MtsbSceneDesc *d) {
     if (se.film_width <= 0 || se.film_height <= 0 || se.crop_width <= 0 || se.crop_height <= 0 || se.crop_x < 0 || se.crop_y < 0 ||
         se.crop_x + se.crop_width > se.film_width || se.crop_y + se.crop_height > se.film_height) { set_error("bad film / crop size"); return MTSB_ERR_INVALID; }
     if (!(se.rfilter_radius > 0) || se.rfilter_radius > 7.5f || se.rfilter > MTSB_RFILTER_BOX) { set_error("bad reconstruction filter"); return MTSB_ERR_INVALID; }
+    if (d->sampler.type > MTSB_SAMPLER_HALTON) { set_error("bad sampler type"); return MTSB_ERR_INVALID; }
     if (!(se.fov_x_deg > 0 && se.fov_x_deg < 180) || !(se.near_clip > 0) || !(se.far_clip > se.near_clip)) { set_error("bad sensor parameters"); return MTSB_ERR_INVALID; }
     return MTSB_OK;
 }
@@ -278,6 +280,27 @@ extern "C" int mtsb_scene_create(const MtsbSceneDesc *d, mtsb_scene_t *out) {
         if ((rc = dev_upload(s, &v.area_cdf, acdf.data(), acdf.size()))) return fail(rc);
         if ((rc = dev_upload(s, &v.area_cdf_offset, aoff.data(), aoff.size()))) return fail(rc);
         if ((rc = dev_upload(s, &v.inv_area, inv_area.data(), inv_area.size()))) return fail(rc);
+    }
+    {   // sample generator tables (halton: primes + digit permutations, halton.cpp:139-149, faure.cpp:22-84)
+        const char *err = "";
+        SamplerView sv;
+        if (!sampler_view_init(d->sampler, d->integrator.sample_count, d->sensor.crop_width, d->sensor.crop_height, sv, &err)) {
+            set_error(err); return fail(MTSB_ERR_INVALID);
+        }
+        if (d->sampler.type == MTSB_SAMPLER_HALTON) {
+            const std::vector<uint16_t> primes = qmc_prime_table();
+            if ((rc = dev_upload(s, &sv.primes, primes.data(), primes.size()))) return fail(rc);
+            if (d->sampler.scramble != 0) {
+                std::vector<uint16_t> perms; std::vector<uint32_t> offsets;
+                qmc_permutations(d->sampler.scramble, primes, perms, offsets);
+                if ((rc = dev_upload(s, &sv.perms, perms.data(), perms.size()))) return fail(rc);
+                if ((rc = dev_upload(s, &sv.perm_offset, offsets.data(), offsets.size()))) return fail(rc);
+                for (int j = 0; j < 2; ++j) sv.inv_perm2[perms[offsets[0] + j]] = (uint16_t) j;     // faure.cpp:130-135
+                for (int j = 0; j < 3; ++j) sv.inv_perm3[perms[offsets[1] + j]] = (uint16_t) j;
+            }
+        }
+        v.sampler_type = sv.type;
+        if ((rc = dev_upload(s, &v.sampler, &sv, 1))) return fail(rc);
     }
     if ((rc = build_bvh(s, v.positions, v.indices, d->n_tris))) return fail(rc);
     {   // Scene::m_aabb -> bounding sphere of the environment emitter (scene.cpp:388-414, constant.cpp:67-71)

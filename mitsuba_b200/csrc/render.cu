@@ -74,6 +74,42 @@ __device__ __forceinline__ SampleStream slot_stream(const SceneView &sc, const P
     return SampleStream(ps.seed, (pixel << 24) | (uint64_t) (ps.s_first + s_local));
 }
 
+// ---- quasi-Monte Carlo draws (halton / ldsampler) -----------------------------------------------
+// The reference samplers hand out dimensions in call order (halton.cpp:358-395, ldsampler.cpp:199-213); the
+// per-path dimension counter lives in the flag word.  Kept out of line: the independent sampler (the
+// benchmarked configuration) never calls them and should not pay registers for them.
+struct QmcDraw { float a, b; uint32_t fl; };
+__device__ __noinline__ QmcDraw qmc_draw(const SamplerView *svp, uint64_t seed, int px_abs, int py_abs, uint32_t s_global,
+                                         uint32_t fl, int n, float ia, float ib) {
+    const SamplerView sv = *svp;
+    QmcDraw r; r.a = ia; r.b = ib; r.fl = fl;
+    if (sv.type == MTSB_SAMPLER_HALTON) {
+        int pm[2];
+        const uint64_t index = halton_pixel_offset(sv, px_abs, py_abs, pm) + sv.stride * (uint64_t) s_global;
+        uint32_t dim = fl >> PF_DIM_SHIFT;
+        r.a = halton_value(sv, dim++, index);
+        if (n == 2) {
+            r.b = halton_value(sv, dim++, index);
+            if (dim == 2) {          // halton.cpp:384-386: the first two dimensions address the pixel
+                r.a = fsub(fmul(r.a, (float) sv.prime_pow[0]), (float) pm[0]);
+                r.b = fsub(fmul(r.b, (float) sv.prime_pow[1]), (float) pm[1]);
+            }
+        }
+        if (dim > 0xFFFu) dim = 0xFFFu;
+        r.fl = (fl & ~PF_DIM_MASK) | (dim << PF_DIM_SHIFT);
+    } else if (sv.type == MTSB_SAMPLER_LDSAMPLER) {
+        const uint64_t pixel = ((uint64_t) (uint32_t) py_abs << 32) | (uint64_t) (uint32_t) px_abs;
+        uint32_t d1 = (fl >> PF_DIM_SHIFT) & 63u, d2 = (fl >> (PF_DIM_SHIFT + 6)) & 63u;
+        if (n == 1) {
+            if (d1 < sv.ld_dimension) { r.a = ld_value_1d(sv, seed, pixel, d1, s_global); ++d1; }      // else: the independent number passed in
+        } else {
+            if (d2 < sv.ld_dimension) { float o[2]; ld_value_2d(sv, seed, pixel, d2, s_global, o); r.a = o[0]; r.b = o[1]; ++d2; }
+        }
+        r.fl = (fl & ~PF_DIM_MASK) | (d1 << PF_DIM_SHIFT) | (d2 << (PF_DIM_SHIFT + 6));
+    }
+    return r;
+}
+
 __global__ void k_pass_begin(PathBuffers pb, uint32_t n_slots) {
     Counters *c = pb.ctr;
     c->n_rays[0] = n_slots; c->n_rays[1] = 0; c->n_shadow = 0;          // k_raygen fills queue entry `slot` for every slot
@@ -81,6 +117,7 @@ __global__ void k_pass_begin(PathBuffers pb, uint32_t n_slots) {
 }
 
 // integrator.cpp:218-241: pixel offset from the sampler, sensor ray, new radiance query
+template <bool QMC>
 __global__ void k_raygen(SceneView sc, PathBuffers pb, PassInfo ps, uint32_t n_slots) {
     for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n_slots; slot += gridDim.x * blockDim.x) {
         int px, py; uint32_t s_local;
@@ -96,13 +133,18 @@ __global__ void k_raygen(SceneView sc, PathBuffers pb, PassInfo ps, uint32_t n_s
         }
         float u[4];
         slot_stream(sc, ps, px, py, s_local).block4(0, 0, u);
+        uint32_t fl0 = 1u | PF_FIRST | PF_VALID;
+        if (QMC) {
+            const QmcDraw qd = qmc_draw(sc.sampler, ps.seed, px + sc.sensor.crop_x, py + sc.sensor.crop_y, ps.s_first + s_local, fl0, 2, u[0], u[1]);
+            u[0] = qd.a; u[1] = qd.b; fl0 = qd.fl;
+        }
         const float sx = (float) px + u[0], sy = (float) py + u[1];
         RayIn ray;
         sensor_ray(sc.sensor, sc.near_x, sc.near_y, sx, sy, ray);
         pb.spos[slot] = make_float2(sx, sy);
         pb.thr_eta[slot] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
         pb.L_bpdf[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-        pb.refn_flags[slot] = make_float4(0, 0, 0, __uint_as_float(1u | PF_FIRST | PF_VALID));
+        pb.refn_flags[slot] = make_float4(0, 0, 0, __uint_as_float(fl0));
         store_ray(pb.rays[0], slot, ray);
     }
 }
@@ -191,7 +233,7 @@ template <int Q> __device__ __forceinline__ bool sample_q(const MtsbMaterial *ma
     return ok;
 }
 
-template <int Q>
+template <int Q, bool QMC>
 __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBuffers pb, PassInfo ps, RenderConst rc, int cur) {
     // Outputs (shadow ray + pending contribution, continuation ray) are staged in shared memory and queue space is
     // reserved once per block and queue at the end of the iteration: one global atomic per block instead of one per warp.
@@ -246,6 +288,10 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBu
                 const float qq = fminf(maxComp(thr) * eta * eta, 0.95f);
                 int px, py; uint32_t s_local; slot_pixel(sc, pb, ps, slot, px, py, s_local);
                 float u[4]; slot_stream(sc, ps, px, py, s_local).block4((uint32_t) d0, 1, u);
+                if (QMC) {
+                    const QmcDraw qd = qmc_draw(sc.sampler, ps.seed, px + sc.sensor.crop_x, py + sc.sensor.crop_y, ps.s_first + s_local, fl, 1, u[1], 0.0f);
+                    u[1] = qd.a; fl = qd.fl;
+                }
                 if (u[1] >= qq) alive = false;
                 else thr = thr / qq;
             }
@@ -270,6 +316,11 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBu
                 if (!bsdf_has_back_or_transmission(m0)) dRec.refN = its.sh.n;              // records.inl:175-179
                 // ---- direct illumination (path.cpp:174-202): only for BSDFs with a smooth component (:176-177) ----
                 const bool smooth = Q == Q_DELTA ? false : Q == Q_GENERIC ? bsdf_is_smooth(sc.materials, m0) : true;
+                const bool qmc = QMC;
+                if (qmc && smooth) {             // path.cpp:178: the emitter sample is drawn only for smooth BSDFs
+                    const QmcDraw qd = qmc_draw(sc.sampler, ps.seed, px + sc.sensor.crop_x, py + sc.sensor.crop_y, ps.s_first + s_local, fl, 2, u[0], u[1]);
+                    u[0] = qd.a; u[1] = qd.b; fl = qd.fl;
+                }
                 P2 ue; ue.x = u[0]; ue.y = u[1];
                 V3 value(0.0f);
                 dRec.pdf = 0;
@@ -293,10 +344,20 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBu
                 }
                 // ---- BSDF sampling (path.cpp:208-221) ----
                 float u1 = 0.0f;
+                if (qmc) {                       // path.cpp:211
+                    const QmcDraw qd = qmc_draw(sc.sampler, ps.seed, px + sc.sensor.crop_x, py + sc.sensor.crop_y, ps.s_first + s_local, fl, 2, u[2], u[3]);
+                    u[2] = qd.a; u[3] = qd.b; fl = qd.fl;
+                }
                 if (Q == Q_DIELECTRIC || Q == Q_GENERIC) {
                     bool need = (Q == Q_DIELECTRIC);
                     if (Q == Q_GENERIC) need = sc.materials[bsdf_effective_material(sc.materials, mat, its.wi.z)].type == MTSB_BSDF_ROUGHDIELECTRIC;
-                    if (need) { float v[4]; ss.block4((uint32_t) depth, 1, v); u1 = v[0]; }
+                    if (need) {
+                        float v[4]; ss.block4((uint32_t) depth, 1, v); u1 = v[0];
+                        if (qmc) {               // roughdielectric.cpp:554
+                            const QmcDraw qd = qmc_draw(sc.sampler, ps.seed, px + sc.sensor.crop_x, py + sc.sensor.crop_y, ps.s_first + s_local, fl, 1, u1, 0.0f);
+                            u1 = qd.a; fl = qd.fl;
+                        }
+                    }
                 }
                 BsdfSample bs;
                 P2 ub; ub.x = u[2]; ub.y = u[3];
@@ -422,6 +483,7 @@ __global__ void __launch_bounds__(256) k_splat(SceneView sc, PathBuffers pb, Pas
     extern __shared__ float4 s_stage[];                 // [chunk][1024] value (rgb, alpha), then [chunk][1024] float2 positions
     __shared__ float s_filter[32];                      // the discretised filter (a per-thread index into kernel parameters would serialise)
     if (threadIdx.x < 32) s_filter[threadIdx.x] = sc.filter_table[threadIdx.x];
+    __syncthreads();                                    // the staging loop's scatter path reads the table
     const float f_scale = sc.filter_scale;
     const int chunk = min((int) ps.spp_pass, MTSB_SPLAT_CHUNK);
     float4 *s_val = s_stage;
@@ -453,6 +515,23 @@ __global__ void __launch_bounds__(256) k_splat(SceneView sc, PathBuffers pb, Pas
                     const float2 sp = pb.spos[slot];
                     // position inside the bordered block: pos - 0.5 - (offset - border)
                     pos = make_float2(sp.x - 0.5f - (float) (ox - b), sp.y - 0.5f - (float) (oy - b));
+                    const float fx = sp.x - (float) (ox + x), fy = sp.y - (float) (oy + y);
+                    if (!(fx >= 0.0f && fx < 1.0f && fy >= 0.0f && fy < 1.0f)) {
+                        // A sample outside its own pixel (the reference's halton sampler with random digit permutations places
+                        // some there; px + u can also round up to px + 1): the gather below assumes samples sit inside their
+                        // pixel, so these take ImageBlock::put's scatter form directly (imageblock.h:155-199), clipped to the block.
+                        const int x0 = max((int) ceilf(pos.x - r), 0), x1 = min((int) floorf(pos.x + r), sx - 1);
+                        const int y0 = max((int) ceilf(pos.y - r), 0), y1 = min((int) floorf(pos.y + r), sy - 1);
+                        for (int Y = y0; Y <= y1; ++Y)
+                            for (int X = x0; X <= x1; ++X) {
+                                const float w = s_filter[min((int) fabsf(((float) X - pos.x) * f_scale), 31)] *
+                                                s_filter[min((int) fabsf(((float) Y - pos.y) * f_scale), 31)];
+                                float *dest = sc.film + ((size_t) (oy + Y) * fsx + (ox + X)) * 5;
+                                atomicAdd(dest, w * val.x); atomicAdd(dest + 1, w * val.y); atomicAdd(dest + 2, w * val.z);
+                                atomicAdd(dest + 3, w * val.w); atomicAdd(dest + 4, w);
+                            }
+                        val = make_float4(0, 0, 0, 0); pos = make_float2(1e30f, 1e30f);
+                    }
                 } else ++n_bad;
             }
             s_val[sl * MTSB_TILE * MTSB_TILE + y * MTSB_TILE + x] = val;
@@ -627,12 +706,13 @@ static int lane_bounce(Scene *s, Lane &L, const RenderConst &rcst, int sm_count)
     k_sort<<<std::max(1, std::min((int) ((L.n_cur + MTSB_SORT_BLOCK - 1) / MTSB_SORT_BLOCK), sm_count * 4)), MTSB_SORT_BLOCK, 0, L.st>>>(v, pb, L.cur);
     // only the queues some material of this scene can feed are launched
     const uint32_t qm = L.queue_mask;
-    if (qm & (1u << Q_DIFFUSE))    { k_shade<Q_DIFFUSE><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
-    if (qm & (1u << Q_CONDUCTOR))  { k_shade<Q_CONDUCTOR><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
-    if (qm & (1u << Q_DIELECTRIC)) { k_shade<Q_DIELECTRIC><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
-    if (qm & (1u << Q_NULL))       { k_shade<Q_NULL><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
-    if (qm & (1u << Q_GENERIC))    { k_shade<Q_GENERIC><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
-    if (qm & (1u << Q_DELTA))      { k_shade<Q_DELTA><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
+    const bool qmc = v.sampler_type != MTSB_SAMPLER_INDEPENDENT;
+    if (qm & (1u << Q_DIFFUSE))    { if (qmc) k_shade<Q_DIFFUSE, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_DIFFUSE, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
+    if (qm & (1u << Q_CONDUCTOR))  { if (qmc) k_shade<Q_CONDUCTOR, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_CONDUCTOR, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
+    if (qm & (1u << Q_DIELECTRIC)) { if (qmc) k_shade<Q_DIELECTRIC, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_DIELECTRIC, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
+    if (qm & (1u << Q_NULL))       { if (qmc) k_shade<Q_NULL, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_NULL, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
+    if (qm & (1u << Q_GENERIC))    { if (qmc) k_shade<Q_GENERIC, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_GENERIC, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
+    if (qm & (1u << Q_DELTA))      { if (qmc) k_shade<Q_DELTA, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_DELTA, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
     k_miss<<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, rcst, L.cur);
     s->launches += 3;
     L.timer->end();
@@ -649,7 +729,8 @@ static int lane_start(Scene *s, Lane &L, const Pass &p, const RenderConst &rcst,
     L.pass = p; L.busy = true; L.cur = 0; L.n_cur = p.n_slots; L.first = true;
     L.timer->begin(ST_RAYGEN);
     k_pass_begin<<<1, 1, 0, L.st>>>(*L.pb, p.n_slots);
-    k_raygen<<<shade_grid(p.n_slots, sm_count), MTSB_SHADE_BLOCK, 0, L.st>>>(s->v, *L.pb, p.ps, p.n_slots);
+    if (s->v.sampler_type != MTSB_SAMPLER_INDEPENDENT) k_raygen<true><<<shade_grid(p.n_slots, sm_count), MTSB_SHADE_BLOCK, 0, L.st>>>(s->v, *L.pb, p.ps, p.n_slots);
+    else k_raygen<false><<<shade_grid(p.n_slots, sm_count), MTSB_SHADE_BLOCK, 0, L.st>>>(s->v, *L.pb, p.ps, p.n_slots);
     s->launches += 2;
     L.timer->end();
     return lane_bounce(s, L, rcst, sm_count);
@@ -686,6 +767,11 @@ extern "C" int mtsb_render(mtsb_scene_t scene, const MtsbRenderParams *params, M
     const int spp = params->spp > 0 ? params->spp : v.integrator.sample_count;
     if (spp <= 0 || (uint64_t) spp + (uint64_t) params->spp_offset >= (1ull << 24)) { set_error("mtsb_render: sample count out of range"); return MTSB_ERR_INVALID; }
     const int tile_count = params->tile_count > 0 ? params->tile_count : 1, tile_index = params->tile_count > 0 ? params->tile_index : 0;
+    if (v.sampler_type == MTSB_SAMPLER_LDSAMPLER) {
+        // ldsampler.cpp:200,208 assert sampleIndex < sampleCount: the point sets hold exactly sampleCount entries
+        int n = v.integrator.sample_count > 0 ? v.integrator.sample_count : 1;
+        if (spp + params->spp_offset > n) { set_error("mtsb_render: ldsampler point sets hold sampleCount samples; spp_offset + spp exceeds it"); return MTSB_ERR_INVALID; }
+    }
     const uint32_t tiles_x = (uint32_t) (v.film_w + MTSB_TILE - 1) / MTSB_TILE, tiles_y = (uint32_t) (v.film_h + MTSB_TILE - 1) / MTSB_TILE;
     std::vector<int> tiles;
     for (uint32_t t = 0; t < tiles_x * tiles_y; ++t) if ((int) (t % (uint32_t) tile_count) == tile_index) tiles.push_back((int) t);

@@ -16,6 +16,10 @@ enum { Q_DIFFUSE = 0, Q_CONDUCTOR = 1, Q_DIELECTRIC = 2, Q_NULL = 3, Q_GENERIC =
 #define PF_SCATTERED  (1u << 17)
 #define PF_ALPHA      (1u << 18)   /* first hit was valid (records.inl:136-152)            */
 #define PF_VALID      (1u << 19)   /* slot maps to a pixel inside the crop window          */
+/* bits 20..31: dimension counter of the quasi-Monte Carlo samplers (qmc.h).  halton: next dimension
+ * (12 bits); ldsampler: next 1D dimension (bits 20..25) and next 2D dimension (bits 26..31).      */
+#define PF_DIM_SHIFT  20
+#define PF_DIM_MASK   0xFFF00000u
 
 struct Counters {
     uint32_t n_rays[2];        // closest-ray queue sizes (double buffered)

@@ -2,6 +2,7 @@
 #pragma once
 #include "../../include/mtsb200.h"
 #include "bvh.h"
+#include "qmc.h"
 
 namespace mtsb {
 
@@ -25,6 +26,8 @@ struct SceneView {
     // sensor (perspective.cpp:127-150, 286-317)
     MtsbSensor sensor; float near_x, near_y;
     MtsbIntegrator integrator;
+    uint32_t sampler_type;                  // MTSB_SAMPLER_*
+    const SamplerView *sampler;             // device copy of the generator description (qmc.h); read only when sampler_type != independent
     // film (imageblock.h:124-206)
     float *film; int film_w, film_h, film_border; float filter_radius, filter_scale;
     float filter_table[32];

@@ -124,9 +124,11 @@ public:
 
 class Sampler : public ConfigurableObject {
 public:
-    explicit Sampler(const Properties &p);       // independent.cpp:55-60
+    explicit Sampler(const Properties &p);       // independent.cpp:55-60, ldsampler.cpp:75-86, halton.cpp:121-130
     EClass getClass() const override { return CSampler; }
     int sampleCount; int seed;
+    uint32_t kind;                               // MTSB_SAMPLER_*
+    int dimension, scramble;                     // ldsampler `dimension`, halton `scramble`
 };
 
 class Sensor : public ConfigurableObject {

@@ -130,6 +130,7 @@ void Scene::flatten(FlatScene &f) const {
     d.integrator.strict_normals = integrator->strictNormals;
     d.integrator.hide_emitters = integrator->hideEmitters;
     d.integrator.sample_count = sensor->sampler->sampleCount;
+    d.sampler.type = sensor->sampler->kind; d.sampler.dimension = sensor->sampler->dimension; d.sampler.scramble = sensor->sampler->scramble; d.sampler._pad = 0;
     f.seed = sensor->sampler->seed;
 }
 

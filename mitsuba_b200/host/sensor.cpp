@@ -62,11 +62,30 @@ void Film::configure() {
 // ---- sampler ---------------------------------------------------------------------------------------
 Sampler::Sampler(const Properties &p) : ConfigurableObject(p) {
     const std::string type = lower(p.getPluginName());
-    if (type != "independent")
-        error("Plugin \"" + type + "\" not found -- the B200 path implements the sampler independent (counter-based streams).");
-    sampleCount = p.getInteger("sampleCount", 4);
-    seed = p.getInteger("seed", 1004);
-    if (sampleCount <= 0) error("independent: 'sampleCount' must be positive");
+    kind = MTSB_SAMPLER_INDEPENDENT; dimension = 4; scramble = -1;
+    if (type == "independent") {                     // independent.cpp:55-60
+        sampleCount = p.getInteger("sampleCount", 4);
+        seed = p.getInteger("seed", 1004);
+    } else if (type == "ldsampler") {                // ldsampler.cpp:75-86
+        kind = MTSB_SAMPLER_LDSAMPLER;
+        sampleCount = p.getInteger("sampleCount", 4);
+        dimension = p.getInteger("dimension", 4);
+        seed = 1004;
+        if (sampleCount > 0 && (sampleCount & (sampleCount - 1))) {
+            int r = 1; while (r < sampleCount) r <<= 1;
+            sampleCount = r;
+            warn("Sample count should be a power of two -- rounding to " + std::to_string(sampleCount));
+        }
+        if (dimension < 0 || dimension > 63) error("ldsampler: 'dimension' must be between 0 and 63 on the B200 path");
+    } else if (type == "halton") {                   // halton.cpp:121-130
+        kind = MTSB_SAMPLER_HALTON;
+        sampleCount = p.getInteger("sampleCount", 4);
+        scramble = p.getInteger("scramble", -1);
+        seed = 1004;
+    } else {
+        error("Plugin \"" + type + "\" not found -- the B200 path implements the samplers independent (counter-based streams), ldsampler and halton.");
+    }
+    if (sampleCount <= 0) error(type + ": 'sampleCount' must be positive");
 }
 
 // ---- perspective sensor ----------------------------------------------------------------------------

@@ -207,6 +207,8 @@ class SceneBuilder:
         self._nt = 0
         self.sensor = abi.Sensor()
         self.integrator = abi.Integrator()
+        self.sampler = abi.Sampler()
+        self.sampler.dimension, self.sampler.scramble = 4, -1
         self.set_integrator()
         self.set_sensor(look_at([0, 0, -5], [0, 0, 0], [0, 1, 0]), 45.0, 64, 64)
         self._keep = None
@@ -219,6 +221,18 @@ class SceneBuilder:
         ig.max_depth, ig.rr_depth = int(max_depth), int(rr_depth)
         ig.strict_normals, ig.hide_emitters = int(strict_normals), int(hide_emitters)
         ig.sample_count = int(sample_count)
+
+    def set_sampler(self, kind="independent", sample_count=None, dimension=4, scramble=-1):
+        """Sample generator: `independent`, `ldsampler` (sample count rounded up to a power of two,
+        src/samplers/ldsampler.cpp:75-86) or `halton` (src/samplers/halton.cpp:121-130)."""
+        kinds = {"independent": abi.SAMPLER_INDEPENDENT, "ldsampler": abi.SAMPLER_LDSAMPLER, "halton": abi.SAMPLER_HALTON}
+        self.sampler.type = kinds[kind]
+        self.sampler.dimension, self.sampler.scramble = int(dimension), int(scramble)
+        if sample_count is not None:
+            self.integrator.sample_count = int(sample_count)
+        if kind == "ldsampler":
+            n = max(1, int(self.integrator.sample_count))
+            self.integrator.sample_count = 1 << (n - 1).bit_length()
 
     def set_sensor(self, to_world, fov, width, height, fov_axis="x", near_clip=1e-2, far_clip=1e4,
                    rfilter="gaussian", stddev=0.5, box_radius=0.5, crop=None):
@@ -346,5 +360,6 @@ class SceneBuilder:
         d.indices = abi.ptr(idx, C.c_uint32)
         d.sensor = self.sensor
         d.integrator = self.integrator
+        d.sampler = self.sampler
         keep = (pos, nrm, uv, idx, shapes, mats, ems)
         return d, keep

@@ -68,6 +68,20 @@ def lib():
         L.orc_fresnel_conductor_exact.argtypes = [C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_microfacet.argtypes = [C.c_int, C.c_float, C.c_float, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_warp.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_halton_sequence.argtypes = [C.c_int] * 9 + [C.c_void_p]
+        L.orc_radical_inverse.argtypes = [C.c_int, C.c_uint64]
+        L.orc_radical_inverse.restype = C.c_float
+        L.orc_radical_inverse_incremental.argtypes = [C.c_int, C.c_float]
+        L.orc_radical_inverse_incremental.restype = C.c_float
+        L.orc_radical_inverse_fast.argtypes = [C.c_int, C.c_uint64]
+        L.orc_radical_inverse_fast.restype = C.c_float
+        L.orc_scrambled_radical_inverse_fast.argtypes = [C.c_int, C.c_uint64, C.c_void_p]
+        L.orc_scrambled_radical_inverse_fast.restype = C.c_float
+        L.orc_permutation.argtypes = [C.c_int, C.c_int, C.c_void_p]
+        L.orc_sample02.argtypes = [C.c_uint32, C.c_void_p, C.c_void_p]
+        L.orc_sample_tea.argtypes = [C.c_uint32, C.c_uint32, C.c_int]
+        L.orc_sample_tea.restype = C.c_uint64
+        L.orc_ldsampler_sets.argtypes = [C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 

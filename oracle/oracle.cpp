@@ -18,10 +18,12 @@
 // tests/golden/ were generated from that library).  The random number stream is NOT the
 // reference's SFMT19937: image parity is statistical.
 #include "orc_scene.h"
+#include "orc_sampler.h"
 #include <cstdio>
 #include <cstdlib>
 #include <string>
 #include <chrono>
+#include <memory>
 
 using namespace orc;
 
@@ -35,7 +37,8 @@ thread_local std::string g_err;
 //  * counter: Philox4x32-10 (Salmon et al., SC'11; published constants) keyed by (seed, pixel<<24 | sample)
 //    and numbered by (bounce, slot) -- the same numbering the CUDA wavefront uses, restated here
 //    independently, so that a CPU render can be compared with the GPU film sample for sample.
-struct Rng {
+struct Rng : orc::SeqRandom {
+    orc::QmcSampler *qmc = nullptr;      // halton / ldsampler: draws go through the stateful sampler in call order
     uint64_t s[4];
     bool counter; uint32_t k0, k1, idLo, idHi;
     static uint64_t splitmix(uint64_t &x) {
@@ -48,13 +51,13 @@ struct Rng {
     Rng(uint64_t seed, uint64_t sampleId) : counter(true), k0((uint32_t) seed), k1((uint32_t) (seed >> 32)),
         idLo((uint32_t) sampleId), idHi((uint32_t) (sampleId >> 32)) { s[0] = s[1] = s[2] = s[3] = 0; }
     static uint64_t rotl(uint64_t x, int k) { return (x << k) | (x >> (64 - k)); }
-    uint64_t nextULong() {
+    uint64_t nextULong() override {
         uint64_t r = rotl(s[1] * 5, 7) * 9, t = s[1] << 17;
         s[2] ^= s[0]; s[3] ^= s[1]; s[1] ^= s[2]; s[0] ^= s[3]; s[2] ^= t; s[3] = rotl(s[3], 45);
         return r;
     }
     static float toFloat(uint32_t v) { union { uint32_t u; float f; } x; x.u = (v >> 9) | 0x3f800000u; return x.f - 1.0f; }
-    float nextFloat() { return toFloat((uint32_t) (nextULong() & 0xFFFFFFFFull)); }
+    float nextFloat() override { return toFloat((uint32_t) (nextULong() & 0xFFFFFFFFull)); }
     P2 next2D() { float a = nextFloat(); float b = nextFloat(); return P2{a, b}; }
     void block(uint32_t blk, uint32_t sub, float out[4]) const {
         uint32_t c[4] = {idLo, idHi, blk, sub}, ka = k0, kb = k1;
@@ -67,11 +70,12 @@ struct Rng {
         for (int i = 0; i < 4; ++i) out[i] = toFloat(c[i]);
     }
     // the four places where the integrator draws numbers
-    P2 pixel2D() { if (!counter) return next2D(); float u[4]; block(0, 0, u); return P2{u[0], u[1]}; }                 // integrator.cpp:227
-    P2 emitter2D(int depth) { if (!counter) return next2D(); float u[4]; block((uint32_t) depth, 0, u); return P2{u[0], u[1]}; }   // path.cpp:178
-    P2 bsdf2D(int depth) { if (!counter) return next2D(); float u[4]; block((uint32_t) depth, 0, u); return P2{u[2], u[3]}; }      // path.cpp:211
-    float extra1D(int depth) { if (!counter) return nextFloat(); float u[4]; block((uint32_t) depth, 1, u); return u[0]; }         // roughdielectric.cpp:554
-    float rr1D(int depth) { if (!counter) return nextFloat(); float u[4]; block((uint32_t) depth, 1, u); return u[1]; }            // path.cpp:285
+    P2 q2() { float o[2]; qmc->next2D(o); return P2{o[0], o[1]}; }
+    P2 pixel2D() { if (qmc) return q2(); if (!counter) return next2D(); float u[4]; block(0, 0, u); return P2{u[0], u[1]}; }                 // integrator.cpp:227
+    P2 emitter2D(int depth) { if (qmc) return q2(); if (!counter) return next2D(); float u[4]; block((uint32_t) depth, 0, u); return P2{u[0], u[1]}; }   // path.cpp:178
+    P2 bsdf2D(int depth) { if (qmc) return q2(); if (!counter) return next2D(); float u[4]; block((uint32_t) depth, 0, u); return P2{u[2], u[3]}; }      // path.cpp:211
+    float extra1D(int depth) { if (qmc) return qmc->next1D(); if (!counter) return nextFloat(); float u[4]; block((uint32_t) depth, 1, u); return u[0]; }         // roughdielectric.cpp:554
+    float rr1D(int depth) { if (qmc) return qmc->next1D(); if (!counter) return nextFloat(); float u[4]; block((uint32_t) depth, 1, u); return u[1]; }            // path.cpp:285
 };
 
 struct Counters { uint64_t closest = 0, shadow = 0, shade = 0, pathLen = 0, samples = 0; double lum = 0, lum2 = 0; };
@@ -424,6 +428,13 @@ int orc_render2(void *h, int spp, uint64_t seed, int nthreads, int max_blocks, O
         for (int i = 0; i < max_blocks; ++i) sub.push_back(blocks[(size_t) i * total / max_blocks]);
         blocks.swap(sub);
     }
+    // sample generator of the scene (src/samplers): halton / ldsampler objects are per worker, as in renderjob.cpp:59-70
+    const MtsbSampler &smp = sc->sd.sampler;
+    std::unique_ptr<orc::Permutations> perms;
+    if (smp.type == MTSB_SAMPLER_HALTON && smp.scramble != 0) perms.reset(new orc::Permutations(smp.scramble));   // halton.cpp:139-149
+    if (smp.type == MTSB_SAMPLER_LDSAMPLER && spp + sppOffset > (int) orc::LowDiscrepancySampler(std::max(1, sc->sd.integrator.sample_count), 0, nullptr).sampleCount) {
+        g_err = "ldsampler: sample index exceeds sampleCount"; return MTSB_ERR_INVALID;
+    }
     std::atomic<size_t> next(0);
     std::mutex filmMutex;
     std::vector<Counters> counters(nthreads);
@@ -439,10 +450,21 @@ int orc_render2(void *h, int spp, uint64_t seed, int nthreads, int max_blocks, O
             int bw = std::min(BS, f.w - ox), bh = std::min(BS, f.h - oy);
             std::fill(buf.begin(), buf.end(), 0.0f);
             Rng rng(seed * 0x100000001b3ULL + (uint64_t) (blocks[bi].second * nbx + blocks[bi].first) + 0x51ed27);
+            std::unique_ptr<orc::QmcSampler> qmc;
+            if (smp.type == MTSB_SAMPLER_HALTON) {
+                orc::HaltonSampler *hs = new orc::HaltonSampler(perms.get());
+                hs->setFilmResolution(sc->sd.sensor.crop_width, sc->sd.sensor.crop_height, true);       // integrator.cpp:38-42
+                qmc.reset(hs);
+            } else if (smp.type == MTSB_SAMPLER_LDSAMPLER) {
+                qmc.reset(new orc::LowDiscrepancySampler((size_t) std::max(1, sc->sd.integrator.sample_count), (size_t) std::max(0, smp.dimension), &rng));
+            }
+            rng.qmc = qmc.get();
             for (int y = 0; y < bh; ++y)
-                for (int x = 0; x < bw; ++x)
+                for (int x = 0; x < bw; ++x) {
+                    if (qmc) qmc->generate(ox + x + sc->sd.sensor.crop_x, oy + y + sc->sd.sensor.crop_y);       // integrator.cpp:222
                     for (int j = 0; j < spp; ++j) {
-                        if (counterRng) {
+                        if (qmc) qmc->setSampleIndex((size_t) (sppOffset + j));                                // advance(), integrator.cpp:240
+                        else if (counterRng) {
                             uint64_t pixel = (uint64_t) (oy + y + sc->sd.sensor.crop_y) * (uint64_t) sc->sd.sensor.film_width + (uint64_t) (ox + x + sc->sd.sensor.crop_x);
                             rng = Rng(seed, (pixel << 24) | (uint64_t) (sppOffset + j));
                         }
@@ -456,6 +478,7 @@ int orc_render2(void *h, int spp, uint64_t seed, int nthreads, int max_blocks, O
                         if (!blockPut(f, buf.data(), ox, oy, bw, bh, samplePos, v)) bad++;
                         else { double l = luminance(L); cnt.lum += l; cnt.lum2 += l * l; }
                     }
+                }
             // film->put(block): overlap-add incl. borders (imageblock.h:103-107)
             std::lock_guard<std::mutex> g(filmMutex);
             int bsx = bw + 2 * f.border;
@@ -530,6 +553,51 @@ void orc_warp(int kind, const float *u2, float *out3) {
     else if (kind == 1) { V3 v = squareToUniformSphere(u); out3[0] = v.x; out3[1] = v.y; out3[2] = v.z; }
     else if (kind == 2) { P2 p = squareToUniformTriangle(u); out3[0] = p.x; out3[1] = p.y; out3[2] = 0; }
     else { P2 p = squareToUniformDiskConcentric(u); out3[0] = p.x; out3[1] = p.y; out3[2] = 0; }
+}
+
+// ---- sample generators (orc_sampler.h), exposed for the known-answer tests --------------------------
+// Halton sampler driven like renderBlock drives it: generate(px,py); for each sample: setSampleIndex, then n1 x next2D
+// followed by n2 x next1D.  res <= 0: setFilmResolution is not called (the state test_samplers.cpp:37-56 runs in).
+int orc_halton_sequence(int resX, int resY, int scramble, int px, int py, int firstSample, int nSamples, int n2D, int n1D, float *out) {
+    try {
+        std::unique_ptr<orc::Permutations> perms;
+        if (scramble != 0) perms.reset(new orc::Permutations(scramble));
+        orc::HaltonSampler hs(perms.get());
+        if (resX > 0) hs.setFilmResolution(resX, resY, true);
+        hs.generate(px, py);
+        for (int j = 0; j < nSamples; ++j) {
+            hs.setSampleIndex((size_t) (firstSample + j));
+            for (int k = 0; k < n2D; ++k) { hs.next2D(out); out += 2; }
+            for (int k = 0; k < n1D; ++k) *out++ = hs.next1D();
+        }
+    } catch (const std::exception &e) { g_err = e.what(); return MTSB_ERR_INVALID; }
+    return MTSB_OK;
+}
+float orc_radical_inverse(int base, uint64_t i) { return orc::radicalInverse(base, i); }
+float orc_radical_inverse_incremental(int base, float x) { return orc::radicalInverseIncremental(base, x); }
+float orc_radical_inverse_fast(int baseIndex, uint64_t index) { return orc::radicalInverseFast(baseIndex, index); }
+float orc_scrambled_radical_inverse_fast(int baseIndex, uint64_t index, const uint16_t *perm) { return orc::radicalInverseFast(baseIndex, index, perm); }
+// permutation of prime `baseIndex` (faure.cpp); returns its length
+int orc_permutation(int scramble, int baseIndex, uint16_t *out) {
+    static std::mutex m; static std::unique_ptr<orc::Permutations> cache; static int cached = 0;
+    std::lock_guard<std::mutex> g(m);
+    if (!cache || cached != scramble) { cache.reset(new orc::Permutations(scramble)); cached = scramble; }
+    const std::vector<uint16_t> &p = cache->perm[baseIndex];
+    std::copy(p.begin(), p.end(), out);
+    return (int) p.size();
+}
+void orc_sample02(uint32_t n, const uint32_t *scramble2, float *out2) { out2[0] = orc::radicalInverse2Single(n, scramble2[0]); out2[1] = orc::sobol2Single(n, scramble2[1]); }
+uint64_t orc_sample_tea(uint32_t v0, uint32_t v1, int rounds) { return orc::sampleTEA(v0, v1, rounds); }
+// LowDiscrepancySampler point sets of one pixel: out1[dim][count], out2[dim][count][2]
+int orc_ldsampler_sets(int sampleCount, int dimension, uint64_t seed, float *out1, float *out2) {
+    Rng rng(seed);
+    orc::LowDiscrepancySampler ld((size_t) sampleCount, (size_t) dimension, &rng);
+    ld.generate(0, 0);
+    for (size_t d = 0; d < ld.maxDimension; ++d) {
+        std::copy(ld.samples1D[d].begin(), ld.samples1D[d].end(), out1 + d * ld.sampleCount);
+        std::copy(ld.samples2D[d].begin(), ld.samples2D[d].end(), out2 + d * 2 * ld.sampleCount);
+    }
+    return (int) ld.sampleCount;
 }
 
 }  // extern "C"

@@ -27,6 +27,8 @@
 #include <boost/filesystem.hpp>
 #include <mutex>
 #include "src/bsdfs/microfacet.h"
+#include <mitsuba/core/qmc.h>
+#include "src/samplers/faure.h"
 #include "../include/mtsb200.h"
 #include <vector>
 
@@ -275,5 +277,25 @@ int ref_spd_to_rgb(const char *path, float *out3) {
         return 0;
     } catch (const std::exception &e) { return 1; }
 }
+
+// ---- quasi-Monte Carlo building blocks (src/libcore/qmc.cpp, include/mitsuba/core/qmc.h, src/samplers/faure.cpp) ----
+float ref_radical_inverse(int base, uint64_t i) { return radicalInverse(base, i); }
+float ref_radical_inverse_incremental(int base, float x) { return radicalInverseIncremental(base, x); }
+float ref_radical_inverse_fast(int baseIndex, uint64_t index) { return radicalInverseFast((uint16_t) baseIndex, index); }
+float ref_scrambled_radical_inverse_fast(int baseIndex, uint64_t index, uint16_t *perm) { return scrambledRadicalInverseFast((uint16_t) baseIndex, index, perm); }
+int ref_prime(int i) { return primeTable[i]; }
+// PermutationStorage(scramble)->getPermutation(baseIndex); inverse != 0: getInversePermutation (bases 2 and 3 only)
+int ref_permutation(int scramble, int baseIndex, int inverse, uint16_t *out) {
+    static std::mutex m; static ref<PermutationStorage> cache;
+    std::lock_guard<std::mutex> g(m);
+    if (cache == NULL || cache->getScramble() != scramble) cache = new PermutationStorage(scramble);
+    const uint16_t *p = inverse ? cache->getInversePermutation(baseIndex) : cache->getPermutation(baseIndex);
+    for (int j = 0; j < primeTable[baseIndex]; ++j) out[j] = p[j];
+    return primeTable[baseIndex];
+}
+void ref_sample02(uint32_t n, uint32_t *scramble2, float *out2) { Point2f p = sample02Single(n, scramble2); out2[0] = p.x; out2[1] = p.y; }
+float ref_radical_inverse2(uint32_t n, uint32_t scramble) { return radicalInverse2Single(n, scramble); }
+float ref_sobol2(uint32_t n, uint32_t scramble) { return sobol2Single(n, scramble); }
+uint64_t ref_sample_tea(uint32_t v0, uint32_t v1, int rounds) { return sampleTEA(v0, v1, rounds); }
 
 }  // extern "C"

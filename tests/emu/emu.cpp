@@ -9,6 +9,8 @@
 #include "../../mitsuba_b200/csrc/traverse.h"
 #include "../../mitsuba_b200/csrc/sensor.h"
 #include "../../mitsuba_b200/csrc/rng.h"
+#include "../../mitsuba_b200/csrc/qmc.h"
+#include "../../mitsuba_b200/csrc/qmc_host.h"
 #include <vector>
 #include <algorithm>
 #include <numeric>
@@ -131,6 +133,59 @@ extern "C" void emu_philox(const uint32_t *ctr4, const uint32_t *key2, uint32_t 
 }
 extern "C" void emu_sample_block(uint64_t seed, uint64_t sample_id, uint32_t block, uint32_t sub, float *out4) {
     SampleStream(seed, sample_id).block4(block, sub, out4);
+}
+
+// ---- quasi-Monte Carlo draws of the kernels (qmc.h), driven in the order k_raygen / k_shade use them ----
+// Halton: for each sample n2D two-dimensional draws (the first one addresses the pixel) followed by n1D one-dimensional ones.
+extern "C" int emu_halton_sequence(int resX, int resY, int scramble, int px, int py, int firstSample, int nSamples, int n2D, int n1D, float *out) {
+    MtsbSampler sd; sd.type = MTSB_SAMPLER_HALTON; sd.dimension = 0; sd.scramble = scramble; sd._pad = 0;
+    SamplerView sv; const char *err = "";
+    if (!sampler_view_init(sd, 1, resX, resY, sv, &err)) return 1;
+    const std::vector<uint16_t> primes = qmc_prime_table();
+    std::vector<uint16_t> perms; std::vector<uint32_t> offsets;
+    sv.primes = primes.data();
+    if (scramble != 0) {
+        qmc_permutations(scramble, primes, perms, offsets);
+        sv.perms = perms.data(); sv.perm_offset = offsets.data();
+        for (int j = 0; j < 2; ++j) sv.inv_perm2[perms[offsets[0] + j]] = (uint16_t) j;
+        for (int j = 0; j < 3; ++j) sv.inv_perm3[perms[offsets[1] + j]] = (uint16_t) j;
+    }
+    for (int j = 0; j < nSamples; ++j) {
+        int pm[2];
+        const uint64_t index = halton_pixel_offset(sv, px, py, pm) + sv.stride * (uint64_t) (firstSample + j);
+        uint32_t dim = 0;
+        for (int k = 0; k < n2D; ++k) {
+            float a = halton_value(sv, dim++, index), b = halton_value(sv, dim++, index);
+            if (dim == 2) { a = fsub(fmul(a, (float) sv.prime_pow[0]), (float) pm[0]); b = fsub(fmul(b, (float) sv.prime_pow[1]), (float) pm[1]); }
+            *out++ = a; *out++ = b;
+        }
+        for (int k = 0; k < n1D; ++k) *out++ = halton_value(sv, dim++, index);
+    }
+    return 0;
+}
+extern "C" float emu_radical_inverse(uint32_t base, uint64_t index, const uint16_t *perm) { return radical_inverse(base, index, perm); }
+extern "C" int emu_permutation(int scramble, int baseIndex, uint16_t *out) {
+    static int cached = 0; static std::vector<uint16_t> perms; static std::vector<uint32_t> offsets;
+    const std::vector<uint16_t> primes = qmc_prime_table();
+    if (perms.empty() || cached != scramble) { qmc_permutations(scramble, primes, perms, offsets); cached = scramble; }
+    std::copy(perms.begin() + offsets[baseIndex], perms.begin() + offsets[baseIndex] + primes[baseIndex], out);
+    return primes[baseIndex];
+}
+extern "C" int emu_prime(int i) { return qmc_prime_table()[i]; }
+extern "C" void emu_sample02(uint32_t n, const uint32_t *scramble2, float *out2) { out2[0] = radical_inverse2_single(n, scramble2[0]); out2[1] = sobol2_single(n, scramble2[1]); }
+extern "C" uint32_t emu_permute_pow2(uint32_t i, uint32_t bits, uint32_t ka, uint32_t kb) { return permute_pow2(i, bits, ka, kb); }
+// ldsampler point sets of one pixel as the kernels see them: out1[dim][count], out2[dim][count][2] (indexed by sample index)
+extern "C" int emu_ldsampler_sets(int sampleCount, int dimension, uint64_t seed, int px, int py, float *out1, float *out2) {
+    MtsbSampler sd; sd.type = MTSB_SAMPLER_LDSAMPLER; sd.dimension = dimension; sd.scramble = 0; sd._pad = 0;
+    SamplerView sv; const char *err = "";
+    if (!sampler_view_init(sd, sampleCount, 1, 1, sv, &err)) return 1;
+    const uint64_t pixel = ((uint64_t) (uint32_t) py << 32) | (uint64_t) (uint32_t) px;
+    for (int d = 0; d < dimension; ++d)
+        for (uint32_t i = 0; i < sv.sample_count; ++i) {
+            out1[(size_t) d * sv.sample_count + i] = ld_value_1d(sv, seed, pixel, (uint32_t) d, i);
+            ld_value_2d(sv, seed, pixel, (uint32_t) d, i, out2 + ((size_t) d * sv.sample_count + i) * 2);
+        }
+    return 0;
 }
 
 // ---- experiment support: the same wide collapse fed by a top-down binned-SAH binary tree ----

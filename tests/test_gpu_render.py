@@ -182,3 +182,96 @@ def test_point_light_and_hide_emitters(gpu_lib, oracle_mod):
     b.add_point_light([278, 400, 279], [4e5, 4e5, 4e5])
     b.set_integrator(max_depth=5, rr_depth=3, hide_emitters=True, sample_count=16)
     check_render(gpu_lib, oracle_mod, b, 16, 128, "point")
+
+
+# ---- quasi-Monte Carlo samplers ---------------------------------------------------------------
+
+def check_same_sequence(gpu_lib, oracle_mod, b, spp, label, **render_kw):
+    """halton is deterministic: the GPU and the oracle (which drives the stateful sampler like renderBlock does) draw the
+    same numbers as the reference itself would, so the films agree pixel by pixel."""
+    sc, orc = gpu_lib.Scene(b), oracle_mod.Oracle(b)
+    st = sc.render(spp=spp, seed=1, **render_kw)
+    fg = sc.film_download().astype(np.float64)
+    ost = orc.render(spp=spp, seed=99)
+    fo = orc.film_download().astype(np.float64)
+    bad = (np.abs(fg - fo) > 1e-3 * np.maximum(np.abs(fo), 1e-3))[..., :3].any(-1)
+    # one sample whose path took a different branch after fp32 rounding touches its whole 5x5 filter footprint
+    assert bad.sum() <= max(2e-3 * bad.size, 25), (label, int(bad.sum()), bad.size)
+    assert st.samples == ost.samples
+    for f in ("closest_rays", "shade_events", "path_length_sum"):
+        a, c = getattr(st, f), getattr(ost, f)
+        assert abs(a - c) <= 1e-3 * c + 2, (label, f, a, c)
+    sc.close()
+
+
+@pytest.mark.parametrize("scramble", [-1, 0, 5])
+def test_halton_same_sequence_cbox(gpu_lib, oracle_mod, scramble):
+    b = scenes.cbox(width=64, height=48, spp=6, max_depth=8)
+    b.set_sampler("halton", sample_count=6, scramble=scramble)
+    check_same_sequence(gpu_lib, oracle_mod, b, 6, "cbox halton scramble=%d" % scramble)
+
+
+def test_halton_same_sequence_mixed_materials_deep_paths(gpu_lib, oracle_mod):
+    """roughdielectric draws an extra dimension, Russian roulette another one from rrDepth on: the dimension counter
+    of every path has to follow the reference's call order (path.cpp:178,211,285; roughdielectric.cpp:554)."""
+    b = scenes.scene_10m(width=96, height=54, spp=4, nu=24, nv=12, n_obj=12)
+    b.set_integrator(max_depth=12, rr_depth=3, sample_count=4)
+    b.set_sampler("halton", sample_count=4)
+    check_same_sequence(gpu_lib, oracle_mod, b, 4, "mixed halton")
+
+
+def test_halton_same_sequence_delta_lobes_and_passes(gpu_lib, oracle_mod):
+    """Dirac lobes skip the emitter sample (path.cpp:176-178): two dimensions fewer at those vertices.  Rendered in
+    several passes: the sequence is addressed by the global sample index."""
+    b = _glass_mirror_cbox(width=200, height=40, spp=8, max_depth=7)
+    b.set_sampler("halton", sample_count=8)
+    check_same_sequence(gpu_lib, oracle_mod, b, 8, "glass+mirror halton", spp_per_pass=3)
+
+
+def test_ldsampler_statistics_and_variance(gpu_lib, oracle_mod):
+    """ldsampler shuffles with the worker's random stream in the reference, so parity is statistical: mean luminance
+    inside the 3-sigma interval, error no worse than the oracle's ldsampler render, and both clearly better than
+    independent sampling at the same sample count (the point of the plugin, path.cpp:79-81)."""
+    b = scenes.cbox(width=64, height=64, spp=16)
+    sc_ind, orc_ind = gpu_lib.Scene(b), oracle_mod.Oracle(b)
+    ref_stats = orc_ind.render(spp=512, seed=11)
+    ref = orc_ind.film_develop().astype(np.float64)
+    sc_ind.render(spp=16, seed=3)
+    e_ind = rel_mse(sc_ind.film_develop().astype(np.float64), ref)
+    sc_ind.close()
+    b.set_sampler("ldsampler", sample_count=16)
+    sc, orc = gpu_lib.Scene(b), oracle_mod.Oracle(b)
+    st = sc.render(spp=16, seed=7)
+    gpu = sc.film_develop().astype(np.float64)
+    ost = orc.render(spp=16, seed=5)
+    cpu = orc.film_develop().astype(np.float64)
+    n = ref_stats.samples
+    mean_ref = ref_stats.lum_sum / n
+    var = max(ref_stats.lum_sq_sum / n - mean_ref ** 2, 0.0)
+    sigma = np.sqrt(var / st.samples + var / n)
+    assert abs(float((gpu @ LUM).mean()) - float((ref @ LUM).mean())) <= 3 * sigma + 1e-3 * float((ref @ LUM).mean())
+    e_gpu, e_cpu = rel_mse(gpu, ref), rel_mse(cpu, ref)
+    assert e_gpu <= 1.5 * e_cpu + 1e-4, (e_gpu, e_cpu)
+    assert e_gpu < 0.9 * e_ind, (e_gpu, e_ind)
+    for f, tol in (("closest_rays", 0.02), ("shade_events", 0.02), ("path_length_sum", 0.02)):
+        a, c = getattr(st, f) / st.samples, getattr(ost, f) / ost.samples
+        assert abs(a - c) <= tol * c, (f, a, c)
+    # the point sets hold sampleCount entries (ldsampler.cpp:200): asking for more is refused, as the reference asserts
+    with pytest.raises(Exception):
+        sc.render(spp=17, seed=7)
+    sc.close()
+
+
+def test_halton_partition_is_exact(gpu_lib):
+    """Tile- and sample-split renders reproduce the single call: the sequence is a function of (pixel, sample index)."""
+    b = scenes.cbox(width=80, height=48, spp=8)
+    b.set_sampler("halton", sample_count=8)
+    sc = gpu_lib.Scene(b)
+    sc.render(spp=8, seed=3)
+    whole = sc.film_download().astype(np.float64)
+    sc.film_clear()
+    for r in range(2):
+        sc.render(spp=5, seed=3, tile_index=r, tile_count=2, keep_film=True)
+        sc.render(spp=3, seed=3, spp_offset=5, tile_index=r, tile_count=2, keep_film=True)
+    assert np.allclose(sc.film_download().astype(np.float64), whole, rtol=1e-4, atol=1e-4)
+    sc.close()

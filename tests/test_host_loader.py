@@ -322,3 +322,21 @@ def test_missing_file_is_an_io_error():
 def test_unqueried_properties_are_warned_about():
     hs = load('<shape type="rectangle"><float name="radius" value="3"/></shape>')
     assert hs.warnings == ['Unqueried attribute "radius" in element "shape"']
+
+
+def test_sampler_plugins():
+    """independent (independent.cpp:55-60), ldsampler (ldsampler.cpp:75-86: the sample count is rounded up to a
+    power of two with a warning) and halton (halton.cpp:121-130)."""
+    base = '<scene version="0.5.0"><integrator type="path"/><sensor type="perspective">%s</sensor></scene>'
+    hs = hostlib.HostScene.load_string(base % '<sampler type="ldsampler"><integer name="sampleCount" value="20"/></sampler>', "mem.xml")
+    d = hs.desc
+    assert (d.sampler.type, d.sampler.dimension, d.integrator.sample_count) == (abi.SAMPLER_LDSAMPLER, 4, 32)
+    assert hs.warnings == ["Sample count should be a power of two -- rounding to 32"]
+    hs = hostlib.HostScene.load_string(base % '<sampler type="ldsampler"><integer name="sampleCount" value="64"/><integer name="dimension" value="7"/></sampler>', "mem.xml")
+    assert (hs.desc.sampler.dimension, hs.desc.integrator.sample_count, hs.warnings) == (7, 64, [])
+    hs = hostlib.HostScene.load_string(base % '<sampler type="halton"><integer name="sampleCount" value="12"/></sampler>', "mem.xml")
+    assert (hs.desc.sampler.type, hs.desc.sampler.scramble, hs.desc.integrator.sample_count) == (abi.SAMPLER_HALTON, -1, 12)
+    hs = hostlib.HostScene.load_string(base % '<sampler type="halton"><integer name="scramble" value="0"/></sampler>', "mem.xml")
+    assert (hs.desc.sampler.scramble, hs.desc.integrator.sample_count) == (0, 4)
+    hs = hostlib.HostScene.load_string(base % '<sampler type="independent"/>', "mem.xml")
+    assert hs.desc.sampler.type == abi.SAMPLER_INDEPENDENT
