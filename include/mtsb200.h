@@ -129,12 +129,15 @@ typedef struct MtsbIntegrator {
  *              sample_count must be a power of two (the host plugin rounds up, ldsampler.cpp:82-86).
  * halton:      the Halton sequence enumerated per pixel (Gruenschloss et al., halton.cpp:240-330),
  *              deterministic: scramble -1 = Faure permutations (default), 0 = none, any other value =
- *              pseudorandom permutations seeded by it (faure.cpp:34-74).                             */
-enum { MTSB_SAMPLER_INDEPENDENT = 0, MTSB_SAMPLER_LDSAMPLER = 1, MTSB_SAMPLER_HALTON = 2 };
+ *              pseudorandom permutations seeded by it (faure.cpp:34-74).
+ * sobol:       the Sobol' sequence (Joe-Kuo direction numbers) enumerated per pixel (sobol.cpp:204-252,
+ *              sobolseq.h:43-134), deterministic; scramble 0 = none (default), otherwise the XOR mask is
+ *              derived from it by TEA (sobol.cpp:96-102).                                                */
+enum { MTSB_SAMPLER_INDEPENDENT = 0, MTSB_SAMPLER_LDSAMPLER = 1, MTSB_SAMPLER_HALTON = 2, MTSB_SAMPLER_SOBOL = 3 };
 typedef struct MtsbSampler {
     uint32_t type;                  /* MTSB_SAMPLER_*                                  */
     int32_t  dimension;             /* ldsampler `dimension`, default 4 (ldsampler.cpp:78) */
-    int32_t  scramble;              /* halton `scramble`, default -1 (halton.cpp:126)  */
+    int32_t  scramble;              /* halton `scramble`, default -1 (halton.cpp:126); sobol `scramble`, default 0 (sobol.cpp:91) */
     uint32_t _pad;
 } MtsbSampler;
 

@@ -19,7 +19,7 @@ RFILTER_GAUSSIAN, RFILTER_BOX = 0, 1
 TRACE_CLOSEST, TRACE_ANY = 0, 1
 NO_HIT = 0xFFFFFFFF
 RENDER_KEEP_FILM = 1
-SAMPLER_INDEPENDENT, SAMPLER_LDSAMPLER, SAMPLER_HALTON = 0, 1, 2
+SAMPLER_INDEPENDENT, SAMPLER_LDSAMPLER, SAMPLER_HALTON, SAMPLER_SOBOL = 0, 1, 2, 3
 
 
 class Material(C.Structure):

@@ -194,7 +194,7 @@ static int validate(const MtsbSceneDesc *d) {
     if (se.film_width <= 0 || se.film_height <= 0 || se.crop_width <= 0 || se.crop_height <= 0 || se.crop_x < 0 || se.crop_y < 0 ||
         se.crop_x + se.crop_width > se.film_width || se.crop_y + se.crop_height > se.film_height) { set_error("bad film / crop size"); return MTSB_ERR_INVALID; }
     if (!(se.rfilter_radius > 0) || se.rfilter_radius > 7.5f || se.rfilter > MTSB_RFILTER_BOX) { set_error("bad reconstruction filter"); return MTSB_ERR_INVALID; }
-    if (d->sampler.type > MTSB_SAMPLER_HALTON) { set_error("bad sampler type"); return MTSB_ERR_INVALID; }
+    if (d->sampler.type > MTSB_SAMPLER_SOBOL) { set_error("bad sampler type"); return MTSB_ERR_INVALID; }
     if (!(se.fov_x_deg > 0 && se.fov_x_deg < 180) || !(se.near_clip > 0) || !(se.far_clip > se.near_clip)) { set_error("bad sensor parameters"); return MTSB_ERR_INVALID; }
     return MTSB_OK;
 }
@@ -298,6 +298,14 @@ extern "C" int mtsb_scene_create(const MtsbSceneDesc *d, mtsb_scene_t *out) {
                 for (int j = 0; j < 2; ++j) sv.inv_perm2[perms[offsets[0] + j]] = (uint16_t) j;     // faure.cpp:130-135
                 for (int j = 0; j < 3; ++j) sv.inv_perm3[perms[offsets[1] + j]] = (uint16_t) j;
             }
+        }
+        if (d->sampler.type == MTSB_SAMPLER_SOBOL) {
+            const std::vector<uint32_t> mat = sobol_matrices32();
+            std::vector<uint64_t> vdc, vdc_inv;
+            if (!sobol_vdc_tables(sv.sobol_log_res, mat, vdc, vdc_inv)) { set_error("sobol: singular pixel map"); return fail(MTSB_ERR_INVALID); }
+            if ((rc = dev_upload(s, &sv.sobol_mat, mat.data(), mat.size()))) return fail(rc);
+            if ((rc = dev_upload(s, &sv.sobol_vdc, vdc.data(), vdc.size()))) return fail(rc);
+            if ((rc = dev_upload(s, &sv.sobol_vdc_inv, vdc_inv.data(), vdc_inv.size()))) return fail(rc);
         }
         v.sampler_type = sv.type;
         if ((rc = dev_upload(s, &v.sampler, &sv, 1))) return fail(rc);

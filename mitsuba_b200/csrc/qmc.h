@@ -33,7 +33,16 @@ struct SamplerView {
     const uint32_t *perm_offset;    // per dimension: offset of its permutation in `perms`
     const uint16_t *perms;          // digit permutations (faure.cpp), NULL when scramble == 0
     uint16_t inv_perm2[2], inv_perm3[3], _pad;   // inverses of the first two permutations (faure.cpp:77-83)
+    // sobol (sobol.cpp:146-158, sobolseq.h:99-134)
+    uint32_t sobol_log_res;         // m: the film is covered by 2^m x 2^m elementary squares
+    float sobol_res;                // 2^m as a float
+    uint64_t sobol_scramble;        // sobol.cpp:89-102
+    const uint32_t *sobol_mat;      // generator matrices, MTSB_SOBOL_SIZE columns per dimension
+    const uint64_t *sobol_vdc;      // MTSB_SOBOL_SIZE entries: pixel bits flipped by sample-index bit c (sobolseq.h:110-113)
+    const uint64_t *sobol_vdc_inv;  // MTSB_SOBOL_SIZE entries: index bits that set pixel bit c (sobolseq.h:126-128)
 };
+#define MTSB_SOBOL_SIZE 52                    /* sobolseq.h:31 */
+#define MTSB_SOBOL_NUM_DIMENSIONS 1024        /* sobolseq.h:30 */
 
 MTSB_HD float u64_to_float(uint64_t v) {
 #if MTSB_DEVICE_CODE
@@ -110,6 +119,33 @@ MTSB_HD uint64_t halton_pixel_offset(const SamplerView &sv, int px, int py, int 
 MTSB_HD float halton_value(const SamplerView &sv, uint32_t dim, uint64_t index) {
     if (dim >= MTSB_PRIME_TABLE_SIZE) dim = MTSB_PRIME_TABLE_SIZE - 1;    // the reference raises an error here (halton.cpp:362-364)
     return radical_inverse(sv.primes[dim], index, sv.perms ? sv.perms + sv.perm_offset[dim] : (const uint16_t *) 0);
+}
+
+// sobol::sampleSingle (sobolseq.h:43-59)
+MTSB_HD float sobol_value(const SamplerView &sv, uint32_t dim, uint64_t index) {
+    if (dim >= MTSB_SOBOL_NUM_DIMENSIONS) dim = MTSB_SOBOL_NUM_DIMENSIONS - 1;     // the reference raises an error (sobol.cpp:228-230)
+    uint32_t result = (uint32_t) sv.sobol_scramble;
+    for (const uint32_t *col = sv.sobol_mat + (size_t) dim * MTSB_SOBOL_SIZE; index; index >>= 1, ++col)
+        if (index & 1) result ^= *col;
+    return fminf(fmul((float) result, 2.3283064365386963e-10f), MTSB_ONE_MINUS_EPS);
+}
+// sobol::look_up (sobolseq.h:99-134, single precision): index of the frame-th point inside pixel (px, py)
+MTSB_HD uint64_t sobol_look_up(const SamplerView &sv, uint32_t frame, uint32_t px, uint32_t py) {
+    const uint32_t m = sv.sobol_log_res;
+    uint64_t index = (uint64_t) frame << (m << 1);
+    uint64_t delta = 0;
+    for (uint32_t c = 0; frame; frame >>= 1, ++c)
+        if (frame & 1) delta ^= sv.sobol_vdc[c];
+    const uint64_t scramble = (sv.sobol_scramble & 0xFFFFFFFFull) >> (32 - m);
+    uint64_t b = ((((uint64_t) px ^ scramble) << m) | ((uint64_t) py ^ scramble)) ^ delta;
+    for (uint32_t c = 0; b; b >>= 1, ++c)
+        if (b & 1) index ^= sv.sobol_vdc_inv[c];
+    return index;
+}
+// SobolSampler::setSampleIndex (sobol.cpp:204-216)
+MTSB_HD uint64_t sobol_sample_index(const SamplerView &sv, uint32_t sample_index, int px, int py) {
+    if (sv.sobol_log_res > 1 && px >= 0) return sobol_look_up(sv, sample_index, (uint32_t) px, (uint32_t) py);
+    return (uint64_t) sample_index;
 }
 
 // radicalInverse2Single / sobol2Single / sample02Single (include/mitsuba/core/qmc.h:41-59, 79-121)

@@ -7,6 +7,8 @@
 #include <map>
 namespace mtsb {
 
+#include "sobol_joe_kuo.inc"
+
 // the first 1024 primes (qmc.cpp:23-84 holds them as a literal table)
 inline std::vector<uint16_t> qmc_prime_table() {
     std::vector<uint16_t> primes;
@@ -85,6 +87,57 @@ inline void qmc_permutations(int scramble, const std::vector<uint16_t> &primes, 
     }
 }
 
+// Generator matrices of the Sobol' sequence from the Joe-Kuo seeds: column c of dimension d is the direction
+// integer m_c placed below the binary point, v_c = m_c / 2^(c+1), kept to 52 bits and cut to the leading 32
+// (the reference's matrices32 table, sobolseq.cpp:33-53283, is matrices64 >> 20).  Bratley-Fox recurrence:
+// m_c = 2 a_1 m_{c-1} ^ 4 a_2 m_{c-2} ^ ... ^ 2^s m_{c-s} ^ m_{c-s}.
+inline std::vector<uint32_t> sobol_matrices32() {
+    std::vector<uint32_t> out((size_t) MTSB_SOBOL_NUM_DIMENSIONS * MTSB_SOBOL_SIZE);
+    for (int d = 0; d < MTSB_SOBOL_NUM_DIMENSIONS; ++d) {
+        const uint32_t poly = kSobolPoly[d];
+        int s = 0; while ((poly >> (s + 1)) != 0) ++s;
+        uint64_t mc[MTSB_SOBOL_SIZE];
+        for (int c = 0; c < MTSB_SOBOL_SIZE; ++c) {
+            if (s == 0) mc[c] = 1;                                 // dimension 0: van der Corput
+            else if (c < s) mc[c] = kSobolInit[d][c];
+            else {
+                uint64_t v = mc[c - s] ^ (mc[c - s] << s);
+                for (int k = 1; k < s; ++k) if ((poly >> (s - k)) & 1u) v ^= mc[c - k] << k;
+                mc[c] = v;
+            }
+            out[(size_t) d * MTSB_SOBOL_SIZE + c] = (uint32_t) ((mc[c] << (MTSB_SOBOL_SIZE - 1 - c)) >> (MTSB_SOBOL_SIZE - 32));
+        }
+    }
+    return out;
+}
+
+// The tables behind sobol::look_up for one resolution 2^m (the reference stores them for every m,
+// sobolseq.cpp:106537-107997).  Dimension 0 is the bit reversal and dimension 1 the classic Sobol' matrix, so the
+// leading m bits of both (= the pixel) are a linear map A of the low 2m index bits; index bit 2m + c flips the
+// pixel's y bits by the leading m bits of column 2m + c of dimension 1 (vdc[c]); vdc_inv[c] = A^-1 e_c with
+// pixel bit c counted from the least significant bit of (px << m | py).
+inline bool sobol_vdc_tables(uint32_t m, const std::vector<uint32_t> &mat32, std::vector<uint64_t> &vdc, std::vector<uint64_t> &vdc_inv) {
+    vdc.assign(MTSB_SOBOL_SIZE, 0); vdc_inv.assign(MTSB_SOBOL_SIZE, 0);
+    if (m == 0 || 2 * m > MTSB_SOBOL_SIZE) return m == 0;
+    // 52-bit columns of dimension 1 are not kept; its matrix is Pascal's triangle mod 2 and m <= 26 <= 32 leading bits suffice
+    auto top = [&](uint32_t dim, uint32_t col) -> uint64_t { return (uint64_t) (mat32[(size_t) dim * MTSB_SOBOL_SIZE + col] >> (32 - m)); };
+    for (uint32_t c = 0; 2 * m + c < MTSB_SOBOL_SIZE; ++c) vdc[c] = top(1, 2 * m + c);
+    // A: column j (index bit j) -> pixel word (px << m | py)
+    const uint32_t n = 2 * m;
+    std::vector<uint64_t> a(n), inv(n);
+    for (uint32_t j = 0; j < n; ++j) { a[j] = (top(0, j) << m) | top(1, j); inv[j] = 1ull << j; }
+    // Gauss-Jordan over GF(2) on columns: reduce [A | I] so that A becomes the identity; inv then holds A^-1 by columns
+    for (uint32_t r = 0; r < n; ++r) {
+        uint32_t piv = r;
+        while (piv < n && !((a[piv] >> r) & 1ull)) ++piv;
+        if (piv == n) return false;
+        std::swap(a[piv], a[r]); std::swap(inv[piv], inv[r]);
+        for (uint32_t j = 0; j < n; ++j) if (j != r && ((a[j] >> r) & 1ull)) { a[j] ^= a[r]; inv[j] ^= inv[r]; }
+    }
+    for (uint32_t c = 0; c < n; ++c) vdc_inv[c] = inv[c];
+    return true;
+}
+
 inline void extended_gcd(uint64_t a, uint64_t b, int64_t &x, int64_t &y) {      // halton.cpp:217-227
     if (b == 0) { x = 1; y = 0; return; }
     int64_t d = (int64_t) (a / b), x_, y_;
@@ -122,6 +175,17 @@ inline bool sampler_view_init(const MtsbSampler &sd, int sample_count, int crop_
             int64_t r = x % n; if (r < 0) r += n;
             sv.mult_inv[i] = (uint64_t) r;
         }
+        return true;
+    }
+    if (sd.type == MTSB_SAMPLER_SOBOL) {                // sobol.cpp:89-102, 146-158
+        uint64_t scramble = (uint64_t) (uint32_t) sd.scramble;          // props.getSize("scramble", 0)
+        if (sd.scramble < 0) { *err = "sobol: 'scramble' must not be negative"; return false; }
+        if (scramble) scramble = sample_tea((uint32_t) scramble, (uint32_t) (scramble >> 32));
+        sv.sobol_scramble = scramble;
+        uint32_t res = (uint32_t) (crop_w > crop_h ? crop_w : crop_h), r = 1, l = 0;
+        while (r < res) { r <<= 1; ++l; }                               // math::roundToPowerOfTwo / log2i
+        sv.sobol_log_res = l; sv.sobol_res = (float) r;
+        if (2 * l > MTSB_SOBOL_SIZE) { *err = "sobol: film resolution too large"; return false; }
         return true;
     }
     *err = "unknown sampler type";

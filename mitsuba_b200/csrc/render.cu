@@ -97,6 +97,19 @@ __device__ __noinline__ QmcDraw qmc_draw(const SamplerView *svp, uint64_t seed, 
         }
         if (dim > 0xFFFu) dim = 0xFFFu;
         r.fl = (fl & ~PF_DIM_MASK) | (dim << PF_DIM_SHIFT);
+    } else if (sv.type == MTSB_SAMPLER_SOBOL) {
+        const uint64_t index = sobol_sample_index(sv, s_global, px_abs, py_abs);
+        uint32_t dim = fl >> PF_DIM_SHIFT;
+        r.a = sobol_value(sv, dim++, index);
+        if (n == 2) {
+            r.b = sobol_value(sv, dim++, index);
+            if (dim == 2 && index != (uint64_t) s_global) {      // sobol.cpp:243-245: the first two dimensions address the pixel
+                r.a = fsub(fmul(r.a, sv.sobol_res), (float) px_abs);
+                r.b = fsub(fmul(r.b, sv.sobol_res), (float) py_abs);
+            }
+        }
+        if (dim > 0xFFFu) dim = 0xFFFu;
+        r.fl = (fl & ~PF_DIM_MASK) | (dim << PF_DIM_SHIFT);
     } else if (sv.type == MTSB_SAMPLER_LDSAMPLER) {
         const uint64_t pixel = ((uint64_t) (uint32_t) py_abs << 32) | (uint64_t) (uint32_t) px_abs;
         uint32_t d1 = (fl >> PF_DIM_SHIFT) & 63u, d2 = (fl >> (PF_DIM_SHIFT + 6)) & 63u;
@@ -498,7 +511,9 @@ __global__ void __launch_bounds__(256) k_splat(SceneView sc, PathBuffers pb, Pas
     const float r = sc.filter_radius;
     const int fsx = sc.film_w + 2 * b;
     unsigned long long n_bad = 0;
-    for (uint32_t c0 = 0; c0 < ps.spp_pass; c0 += (uint32_t) chunk) {
+    // gridDim.y CTAs share a tile: each takes every gridDim.y-th staging round of the pass (a rank of a multi-GPU
+    // job renders few tiles at many samples; one CTA per tile would leave most SMs idle)
+    for (uint32_t c0 = blockIdx.y * (uint32_t) chunk; c0 < ps.spp_pass; c0 += gridDim.y * (uint32_t) chunk) {
         const int nc = min(chunk, (int) (ps.spp_pass - c0));
         // ---- stage: slot (pixel in Morton order, sample) -> smem[sample][y][x] ----
         for (int i = threadIdx.x; i < nc * MTSB_TILE * MTSB_TILE; i += blockDim.x) {
@@ -739,7 +754,14 @@ static int lane_start(Scene *s, Lane &L, const Pass &p, const RenderConst &rcst,
 static void lane_finish(Scene *s, Lane &L, size_t splat_smem) {
     L.timer->begin(ST_SPLAT);
     k_pass_end<<<1, 1, 0, L.st>>>(*L.pb);
-    k_splat<<<L.pass.ps.n_tiles, 256, splat_smem, L.st>>>(s->v, *L.pb, L.pass.ps, s->d_film_bad);
+    {
+        // enough CTAs for ~8 per SM: split the samples of a tile over gridDim.y CTAs when the pass has few tiles
+        const uint32_t rounds = (L.pass.ps.spp_pass + MTSB_SPLAT_CHUNK - 1) / MTSB_SPLAT_CHUNK;
+        const uint32_t want = (uint32_t) device_sm_count() * 8u;
+        uint32_t split = (want + L.pass.ps.n_tiles - 1) / L.pass.ps.n_tiles;
+        split = std::max(1u, std::min(std::min(split, rounds), 64u));
+        k_splat<<<dim3(L.pass.ps.n_tiles, split), 256, splat_smem, L.st>>>(s->v, *L.pb, L.pass.ps, s->d_film_bad);
+    }
     s->launches += 2;
     L.timer->end();
     L.busy = false;

@@ -82,8 +82,14 @@ Sampler::Sampler(const Properties &p) : ConfigurableObject(p) {
         sampleCount = p.getInteger("sampleCount", 4);
         scramble = p.getInteger("scramble", -1);
         seed = 1004;
+    } else if (type == "sobol") {                    // sobol.cpp:85-107
+        kind = MTSB_SAMPLER_SOBOL;
+        sampleCount = p.getInteger("sampleCount", 4);
+        scramble = p.getInteger("scramble", 0);
+        seed = 1004;
+        if (scramble < 0) error("sobol: 'scramble' must not be negative");
     } else {
-        error("Plugin \"" + type + "\" not found -- the B200 path implements the samplers independent (counter-based streams), ldsampler and halton.");
+        error("Plugin \"" + type + "\" not found -- the B200 path implements the samplers independent (counter-based streams), ldsampler, halton and sobol.");
     }
     if (sampleCount <= 0) error(type + ": 'sampleCount' must be positive");
 }

@@ -222,11 +222,15 @@ class SceneBuilder:
         ig.strict_normals, ig.hide_emitters = int(strict_normals), int(hide_emitters)
         ig.sample_count = int(sample_count)
 
-    def set_sampler(self, kind="independent", sample_count=None, dimension=4, scramble=-1):
+    def set_sampler(self, kind="independent", sample_count=None, dimension=4, scramble=None):
         """Sample generator: `independent`, `ldsampler` (sample count rounded up to a power of two,
-        src/samplers/ldsampler.cpp:75-86) or `halton` (src/samplers/halton.cpp:121-130)."""
-        kinds = {"independent": abi.SAMPLER_INDEPENDENT, "ldsampler": abi.SAMPLER_LDSAMPLER, "halton": abi.SAMPLER_HALTON}
+        src/samplers/ldsampler.cpp:75-86) `halton` (src/samplers/halton.cpp:121-130)
+        or `sobol` (src/samplers/sobol.cpp:85-107)."""
+        kinds = {"independent": abi.SAMPLER_INDEPENDENT, "ldsampler": abi.SAMPLER_LDSAMPLER, "halton": abi.SAMPLER_HALTON,
+                 "sobol": abi.SAMPLER_SOBOL}
         self.sampler.type = kinds[kind]
+        if scramble is None:
+            scramble = 0 if kind == "sobol" else -1          # sobol.cpp:91, halton.cpp:126
         self.sampler.dimension, self.sampler.scramble = int(dimension), int(scramble)
         if sample_count is not None:
             self.integrator.sample_count = int(sample_count)

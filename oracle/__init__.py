@@ -69,6 +69,12 @@ def lib():
         L.orc_microfacet.argtypes = [C.c_int, C.c_float, C.c_float, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_warp.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
         L.orc_halton_sequence.argtypes = [C.c_int] * 9 + [C.c_void_p]
+        L.orc_sobol_sequence.argtypes = [C.c_int] * 9 + [C.c_void_p]
+        L.orc_sobol_matrix32.argtypes = [C.c_uint32, C.c_uint32]
+        L.orc_sobol_matrix32.restype = C.c_uint32
+        L.orc_sobol_vdc.argtypes = [C.c_uint32, C.c_void_p, C.c_void_p]
+        L.orc_sobol_sample.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32]
+        L.orc_sobol_sample.restype = C.c_float
         L.orc_radical_inverse.argtypes = [C.c_int, C.c_uint64]
         L.orc_radical_inverse.restype = C.c_float
         L.orc_radical_inverse_incremental.argtypes = [C.c_int, C.c_float]

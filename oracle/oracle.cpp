@@ -455,6 +455,10 @@ int orc_render2(void *h, int spp, uint64_t seed, int nthreads, int max_blocks, O
                 orc::HaltonSampler *hs = new orc::HaltonSampler(perms.get());
                 hs->setFilmResolution(sc->sd.sensor.crop_width, sc->sd.sensor.crop_height, true);       // integrator.cpp:38-42
                 qmc.reset(hs);
+            } else if (smp.type == MTSB_SAMPLER_SOBOL) {
+                orc::SobolSampler *ss = new orc::SobolSampler((uint64_t) (uint32_t) smp.scramble);
+                ss->setFilmResolution(sc->sd.sensor.crop_width, sc->sd.sensor.crop_height, true);
+                qmc.reset(ss);
             } else if (smp.type == MTSB_SAMPLER_LDSAMPLER) {
                 qmc.reset(new orc::LowDiscrepancySampler((size_t) std::max(1, sc->sd.integrator.sample_count), (size_t) std::max(0, smp.dimension), &rng));
             }
@@ -573,6 +577,26 @@ int orc_halton_sequence(int resX, int resY, int scramble, int px, int py, int fi
     } catch (const std::exception &e) { g_err = e.what(); return MTSB_ERR_INVALID; }
     return MTSB_OK;
 }
+// Sobol sampler driven the same way
+int orc_sobol_sequence(int resX, int resY, int scramble, int px, int py, int firstSample, int nSamples, int n2D, int n1D, float *out) {
+    try {
+        orc::SobolSampler ss((uint64_t) (uint32_t) scramble);
+        if (resX > 0) ss.setFilmResolution(resX, resY, true);
+        ss.generate(px, py);
+        for (int j = 0; j < nSamples; ++j) {
+            ss.setSampleIndex((size_t) (firstSample + j));
+            for (int k = 0; k < n2D; ++k) { ss.next2D(out); out += 2; }
+            for (int k = 0; k < n1D; ++k) *out++ = ss.next1D();
+        }
+    } catch (const std::exception &e) { g_err = e.what(); return MTSB_ERR_INVALID; }
+    return MTSB_OK;
+}
+uint32_t orc_sobol_matrix32(uint32_t dimension, uint32_t column) { return orc::SobolTables::get().matrices32[(size_t) dimension * 52 + column]; }
+void orc_sobol_vdc(uint32_t m, uint64_t *vdc52, uint64_t *inv52) {
+    std::vector<uint64_t> a, b; orc::SobolTables::get().pixelTables(m, a, b);
+    std::copy(a.begin(), a.end(), vdc52); std::copy(b.begin(), b.end(), inv52);
+}
+float orc_sobol_sample(uint64_t index, uint32_t dimension, uint32_t scramble) { return orc::sobolSampleSingle(index, dimension, scramble); }
 float orc_radical_inverse(int base, uint64_t i) { return orc::radicalInverse(base, i); }
 float orc_radical_inverse_incremental(int base, float x) { return orc::radicalInverseIncremental(base, x); }
 float orc_radical_inverse_fast(int baseIndex, uint64_t index) { return orc::radicalInverseFast(baseIndex, index); }

@@ -259,4 +259,111 @@ struct LowDiscrepancySampler : QmcSampler {
     }
 };
 
+// ---- Sobol' sequence: sobolseq.h:29-134 (sampleSingle, look_up) and SobolSampler, sobol.cpp:85-252 ----
+// The reference carries the expanded generator matrices and the per-resolution pixel tables as literal data
+// (sobolseq.cpp, 108 000 lines).  They are functions of the Joe-Kuo seed numbers, so they are rebuilt here from the
+// seeds (../mitsuba_b200/csrc/sobol_joe_kuo.inc holds only those seeds, generated from the public data set) with the
+// textbook direction-number recurrence v_c = v_{c-s} ^ (v_{c-s} >> s) ^ sum_k a_k v_{c-k}; tests/golden/qmc_sobol.npz
+// pins every entry of the result against the reference's own tables.
+namespace sobol_data {
+#include "../mitsuba_b200/csrc/sobol_joe_kuo.inc"
+}
+struct SobolTables {
+    static const uint32_t numDimensions = 1024, size = 52;
+    std::vector<uint64_t> matrices64;                 // direction numbers scaled by 2^52
+    std::vector<uint32_t> matrices32;                 // their leading 32 bits
+    SobolTables() : matrices64((size_t) numDimensions * size), matrices32((size_t) numDimensions * size) {
+        for (uint32_t d = 0; d < numDimensions; ++d) {
+            uint64_t *v = &matrices64[(size_t) d * size];
+            const uint32_t poly = sobol_data::kSobolPoly[d];
+            uint32_t s = 0; while (poly >> (s + 1)) ++s;
+            for (uint32_t c = 0; c < size; ++c) {
+                if (s == 0) v[c] = 1ull << (size - 1 - c);
+                else if (c < s) v[c] = (uint64_t) sobol_data::kSobolInit[d][c] << (size - 1 - c);
+                else {
+                    v[c] = v[c - s] ^ (v[c - s] >> s);
+                    for (uint32_t k = 1; k < s; ++k) if ((poly >> (s - k)) & 1u) v[c] ^= v[c - k];
+                }
+                matrices32[(size_t) d * size + c] = (uint32_t) (v[c] >> (size - 32));
+            }
+        }
+    }
+    // pixel tables of one resolution 2^m: vdc[c] = y bits flipped by index bit 2m+c; inv[c] = low index bits that
+    // set bit c of (px << m | py).  Built by solving the 2m x 2m system bit by bit (row elimination).
+    void pixelTables(uint32_t m, std::vector<uint64_t> &vdc, std::vector<uint64_t> &inv) const {
+        vdc.assign(size, 0); inv.assign(size, 0);
+        if (m == 0) return;
+        const uint32_t n = 2 * m;
+        auto word = [&](uint32_t col) { return ((matrices64[col] >> (size - m)) << m) | (matrices64[size + col] >> (size - m)); };
+        for (uint32_t c = 0; n + c < size; ++c) vdc[c] = matrices64[size + n + c] >> (size - m);
+        // rows[r]: bit j = coefficient of index bit j in output bit r; augmented with the identity in the high half
+        std::vector<unsigned __int128> rows(n);
+        for (uint32_t r = 0; r < n; ++r) {
+            unsigned __int128 row = (unsigned __int128) 1 << (64 + r);
+            for (uint32_t j = 0; j < n; ++j) if ((word(j) >> r) & 1ull) row |= (unsigned __int128) 1 << j;
+            rows[r] = row;
+        }
+        for (uint32_t j = 0; j < n; ++j) {
+            uint32_t p = j; while (p < n && !((rows[p] >> j) & 1)) ++p;
+            if (p == n) throw std::runtime_error("sobol: singular pixel map");
+            std::swap(rows[p], rows[j]);
+            for (uint32_t r = 0; r < n; ++r) if (r != j && ((rows[r] >> j) & 1)) rows[r] ^= rows[j];
+        }
+        // now index bit j = sum over output bits r of rows[j].high[r] * out_r  =>  column c of the inverse
+        for (uint32_t c = 0; c < n; ++c) { uint64_t col = 0; for (uint32_t j = 0; j < n; ++j) if ((rows[j] >> (64 + c)) & 1) col |= 1ull << j; inv[c] = col; }
+    }
+    static const SobolTables &get() { static SobolTables t; return t; }
+};
+// sobolseq.h:43-59
+inline float sobolSampleSingle(uint64_t index, uint32_t dimension, uint32_t scramble = 0) {
+    const SobolTables &t = SobolTables::get();
+    uint32_t result = scramble;
+    for (uint32_t i = dimension * SobolTables::size; index; index >>= 1, ++i) if (index & 1) result ^= t.matrices32[i];
+    return std::min(result * (1.0f / (1ULL << 32)), 0.999999940395355225f);
+}
+// sobolseq.h:99-134 (single precision branch)
+inline uint64_t sobolLookUp(uint32_t m, uint32_t frame, uint32_t px, uint32_t py, uint64_t scramble, const std::vector<uint64_t> &vdc, const std::vector<uint64_t> &inv) {
+    const uint32_t m2 = m << 1;
+    uint64_t index = uint64_t(frame) << m2, delta = 0;
+    for (uint32_t c = 0; frame; frame >>= 1, ++c) if (frame & 1) delta ^= vdc[c];
+    scramble = (scramble & 0xFFFFFFFF) >> (32 - m);
+    uint64_t b = (((uint64_t) (px ^ scramble) << m) | (py ^ scramble)) ^ delta;
+    for (uint32_t c = 0; b; b >>= 1, ++c) if (b & 1) index ^= inv[c];
+    return index;
+}
+struct SobolSampler : QmcSampler {
+    uint32_t dimension = 0, logResolution = 0; uint64_t scramble, sobolSampleIndex = 0; float resolution = 1;
+    int pixelPosition[2] = {0, 0}; size_t sampleIndex = 0;
+    std::vector<uint64_t> vdc, inv;
+    explicit SobolSampler(uint64_t scrambleProp) : scramble(scrambleProp) {             // sobol.cpp:85-107
+        if (scramble) { union { uint64_t ui64; uint32_t v[2]; } u = {scramble}; scramble = sampleTEA(u.v[0], u.v[1]); }
+    }
+    void setFilmResolution(int resX, int resY, bool bucketed) {                         // :146-158
+        if (!bucketed) { resolution = 1; logResolution = 0; }
+        else {
+            uint32_t r = 1, l = 0; while (r < (uint32_t) std::max(resX, resY)) { r <<= 1; ++l; }
+            resolution = (float) r; logResolution = l;
+        }
+        SobolTables::get().pixelTables(logResolution, vdc, inv);
+    }
+    void generate(int px, int py) override { pixelPosition[0] = px; pixelPosition[1] = py; setSampleIndex(0); }   // :172-175
+    void setSampleIndex(size_t i) override {                                            // :204-216
+        dimension = 0; sampleIndex = i;
+        if (logResolution > 1 && pixelPosition[0] >= 0)
+            sobolSampleIndex = sobolLookUp(logResolution, (uint32_t) sampleIndex, (uint32_t) pixelPosition[0], (uint32_t) pixelPosition[1], scramble, vdc, inv);
+        else sobolSampleIndex = (uint64_t) sampleIndex;
+    }
+    float draw() {
+        if (dimension >= SobolTables::numDimensions) throw std::runtime_error("Lookup dimension exceeds the direction number table size!");
+        return sobolSampleSingle(sobolSampleIndex, dimension++, (uint32_t) scramble);
+    }
+    float next1D() override { return draw(); }                                          // :218-229
+    void next2D(float out[2]) override {                                                // :231-252
+        if (dimension == 0 && sobolSampleIndex != (uint64_t) sampleIndex) {
+            out[0] = draw() * resolution - pixelPosition[0];
+            out[1] = draw() * resolution - pixelPosition[1];
+        } else { out[0] = draw(); out[1] = draw(); }
+    }
+};
+
 }  // namespace orc

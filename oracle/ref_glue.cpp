@@ -29,6 +29,7 @@
 #include "src/bsdfs/microfacet.h"
 #include <mitsuba/core/qmc.h>
 #include "src/samplers/faure.h"
+#include "src/samplers/sobolseq.h"
 #include "../include/mtsb200.h"
 #include <vector>
 
@@ -297,5 +298,11 @@ void ref_sample02(uint32_t n, uint32_t *scramble2, float *out2) { Point2f p = sa
 float ref_radical_inverse2(uint32_t n, uint32_t scramble) { return radicalInverse2Single(n, scramble); }
 float ref_sobol2(uint32_t n, uint32_t scramble) { return sobol2Single(n, scramble); }
 uint64_t ref_sample_tea(uint32_t v0, uint32_t v1, int rounds) { return sampleTEA(v0, v1, rounds); }
+
+// ---- Sobol' sequence (src/samplers/sobolseq.h, tables in sobolseq.cpp) ----
+float ref_sobol_sample(uint64_t index, uint32_t dimension, uint64_t scramble) { return sobol::sample(index, dimension, scramble); }
+uint64_t ref_sobol_look_up(uint32_t m, uint32_t frame, uint32_t px, uint32_t py, uint64_t scramble) { return sobol::look_up(m, frame, px, py, scramble); }
+uint32_t ref_sobol_matrix32(uint32_t dimension, uint32_t column) { return sobol::Matrices::matrices32[dimension * sobol::Matrices::size + column]; }
+uint64_t ref_sobol_vdc(uint32_t m, uint32_t column, int inverse) { return inverse ? sobol::Matrices::vdc_sobol_matrices_inv[m - 1][column] : sobol::Matrices::vdc_sobol_matrices[m - 1][column]; }
 
 }  // extern "C"

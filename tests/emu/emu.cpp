@@ -163,6 +163,35 @@ extern "C" int emu_halton_sequence(int resX, int resY, int scramble, int px, int
     }
     return 0;
 }
+extern "C" int emu_sobol_sequence(int resX, int resY, int scramble, int px, int py, int firstSample, int nSamples, int n2D, int n1D, float *out) {
+    MtsbSampler sd; sd.type = MTSB_SAMPLER_SOBOL; sd.dimension = 0; sd.scramble = scramble; sd._pad = 0;
+    SamplerView sv; const char *err = "";
+    if (!sampler_view_init(sd, 1, resX, resY, sv, &err)) return 1;
+    static const std::vector<uint32_t> mat = sobol_matrices32();
+    std::vector<uint64_t> vdc, vdc_inv;
+    if (!sobol_vdc_tables(sv.sobol_log_res, mat, vdc, vdc_inv)) return 2;
+    sv.sobol_mat = mat.data(); sv.sobol_vdc = vdc.data(); sv.sobol_vdc_inv = vdc_inv.data();
+    for (int j = 0; j < nSamples; ++j) {
+        const uint32_t s_global = (uint32_t) (firstSample + j);
+        const uint64_t index = sobol_sample_index(sv, s_global, px, py);
+        uint32_t dim = 0;
+        for (int k = 0; k < n2D; ++k) {
+            float a = sobol_value(sv, dim++, index), b = sobol_value(sv, dim++, index);
+            if (dim == 2 && index != (uint64_t) s_global) { a = fsub(fmul(a, sv.sobol_res), (float) px); b = fsub(fmul(b, sv.sobol_res), (float) py); }
+            *out++ = a; *out++ = b;
+        }
+        for (int k = 0; k < n1D; ++k) *out++ = sobol_value(sv, dim++, index);
+    }
+    return 0;
+}
+extern "C" uint32_t emu_sobol_matrix32(uint32_t dimension, uint32_t column) { static const std::vector<uint32_t> mat = sobol_matrices32(); return mat[(size_t) dimension * MTSB_SOBOL_SIZE + column]; }
+extern "C" int emu_sobol_vdc(uint32_t m, uint64_t *vdc52, uint64_t *inv52) {
+    static const std::vector<uint32_t> mat = sobol_matrices32();
+    std::vector<uint64_t> a, b;
+    if (!sobol_vdc_tables(m, mat, a, b)) return 1;
+    std::copy(a.begin(), a.end(), vdc52); std::copy(b.begin(), b.end(), inv52);
+    return 0;
+}
 extern "C" float emu_radical_inverse(uint32_t base, uint64_t index, const uint16_t *perm) { return radical_inverse(base, index, perm); }
 extern "C" int emu_permutation(int scramble, int baseIndex, uint16_t *out) {
     static int cached = 0; static std::vector<uint16_t> perms; static std::vector<uint32_t> offsets;

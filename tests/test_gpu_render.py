@@ -228,6 +228,15 @@ def test_halton_same_sequence_delta_lobes_and_passes(gpu_lib, oracle_mod):
     check_same_sequence(gpu_lib, oracle_mod, b, 8, "glass+mirror halton", spp_per_pass=3)
 
 
+@pytest.mark.parametrize("scramble", [0, 9])
+def test_sobol_same_sequence(gpu_lib, oracle_mod, scramble):
+    """sobol is deterministic too (sobol.cpp:204-252): per-pixel enumeration of the Joe-Kuo sequence."""
+    b = scenes.scene_10m(width=96, height=54, spp=5, nu=24, nv=12, n_obj=12)
+    b.set_integrator(max_depth=9, rr_depth=3, sample_count=5)
+    b.set_sampler("sobol", sample_count=5, scramble=scramble)
+    check_same_sequence(gpu_lib, oracle_mod, b, 5, "mixed sobol scramble=%d" % scramble, spp_per_pass=2)
+
+
 def test_ldsampler_statistics_and_variance(gpu_lib, oracle_mod):
     """ldsampler shuffles with the worker's random stream in the reference, so parity is statistical: mean luminance
     inside the 3-sigma interval, error no worse than the oracle's ldsampler render, and both clearly better than

@@ -295,7 +295,7 @@ ERRORS = [
      "'nearClip' parameter must be greater than zero"),
     ('<scene version="0.5.0"><integrator type="path"/><sensor type="perspective"><film type="hdrfilm"><rfilter type="lanczos"/></film>'
      '</sensor></scene>', 'Plugin "lanczos" not found'),
-    ('<scene version="0.5.0"><integrator type="path"/><sensor type="perspective"><sampler type="sobol"/></sensor></scene>', 'Plugin "sobol" not found'),
+    ('<scene version="0.5.0"><integrator type="path"/><sensor type="perspective"><sampler type="stratified"/></sensor></scene>', 'Plugin "stratified" not found'),
     (HEAD + '<shape type="rectangle"><float name="a" value="1"/><float name="a" value="2"/></shape></scene>', "specified multiple times"),
     (HEAD + '<shape type="obj"><string name="filename" value="does_not_exist.obj"/></shape></scene>', "not found"),
     (HEAD + '<shape type="rectangle"><medium type="homogeneous"/></shape></scene>', "participating media"),
@@ -338,5 +338,7 @@ def test_sampler_plugins():
     assert (hs.desc.sampler.type, hs.desc.sampler.scramble, hs.desc.integrator.sample_count) == (abi.SAMPLER_HALTON, -1, 12)
     hs = hostlib.HostScene.load_string(base % '<sampler type="halton"><integer name="scramble" value="0"/></sampler>', "mem.xml")
     assert (hs.desc.sampler.scramble, hs.desc.integrator.sample_count) == (0, 4)
+    hs = hostlib.HostScene.load_string(base % '<sampler type="sobol"><integer name="sampleCount" value="9"/><integer name="scramble" value="3"/></sampler>', "mem.xml")
+    assert (hs.desc.sampler.type, hs.desc.sampler.scramble, hs.desc.integrator.sample_count) == (abi.SAMPLER_SOBOL, 3, 9)
     hs = hostlib.HostScene.load_string(base % '<sampler type="independent"/>', "mem.xml")
     assert hs.desc.sampler.type == abi.SAMPLER_INDEPENDENT
