@@ -39,7 +39,7 @@
 extern "C" {
 #endif
 
-#define MTSB_ABI_VERSION 3
+#define MTSB_ABI_VERSION 4
 
 /* ---- status codes ---------------------------------------------------- */
 enum {
@@ -87,8 +87,9 @@ typedef struct MtsbShape {
     uint32_t has_texcoords;
 } MtsbShape;                        /* 32 bytes */
 
-/* ---- emitters (reference: src/emitters/{area,point,constant}.cpp) ----- */
-enum { MTSB_EMITTER_AREA = 0, MTSB_EMITTER_POINT = 1, MTSB_EMITTER_CONSTANT = 2 };
+/* ---- emitters (reference: src/emitters/{area,point,constant,envmap}.cpp) ----- */
+enum { MTSB_EMITTER_AREA = 0, MTSB_EMITTER_POINT = 1, MTSB_EMITTER_CONSTANT = 2,
+       MTSB_EMITTER_ENVMAP = 3 /* image data in MtsbSceneDesc::envmap; `radiance` unused */ };
 
 typedef struct MtsbEmitter {
     uint32_t type;
@@ -98,6 +99,18 @@ typedef struct MtsbEmitter {
     float    sampling_weight;       /* Emitter::getSamplingWeight, default 1           */
     float    _pad[3];
 } MtsbEmitter;                      /* 48 bytes */
+
+/* Latitude-longitude environment map (envmap.cpp): the image is stored in half precision on the device as the
+ * reference stores it (envmap.cpp:101-103), looked up bilinearly at level 0 (repeat in u, clamp in v) and importance
+ * sampled through marginal / conditional CDFs over luminance x sin(theta) (envmap.cpp:260-329, 567-600).           */
+typedef struct MtsbEnvmap {
+    int32_t width, height;          /* < 65536 each (envmap.cpp:164-166)                */
+    const float *rgb;               /* width*height*3 linear RGB, row-major, row 0 = +Y pole */
+    float to_world[16];             /* emitter `toWorld`, row-major; only its linear part acts on directions */
+    float to_local[16];             /* its inverse (Transform keeps both, transform.h)  */
+    float scale;                    /* `scale`, default 1 (envmap.cpp:188)              */
+    uint32_t _pad[3];
+} MtsbEnvmap;
 
 /* ---- sensor + film + filter ------------------------------------------- */
 enum { MTSB_RFILTER_GAUSSIAN = 0, MTSB_RFILTER_BOX = 1 };
@@ -155,6 +168,7 @@ typedef struct MtsbSceneDesc {
     MtsbSensor      sensor;
     MtsbIntegrator  integrator;
     MtsbSampler     sampler;        /* zero-initialised = independent                  */
+    const MtsbEnvmap *envmap;       /* required iff an emitter has type MTSB_EMITTER_ENVMAP, else NULL */
 } MtsbSceneDesc;
 
 /* ---- rays and hit records (cfg 4 and the parity tests) ---------------- */

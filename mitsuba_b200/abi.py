@@ -8,13 +8,13 @@ import ctypes as C
 
 import numpy as np
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 OK, ERR_INVALID, ERR_NO_DEVICE, ERR_CUDA, ERR_CANCELLED, ERR_IO, ERR_PARSE = range(7)
 BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_ROUGHDIELECTRIC, BSDF_NULL, BSDF_DIELECTRIC, BSDF_CONDUCTOR, BSDF_PLASTIC = range(7)
 DISTR_BECKMANN, DISTR_GGX = 0, 1
 MAT_TWOSIDED, MAT_SAMPLE_VISIBLE, MAT_NONLINEAR = 1, 2, 4
-EMITTER_AREA, EMITTER_POINT, EMITTER_CONSTANT = 0, 1, 2
+EMITTER_AREA, EMITTER_POINT, EMITTER_CONSTANT, EMITTER_ENVMAP = 0, 1, 2, 3
 RFILTER_GAUSSIAN, RFILTER_BOX = 0, 1
 TRACE_CLOSEST, TRACE_ANY = 0, 1
 NO_HIT = 0xFFFFFFFF
@@ -56,13 +56,19 @@ class Sampler(C.Structure):
     _fields_ = [("type", C.c_uint32), ("dimension", C.c_int32), ("scramble", C.c_int32), ("_pad", C.c_uint32)]
 
 
+class Envmap(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("rgb", C.POINTER(C.c_float)), ("to_world", C.c_float * 16),
+                ("to_local", C.c_float * 16), ("scale", C.c_float), ("_pad", C.c_uint32 * 3)]
+
+
 class SceneDesc(C.Structure):
     _fields_ = [("abi_version", C.c_uint32), ("n_shapes", C.c_uint32), ("n_materials", C.c_uint32),
                 ("n_emitters", C.c_uint32), ("n_vertices", C.c_uint64), ("n_tris", C.c_uint64),
                 ("shapes", C.POINTER(Shape)), ("materials", C.POINTER(Material)), ("emitters", C.POINTER(Emitter)),
                 ("positions", C.POINTER(C.c_float)), ("normals", C.POINTER(C.c_float)),
                 ("texcoords", C.POINTER(C.c_float)), ("indices", C.POINTER(C.c_uint32)),
-                ("sensor", Sensor), ("integrator", Integrator), ("sampler", Sampler)]
+                ("sensor", Sensor), ("integrator", Integrator), ("sampler", Sampler),
+                ("envmap", C.POINTER(Envmap))]
 
 
 class RenderParams(C.Structure):

@@ -186,9 +186,14 @@ static int validate(const MtsbSceneDesc *d) {
     int n_env = 0;
     for (uint32_t i = 0; i < d->n_emitters; ++i) {
         const MtsbEmitter &e = d->emitters[i];
-        if (e.type > MTSB_EMITTER_CONSTANT) { set_error("bad emitter type"); return MTSB_ERR_INVALID; }
+        if (e.type > MTSB_EMITTER_ENVMAP) { set_error("bad emitter type"); return MTSB_ERR_INVALID; }
+        if (e.type == MTSB_EMITTER_ENVMAP) {
+            const MtsbEnvmap *em = d->envmap;
+            if (!em || !em->rgb || em->width <= 0 || em->height <= 0) { set_error("envmap emitter without image data"); return MTSB_ERR_INVALID; }
+            if (em->width > 0xFFFF || em->height > 0xFFFF) { set_error("Environment maps images must be smaller than 65536 pixels in width and height"); return MTSB_ERR_INVALID; }
+        }
         if (e.type == MTSB_EMITTER_AREA && (e.shape < 0 || e.shape >= (int32_t) d->n_shapes)) { set_error("area emitter without a shape"); return MTSB_ERR_INVALID; }
-        if (e.type == MTSB_EMITTER_CONSTANT && ++n_env > 1) { set_error("only one environment emitter is allowed (scene.cpp:575-579)"); return MTSB_ERR_INVALID; }
+        if ((e.type == MTSB_EMITTER_CONSTANT || e.type == MTSB_EMITTER_ENVMAP) && ++n_env > 1) { set_error("only one environment emitter is allowed (scene.cpp:575-579)"); return MTSB_ERR_INVALID; }
     }
     const MtsbSensor &se = d->sensor;
     if (se.film_width <= 0 || se.film_height <= 0 || se.crop_width <= 0 || se.crop_height <= 0 || se.crop_x < 0 || se.crop_y < 0 ||
@@ -243,7 +248,7 @@ extern "C" int mtsb_scene_create(const MtsbSceneDesc *d, mtsb_scene_t *out) {
         v.env_emitter = -1;
         for (uint32_t i = 0; i < d->n_emitters; ++i) {
             cdf.push_back(cdf.back() + d->emitters[i].sampling_weight);
-            if (d->emitters[i].type == MTSB_EMITTER_CONSTANT) v.env_emitter = (int) i;
+            if (d->emitters[i].type == MTSB_EMITTER_CONSTANT || d->emitters[i].type == MTSB_EMITTER_ENVMAP) v.env_emitter = (int) i;
         }
         float sum = cdf.back();
         v.emitter_norm = 0.0f;
@@ -280,6 +285,56 @@ extern "C" int mtsb_scene_create(const MtsbSceneDesc *d, mtsb_scene_t *out) {
         if ((rc = dev_upload(s, &v.area_cdf, acdf.data(), acdf.size()))) return fail(rc);
         if ((rc = dev_upload(s, &v.area_cdf_offset, aoff.data(), aoff.size()))) return fail(rc);
         if ((rc = dev_upload(s, &v.inv_area, inv_area.data(), inv_area.size()))) return fail(rc);
+    }
+    v.envmap = nullptr;
+    if (v.env_emitter >= 0 && d->emitters[v.env_emitter].type == MTSB_EMITTER_ENVMAP) {
+        // EnvironmentMap::configure (envmap.cpp:260-329): half-precision texels, marginal / conditional CDFs over
+        // luminance weighted by sin(theta), normalisation.  Arithmetic types follow the reference: Float sums,
+        // float tables, M_PI as a double constant.
+        const MtsbEnvmap &em = *d->envmap;
+        const int W = em.width, H = em.height;
+        std::vector<HalfTexel> tex((size_t) W * H);
+        std::vector<float> cdf_cols((size_t) (W + 1) * H), cdf_rows((size_t) H + 1), row_w((size_t) H);
+        size_t colPos = 0, rowPos = 0;
+        volatile float rowSum = 0.0f;
+        cdf_rows[rowPos++] = 0;
+        for (int y = 0; y < H; ++y) {
+            volatile float colSum = 0;
+            cdf_cols[colPos++] = 0;
+            for (int x = 0; x < W; ++x) {
+                const float *p = em.rgb + 3 * ((size_t) y * W + x);
+                const uint32_t hr = __half_as_ushort(__float2half_rn(p[0])), hg = __half_as_ushort(__float2half_rn(p[1])), hb = __half_as_ushort(__float2half_rn(p[2]));
+                HalfTexel t; t.x = hr | (hg << 16); t.y = hb;
+                tex[(size_t) y * W + x] = t;
+                volatile float lum = half_bits_to_float(hr) * 0.212671f;                    // Spectrum::getLuminance, spectrum.h:724-727
+                lum = lum + half_bits_to_float(hg) * 0.715160f; lum = lum + half_bits_to_float(hb) * 0.072169f;
+                colSum = colSum + lum;
+                cdf_cols[colPos++] = colSum;
+            }
+            const float normalization = 1.0f / colSum;
+            for (int x = 1; x < W; ++x) cdf_cols[colPos - x - 1] *= normalization;
+            cdf_cols[colPos - 1] = 1.0f;
+            const float weight = (float) std::sin((double) ((float) y + 0.5f) * 3.14159265358979323846 / (double) H);
+            row_w[y] = weight;
+            volatile float cw = colSum * weight;
+            rowSum = rowSum + cw;
+            cdf_rows[rowPos++] = rowSum;
+        }
+        const float normalization = 1.0f / rowSum;
+        for (int y = 1; y < H; ++y) cdf_rows[rowPos - y - 1] *= normalization;
+        cdf_rows[rowPos - 1] = 1.0f;
+        if (rowSum == 0) { set_error("The environment map is completely black -- this is not allowed."); return fail(MTSB_ERR_INVALID); }
+        if (!std::isfinite(rowSum)) { set_error("The environment map contains an invalid floating point value (nan/inf) -- giving up."); return fail(MTSB_ERR_INVALID); }
+        EnvmapView ev{};
+        ev.width = W; ev.height = H; ev.scale = em.scale;
+        ev.normalization = (float) (1.0f / ((double) rowSum * (2 * 3.14159265358979323846 / W) * (3.14159265358979323846 / H)));
+        ev.pixel_size_x = (float) (2 * 3.14159265358979323846 / W); ev.pixel_size_y = (float) (3.14159265358979323846 / H);
+        for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) { ev.to_world[3 * r + c] = em.to_world[4 * r + c]; ev.to_local[3 * r + c] = em.to_local[4 * r + c]; }
+        if ((rc = dev_upload(s, &ev.texels, tex.data(), tex.size()))) return fail(rc);
+        if ((rc = dev_upload(s, &ev.cdf_rows, cdf_rows.data(), cdf_rows.size()))) return fail(rc);
+        if ((rc = dev_upload(s, &ev.cdf_cols, cdf_cols.data(), cdf_cols.size()))) return fail(rc);
+        if ((rc = dev_upload(s, &ev.row_weights, row_w.data(), row_w.size()))) return fail(rc);
+        if ((rc = dev_upload(s, &v.envmap, &ev, 1))) return fail(rc);
     }
     {   // sample generator tables (halton: primes + digit permutations, halton.cpp:139-149, faure.cpp:22-84)
         const char *err = "";

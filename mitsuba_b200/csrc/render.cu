@@ -449,11 +449,13 @@ __global__ void k_miss(SceneView sc, PathBuffers pb, RenderConst rc, int cur) {
         if (sc.env_emitter >= 0) {
             const float4 te = pb.thr_eta[slot];
             const V3 thr(te.x, te.y, te.z);
-            const V3 value = ld3(sc.emitters[sc.env_emitter].radiance);       // constant.cpp:242-244
+            RayIn ray;
+            if (!(fl & PF_FIRST) || sc.envmap) ray = load_ray(pb.rays[cur], q);     // a constant environment needs no direction
+            else { ray.ox = ray.oy = ray.oz = ray.dx = ray.dy = 0.0f; ray.dz = 1.0f; ray.mint = ray.maxt = 0.0f; }
+            const V3 value = environment_eval(sc, V3(ray.dx, ray.dy, ray.dz));      // constant.cpp:242-244 / envmap.cpp:380-410
             if (fl & PF_FIRST) {
                 if (!rc.hide_emitters) { lb.x += thr.x * value.x; lb.y += thr.y * value.y; lb.z += thr.z * value.z; }
             } else {
-                const RayIn ray = load_ray(pb.rays[cur], q);
                 // fillDirectSamplingRecord (constant.cpp:246-260): the ray must start inside the bounding sphere
                 float nearT, farT;
                 const V3 o(ray.ox, ray.oy, ray.oz), d(ray.dx, ray.dy, ray.dz);

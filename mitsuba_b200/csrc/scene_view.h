@@ -3,6 +3,7 @@
 #include "../../include/mtsb200.h"
 #include "bvh.h"
 #include "qmc.h"
+#include "envmap.h"
 
 namespace mtsb {
 
@@ -21,7 +22,8 @@ struct SceneView {
     const float *area_cdf;                  // concatenated per emitter shape
     const uint32_t *area_cdf_offset;        // per shape: offset into area_cdf (n_tris+1 entries), or 0xFFFFFFFF
     const float *inv_area;                  // per shape
-    int env_emitter;                        // index of the `constant` emitter or -1
+    int env_emitter;                        // index of the environment emitter (`constant` or `envmap`) or -1
+    const EnvmapView *envmap;               // device copy of the `envmap` tables, or NULL
     float bsphere_c[3], bsphere_r;          // constant.cpp:67-71
     // sensor (perspective.cpp:127-150, 286-317)
     MtsbSensor sensor; float near_x, near_y;

@@ -114,6 +114,13 @@ MTSB_HD V3 area_eval(const MtsbEmitter &e, V3 shN, V3 d) {       // area.cpp:104
     return ld3(e.radiance);
 }
 
+// Scene::evalEnvironment (scene.h:914-917): radiance arriving along a ray of direction d that left the scene
+MTSB_HD V3 environment_eval(const SceneView &sc, V3 d) {
+    const MtsbEmitter &e = sc.emitters[sc.env_emitter];
+    if (e.type == MTSB_EMITTER_ENVMAP) { const EnvmapView &ev = *sc.envmap; return envmap_eval(ev, d); }
+    return ld3(e.radiance);                                                  // constant.cpp:242-244
+}
+
 MTSB_HD V3 emitter_sample_direct(const SceneView &sc, int ei, DRec &dRec, P2 u) {
     const MtsbEmitter &e = sc.emitters[ei];
     if (e.type == MTSB_EMITTER_AREA) {
@@ -152,6 +159,21 @@ MTSB_HD V3 emitter_sample_direct(const SceneView &sc, int ei, DRec &dRec, P2 u) 
         dRec.d *= invDist;
         dRec.n = V3(0.0f);
         return ld3(e.radiance) * (invDist * invDist);
+    } else if (e.type == MTSB_EMITTER_ENVMAP) {
+        // EnvironmentMap::sampleDirect (envmap.cpp:516-543)
+        const EnvmapView &ev = *sc.envmap;
+        V3 dl, value; float pdf;
+        envmap_sample_direction(ev, u.x, u.y, dl, value, pdf);
+        const V3 d = envmap_xform(ev.to_world, dl);
+        float nearT, farT;
+        dRec.pdf = 0.0f;
+        if (isZero(value) || pdf == 0 || !bsphere_intersect(sc.bsphere_c, sc.bsphere_r, dRec.ref, d, nearT, farT) || nearT >= 0 || farT <= 0)
+            return V3(0.0f);
+        dRec.pdf = pdf;
+        dRec.p = dRec.ref + d * farT;
+        dRec.n = normalize(ld3(sc.bsphere_c) - dRec.p);
+        dRec.dist = farT; dRec.d = d; dRec.measure = MTSB_MEASURE_SOLID_ANGLE;
+        return value / pdf;
     } else {
         V3 d; float pdf;
         if (!isZero(dRec.refN)) {
@@ -186,6 +208,11 @@ MTSB_HD float emitter_pdf_direct(const SceneView &sc, int ei, const DRec &dRec) 
         return 0.0f;
     } else if (e.type == MTSB_EMITTER_POINT) {
         return dRec.measure == MTSB_MEASURE_DISCRETE ? 1.0f : 0.0f;
+    } else if (e.type == MTSB_EMITTER_ENVMAP) {
+        // EnvironmentMap::pdfDirect (envmap.cpp:545-556)
+        const EnvmapView &ev = *sc.envmap;
+        const float pdfSA = envmap_pdf_direction(ev, envmap_xform(ev.to_local, dRec.d));
+        return dRec.measure == MTSB_MEASURE_SOLID_ANGLE ? pdfSA : 0.0f;
     }
     float pdfSA;
     if (!isZero(dRec.refN)) pdfSA = MTSB_INV_PI * fmaxf(0.0f, dot(dRec.d, dRec.refN));

@@ -61,15 +61,25 @@ private:
 };
 
 // ---- emitters ----------------------------------------------------------------------------------
+struct Image {              // linear RGB, row 0 on top
+    int width = 0, height = 0;
+    std::vector<float> rgb;
+};
+Image readImage(const std::string &path);     // imageio.cpp: PFM, Radiance RGBE
+
 class Emitter : public ConfigurableObject {
 public:
-    explicit Emitter(const Properties &p);
+    explicit Emitter(const Properties &p, const std::string &baseDir = std::string());
     EClass getClass() const override { return CEmitter; }
     bool isArea() const { return m_rec.type == MTSB_EMITTER_AREA; }
     const MtsbEmitter &record() const { return m_rec; }
     int m_parents = 0;      // area.cpp:192-201: exactly one parent shape
+    bool isEnvmap() const { return m_rec.type == MTSB_EMITTER_ENVMAP; }
+    // envmap.cpp:105-189: image + toWorld + scale; `rgb` of the returned record points into this object
+    MtsbEnvmap envmapRecord() const;
 private:
     MtsbEmitter m_rec;
+    Image m_image; Transform m_toWorld; float m_scale = 1.0f;
 };
 
 // ---- shapes ------------------------------------------------------------------------------------
@@ -160,6 +170,7 @@ struct FlatScene {          // owns the buffers MtsbSceneDesc points into
     std::vector<MtsbEmitter> emitters;
     std::vector<float> positions, normals, texcoords;
     std::vector<uint32_t> indices;
+    MtsbEnvmap envmap;          // valid when an emitter has type MTSB_EMITTER_ENVMAP (points into the Emitter object)
     MtsbSceneDesc desc;
     int seed = 1004;
 };

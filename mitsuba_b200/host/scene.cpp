@@ -18,7 +18,7 @@ ObjRef createObject(EClass expected, const Properties &props, const std::string 
         case CRFilter: return std::make_shared<RFilter>(props);
         case CShape: return std::make_shared<Shape>(props, baseDir);
         case CBsdf: return std::make_shared<Bsdf>(props);
-        case CEmitter: return std::make_shared<Emitter>(props);
+        case CEmitter: return std::make_shared<Emitter>(props, baseDir);
         case CTexture:
             error("Textures are not part of the B200 path: give constant <rgb>/<spectrum>/<float> values (plugin \"" +
                   props.getPluginName() + "\").");
@@ -63,7 +63,7 @@ void Scene::configure() {
     if (!sensor)
         error("The scene has no <sensor>: add a perspective sensor (the reference's automatic camera placement is not implemented).");
     int nEnv = 0;
-    for (auto &e : emitters) if (e->record().type == MTSB_EMITTER_CONSTANT) ++nEnv;
+    for (auto &e : emitters) if (e->record().type == MTSB_EMITTER_CONSTANT || e->record().type == MTSB_EMITTER_ENVMAP) ++nEnv;
     if (nEnv > 1) error("The scene may only contain one environment emitter");      // scene.cpp:339-341
 }
 
@@ -130,6 +130,8 @@ void Scene::flatten(FlatScene &f) const {
     d.integrator.strict_normals = integrator->strictNormals;
     d.integrator.hide_emitters = integrator->hideEmitters;
     d.integrator.sample_count = sensor->sampler->sampleCount;
+    d.envmap = nullptr;
+    for (auto &e : emitters) if (e->isEnvmap()) { f.envmap = e->envmapRecord(); d.envmap = &f.envmap; }
     d.sampler.type = sensor->sampler->kind; d.sampler.dimension = sensor->sampler->dimension; d.sampler.scramble = sensor->sampler->scramble; d.sampler._pad = 0;
     f.seed = sensor->sampler->seed;
 }

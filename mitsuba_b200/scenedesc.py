@@ -324,6 +324,24 @@ class SceneBuilder:
         e.radiance, e.sampling_weight = _f3(radiance), sampling_weight
         self.emitters.append(e)
 
+    def add_envmap(self, image, to_world=None, scale=1.0, sampling_weight=1.0):
+        """`envmap` emitter (src/emitters/envmap.cpp:105-189): `image` is a (height, width, 3) linear RGB array in
+        latitude-longitude layout, row 0 at the +Y pole."""
+        img = np.ascontiguousarray(image, dtype=np.float32)
+        assert img.ndim == 3 and img.shape[2] == 3
+        tw = np.eye(4, dtype=np.float64) if to_world is None else np.asarray(to_world, np.float64).reshape(4, 4)
+        em = abi.Envmap()
+        em.height, em.width = img.shape[0], img.shape[1]
+        em.rgb = abi.ptr(img, C.c_float)
+        em.to_world = (C.c_float * 16)(*[float(x) for x in tw.astype(np.float32).reshape(16)])
+        em.to_local = (C.c_float * 16)(*[float(x) for x in np.linalg.inv(tw).astype(np.float32).reshape(16)])
+        em.scale = float(scale)
+        self.envmap, self._envmap_image = em, img
+        e = abi.Emitter()
+        e.type, e.shape = abi.EMITTER_ENVMAP, -1
+        e.radiance, e.sampling_weight = _f3([0, 0, 0]), sampling_weight
+        self.emitters.append(e)
+
     # -- convenience geometry --------------------------------------------------
     def add_quad(self, p0, p1, p2, p3, material, **kw):
         """Two triangles (p0,p1,p2), (p0,p2,p3)."""
@@ -365,5 +383,7 @@ class SceneBuilder:
         d.sensor = self.sensor
         d.integrator = self.integrator
         d.sampler = self.sampler
+        if getattr(self, "envmap", None) is not None:
+            d.envmap = C.pointer(self.envmap)
         keep = (pos, nrm, uv, idx, shapes, mats, ems)
         return d, keep

@@ -207,3 +207,24 @@ def chord_rays(center, radius, n, seed=SEED):
     rays["mint"] = 0.0
     rays["maxt"] = ln[:, 0].astype(np.float32)
     return rays
+
+
+def synthetic_sky(width=64, height=32, seed=4, sun=True):
+    """A small synthetic HDR latitude-longitude map (row 0 = +Y pole): blue-ish gradient sky, a warm horizon band, a
+    dim ground and (optionally) a bright sun a few texels wide -- enough dynamic range to exercise the importance
+    sampling tables of the `envmap` emitter.  Deterministic."""
+    rng = np.random.default_rng(seed)
+    theta = (np.arange(height) + 0.5) * np.pi / height
+    phi = (np.arange(width) + 0.5) * 2 * np.pi / width
+    T, P = np.meshgrid(theta, phi, indexing="ij")
+    up = np.cos(T)
+    img = np.zeros((height, width, 3), np.float32)
+    sky = np.clip(up, 0, 1)[..., None] * np.array([0.25, 0.45, 0.9]) + np.exp(-8 * np.abs(up))[..., None] * np.array([0.9, 0.6, 0.3])
+    ground = np.array([0.08, 0.07, 0.05]) * (1 + 0.3 * np.sin(3 * P))[..., None]
+    img[:] = np.where((up > 0)[..., None], sky, ground)
+    img *= (1 + 0.1 * rng.standard_normal((height, width, 1))).clip(0.5, 1.5)
+    if sun:
+        sd = np.array([np.sin(0.9) * np.sin(2.2), np.cos(0.9), -np.sin(0.9) * np.cos(2.2)])
+        d = np.stack([np.sin(T) * np.sin(P), np.cos(T), -np.sin(T) * np.cos(P)], -1)
+        img += (np.exp(-((1 - d @ sd) / 0.004)) * 400.0)[..., None] * np.array([1.0, 0.9, 0.7])
+    return img.astype(np.float32)

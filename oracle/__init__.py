@@ -68,6 +68,12 @@ def lib():
         L.orc_fresnel_conductor_exact.argtypes = [C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_microfacet.argtypes = [C.c_int, C.c_float, C.c_float, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_warp.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_float_to_half.argtypes = [C.c_float]
+        L.orc_float_to_half.restype = C.c_uint16
+        L.orc_half_to_float.argtypes = [C.c_uint16]
+        L.orc_half_to_float.restype = C.c_float
+        L.orc_square_to_tent.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_envmap_query.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]
         L.orc_halton_sequence.argtypes = [C.c_int] * 9 + [C.c_void_p]
         L.orc_sobol_sequence.argtypes = [C.c_int] * 9 + [C.c_void_p]
         L.orc_sobol_matrix32.argtypes = [C.c_uint32, C.c_uint32]
@@ -212,6 +218,14 @@ class Oracle:
         q = np.ascontiguousarray(q, dtype=abi.DIRECT_QUERY_DTYPE)
         out = np.zeros(q.shape[0], dtype=abi.DIRECT_RESULT_DTYPE)
         lib().orc_emitter_sample(self.h, _vp(q), q.shape[0], _vp(out))
+        return out
+
+    def envmap_query(self, kind, q):
+        """kind 0: evalEnvironment(direction); 1: internalSampleDirection(u) -> (d, value, pdf); 2: internalPdfDirection(d)."""
+        q = np.ascontiguousarray(q, dtype=np.float32).reshape(-1, 3)
+        out = np.zeros((q.shape[0], 7), np.float32)
+        if lib().orc_envmap_query(self.h, kind, _vp(q), q.shape[0], _vp(out)):
+            raise RuntimeError(lib().orc_last_error().decode())
         return out
 
     def fill_intersection(self, rays, hits):

@@ -114,7 +114,7 @@ V3 Li(const Scene &sc, const MtsbRay &primary, Rng &rng, Counters &cnt, float &a
     while (depth <= maxDepth || maxDepth < 0) {
         if (!its.valid) {
             if (emittedRadiance && (!hideEmitters || scattered) && sc.envEmitter >= 0)
-                L += throughput * rgb(sc.emitters[sc.envEmitter].radiance);   // evalEnvironment constant.cpp:242-244
+                L += throughput * evalEnvironment(sc, V3(ray.d[0], ray.d[1], ray.d[2]));   // path.cpp:141-143
             break;
         }
         const MtsbShape &shape = sc.shapes[its.shape];
@@ -146,7 +146,7 @@ V3 Li(const Scene &sc, const MtsbRay &primary, Rng &rng, Counters &cnt, float &a
                 const V3 bsdfVal = bsdf_eval(sc.materials.data(), mat, its.wi, wo);
                 if (!isZero(bsdfVal) && (!strictNormals || dot(its.geoN, dRec.d) * cosTheta(wo) > 0)) {
                     const MtsbEmitter &em = sc.emitters[dRec.emitter];
-                    bool onSurface = em.type == MTSB_EMITTER_AREA || em.type == MTSB_EMITTER_CONSTANT;
+                    bool onSurface = em.type != MTSB_EMITTER_POINT;
                     float bsdfPdf = (onSurface && dRec.measure == kSolidAngle) ? bsdf_pdf(sc.materials.data(), mat, its.wi, wo) : 0;
                     float weight = miWeight(dRec.pdf, bsdfPdf);
                     L += throughput * value * bsdfVal * weight;
@@ -186,7 +186,7 @@ V3 Li(const Scene &sc, const MtsbRay &primary, Rng &rng, Counters &cnt, float &a
         } else {
             if (sc.envEmitter >= 0) {
                 if (hideEmitters && !scattered) break;
-                value = rgb(sc.emitters[sc.envEmitter].radiance);
+                value = evalEnvironment(sc, wo);                                  // path.cpp:240
                 // fillDirectSamplingRecord constant.cpp:246-260
                 float nearT, farT;
                 if (!bsphereIntersect(sc.bsphereC, sc.bsphereR, V3(ray.o[0], ray.o[1], ray.o[2]), wo, nearT, farT) || nearT > 0 || farT < 0) break;
@@ -260,7 +260,11 @@ int orc_scene_create(const MtsbSceneDesc *d, void **out) {
     sc->accel.build(sc->sd);
     for (size_t i = 0; i < sc->emitters.size(); ++i) {
         sc->emitterPdf.append(sc->emitters[i].sampling_weight);
-        if (sc->emitters[i].type == MTSB_EMITTER_CONSTANT) sc->envEmitter = (int) i;
+        if (sc->emitters[i].type == MTSB_EMITTER_CONSTANT || sc->emitters[i].type == MTSB_EMITTER_ENVMAP) sc->envEmitter = (int) i;
+        if (sc->emitters[i].type == MTSB_EMITTER_ENVMAP) {
+            if (!d->envmap || !d->envmap->rgb) { g_err = "envmap emitter without image data"; delete sc; return MTSB_ERR_INVALID; }
+            try { sc->envmap.build(*d->envmap); } catch (const std::exception &e) { g_err = e.what(); delete sc; return MTSB_ERR_INVALID; }
+        }
     }
     if (!sc->emitters.empty()) sc->emitterPdf.normalize();
     // Scene::m_aabb: kd-tree box (+ sensor position, + emitter boxes) scene.cpp:388-414;
@@ -622,6 +626,28 @@ int orc_ldsampler_sets(int sampleCount, int dimension, uint64_t seed, float *out
         std::copy(ld.samples2D[d].begin(), ld.samples2D[d].end(), out2 + d * 2 * ld.sampleCount);
     }
     return (int) ld.sampleCount;
+}
+
+// ---- environment map (orc_scene.h: Envmap), exposed for the unit tests --------------------------------------------
+uint16_t orc_float_to_half(float f) { return floatToHalf(f); }
+float orc_half_to_float(uint16_t h) { return halfToFloat(h); }
+void orc_square_to_tent(const float *u2, float *out2) { out2[0] = Envmap::intervalToTent(u2[0]); out2[1] = Envmap::intervalToTent(u2[1]); }
+// kind 0: evalEnvironment(d) -> rgb; kind 1: internalSampleDirection(u) -> d(3, local frame), value(3), pdf;
+// kind 2: internalPdfDirection(d local) -> pdf.  `in` holds 3 floats per query, `out` 7 floats per query.
+int orc_envmap_query(void *h, int kind, const float *in, size_t n, float *out) {
+    Scene *sc = S(h);
+    if (!sc->envmap.present()) { g_err = "scene has no envmap"; return MTSB_ERR_INVALID; }
+    for (size_t i = 0; i < n; ++i) {
+        const float *q = in + 3 * i; float *o = out + 7 * i;
+        for (int k = 0; k < 7; ++k) o[k] = 0;
+        if (kind == 0) { V3 v = sc->envmap.eval(V3(q[0], q[1], q[2])); o[0] = v.x; o[1] = v.y; o[2] = v.z; }
+        else if (kind == 1) {
+            V3 d, value; float pdf;
+            sc->envmap.sampleDirection(P2{q[0], q[1]}, d, value, pdf);
+            o[0] = d.x; o[1] = d.y; o[2] = d.z; o[3] = value.x; o[4] = value.y; o[5] = value.z; o[6] = pdf;
+        } else o[6] = sc->envmap.pdfDirection(V3(q[0], q[1], q[2]));
+    }
+    return MTSB_OK;
 }
 
 }  // extern "C"

@@ -6,6 +6,10 @@
 #include "orc_accel.h"
 #include <vector>
 #include <mutex>
+#include <stdexcept>
+#include <cstring>
+#include <algorithm>
+#include <cmath>
 
 namespace orc {
 
@@ -73,6 +77,153 @@ struct Film {
     int stride() const { return w + 2 * border; }
 };
 
+// ---- EnvironmentMap (src/emitters/envmap.cpp) ---------------------------------------------------------------
+// half (src/libcore/half.cpp:78-211, include/mitsuba/core/half.h): the map is stored as SpectrumHalf
+inline uint16_t floatToHalf(float f) {
+    union { float f; int i; } x; x.f = f;
+    int i = x.i;
+    int s = (i >> 16) & 0x00008000, e = ((i >> 23) & 0x000000ff) - (127 - 15), m = i & 0x007fffff;
+    if (e <= 0) {
+        if (e < -10) return (uint16_t) s;
+        m = m | 0x00800000;
+        int t = 14 - e, a = (1 << (t - 1)) - 1, b = (m >> t) & 1;
+        m = (m + a + b) >> t;
+        return (uint16_t) (s | m);
+    } else if (e == 0xff - (127 - 15)) {
+        if (m == 0) return (uint16_t) (s | 0x7c00);
+        m >>= 13;
+        return (uint16_t) (s | 0x7c00 | m | (m == 0));
+    } else {
+        m = m + 0x00000fff + ((m >> 13) & 1);
+        if (m & 0x00800000) { m = 0; e += 1; }
+        if (e > 30) return (uint16_t) (s | 0x7c00);
+        return (uint16_t) (s | (e << 10) | (m >> 13));
+    }
+}
+inline float halfToFloat(uint16_t h) {            // half.cpp:50-75 (the table the reference builds at start-up)
+    int s = (h >> 15) & 1, e = (h >> 10) & 0x1f, m = h & 0x3ff;
+    union { float f; uint32_t i; } x;
+    if (e == 0) {
+        if (m == 0) { x.i = (uint32_t) s << 31; return x.f; }
+        while (!(m & 0x00000400)) { m <<= 1; e -= 1; }
+        e += 1; m &= ~0x00000400;
+    } else if (e == 31) { x.i = ((uint32_t) s << 31) | 0x7f800000u | ((uint32_t) m << 13); return x.f; }
+    e = e + (127 - 15); m = m << 13;
+    x.i = ((uint32_t) s << 31) | ((uint32_t) e << 23) | (uint32_t) m;
+    return x.f;
+}
+struct Envmap {
+    int w = 0, h = 0;
+    std::vector<uint16_t> texels;             // 3 per texel
+    std::vector<float> cdfRows, cdfCols, rowWeights;
+    float normalization = 0, scale = 1; P2 pixelSize{0, 0};
+    float toWorld[16], toLocal[16];
+    bool present() const { return w > 0; }
+    // MIPMap::evalTexel (mipmap.h:503-563), ERepeat in u, EClamp in v
+    V3 evalTexel(int x, int y) const {
+        if (x < 0 || x >= w) { x = x % w; if (x < 0) x += w; }
+        if (y < 0 || y >= h) y = std::min(std::max(y, 0), h - 1);
+        const uint16_t *t = &texels[3 * ((size_t) y * w + x)];
+        return V3(halfToFloat(t[0]), halfToFloat(t[1]), halfToFloat(t[2]));
+    }
+    // MIPMap::evalBilinear(0, uv) (mipmap.h:575-596)
+    V3 evalBilinear(P2 uv) const {
+        if (!std::isfinite(uv.x) || !std::isfinite(uv.y)) return V3(0.0f);
+        float u = uv.x * w - 0.5f, v = uv.y * h - 0.5f;
+        int xPos = (int) std::floor(u), yPos = (int) std::floor(v);
+        float dx1 = u - xPos, dx2 = 1.0f - dx1, dy1 = v - yPos, dy2 = 1.0f - dy1;
+        return evalTexel(xPos, yPos) * dx2 * dy2 + evalTexel(xPos, yPos + 1) * dx2 * dy1
+             + evalTexel(xPos + 1, yPos) * dx1 * dy2 + evalTexel(xPos + 1, yPos + 1) * dx1 * dy1;
+    }
+    // configure() (envmap.cpp:260-329)
+    void build(const MtsbEnvmap &em) {
+        w = em.width; h = em.height; scale = em.scale;
+        std::memcpy(toWorld, em.to_world, sizeof(toWorld)); std::memcpy(toLocal, em.to_local, sizeof(toLocal));
+        texels.resize((size_t) 3 * w * h);
+        for (size_t i = 0; i < texels.size(); ++i) texels[i] = floatToHalf(em.rgb[i]);
+        size_t nEntries = (size_t) (w + 1) * (size_t) h;
+        cdfCols.assign(nEntries, 0); cdfRows.assign((size_t) h + 1, 0); rowWeights.assign((size_t) h, 0);
+        size_t colPos = 0, rowPos = 0;
+        float rowSum = 0.0f;
+        cdfRows[rowPos++] = 0;
+        for (int y = 0; y < h; ++y) {
+            float colSum = 0;
+            cdfCols[colPos++] = 0;
+            for (int x = 0; x < w; ++x) {
+                V3 value = evalTexel(x, y);
+                colSum += luminance(value);
+                cdfCols[colPos++] = (float) colSum;
+            }
+            float normalization = 1.0f / (float) colSum;
+            for (int x = 1; x < w; ++x) cdfCols[colPos - x - 1] *= normalization;
+            cdfCols[colPos - 1] = 1.0f;
+            float weight = std::sin((y + 0.5f) * M_PI / h);
+            rowWeights[y] = weight;
+            rowSum += colSum * weight;
+            cdfRows[rowPos++] = (float) rowSum;
+        }
+        float norm = 1.0f / (float) rowSum;
+        for (int y = 1; y < h; ++y) cdfRows[rowPos - y - 1] *= norm;
+        cdfRows[rowPos - 1] = 1.0f;
+        if (rowSum == 0) throw std::runtime_error("The environment map is completely black -- this is not allowed.");
+        if (!std::isfinite(rowSum)) throw std::runtime_error("The environment map contains an invalid floating point value (nan/inf) -- giving up.");
+        normalization = 1.0f / (rowSum * (2 * M_PI / w) * (M_PI / h));
+        pixelSize = P2{(float) (2 * M_PI / w), (float) (M_PI / h)};
+    }
+    // sampleReuse (envmap.cpp:655-661)
+    static uint32_t sampleReuse(const float *cdf, uint32_t size, float &sample) {
+        const float *entry = std::lower_bound(cdf, cdf + size + 1, (float) sample);
+        uint32_t index = std::min((uint32_t) std::max((ptrdiff_t) 0, entry - cdf - 1), size - 1);
+        sample = (sample - (float) cdf[index]) / (float) (cdf[index + 1] - cdf[index]);
+        return index;
+    }
+    static float intervalToTent(float sample) {                   // warp.cpp:157-169
+        float sign;
+        if (sample < 0.5f) { sign = 1; sample *= 2; } else { sign = -1; sample = 2 * (sample - 0.5f); }
+        return sign * (1 - std::sqrt(sample));
+    }
+    // internalSampleDirection (envmap.cpp:567-600)
+    void sampleDirection(P2 sample, V3 &d, V3 &value, float &pdf) const {
+        uint32_t row = sampleReuse(cdfRows.data(), (uint32_t) h, sample.y),
+                 col = sampleReuse(cdfCols.data() + (size_t) row * (w + 1), (uint32_t) w, sample.x);
+        P2 pos{(float) col + intervalToTent(sample.x), (float) row + intervalToTent(sample.y)};
+        int xPos = (int) std::floor(pos.x), yPos = (int) std::floor(pos.y);
+        float dx1 = pos.x - xPos, dx2 = 1.0f - dx1, dy1 = pos.y - yPos, dy2 = 1.0f - dy1;
+        V3 value1 = evalTexel(xPos, yPos) * dx2 * dy2 + evalTexel(xPos + 1, yPos) * dx1 * dy2;
+        V3 value2 = evalTexel(xPos, yPos + 1) * dx2 * dy1 + evalTexel(xPos + 1, yPos + 1) * dx1 * dy1;
+        value = (value1 + value2) * scale;
+        pdf = (luminance(value1) * rowWeights[std::min(std::max(yPos, 0), h - 1)] +
+               luminance(value2) * rowWeights[std::min(std::max(yPos + 1, 0), h - 1)]) * normalization;
+        float sinPhi = std::sin(pixelSize.x * (pos.x + 0.5f)), cosPhi = std::cos(pixelSize.x * (pos.x + 0.5f));
+        float sinTheta = std::sin(pixelSize.y * (pos.y + 0.5f)), cosTheta = std::cos(pixelSize.y * (pos.y + 0.5f));
+        d = V3(sinPhi * sinTheta, cosTheta, -cosPhi * sinTheta);
+        pdf /= std::max(std::abs(sinTheta), kEpsilon);
+    }
+    // internalPdfDirection (envmap.cpp:603-633)
+    float pdfDirection(V3 d) const {
+        P2 uv{std::atan2(d.x, -d.z) * kInvTwoPi, std::acos(std::min(1.0f, std::max(-1.0f, d.y))) * kInvPi};
+        if (!std::isfinite(uv.x) || !std::isfinite(uv.y)) return 0.0f;
+        float u = uv.x * w - 0.5f, v = uv.y * h - 0.5f;
+        int xPos = (int) std::floor(u), yPos = (int) std::floor(v);
+        float dx1 = u - xPos, dx2 = 1.0f - dx1, dy1 = v - yPos, dy2 = 1.0f - dy1;
+        V3 value1 = evalTexel(xPos, yPos) * dx2 * dy2 + evalTexel(xPos + 1, yPos) * dx1 * dy2;
+        V3 value2 = evalTexel(xPos, yPos + 1) * dx2 * dy1 + evalTexel(xPos + 1, yPos + 1) * dx1 * dy1;
+        float sinTheta = std::sqrt(std::max(0.0f, 1 - d.y * d.y));
+        return (luminance(value1) * rowWeights[std::min(std::max(yPos, 0), h - 1)] +
+                luminance(value2) * rowWeights[std::min(std::max(yPos + 1, 0), h - 1)]) * normalization / std::max(std::abs(sinTheta), kEpsilon);
+    }
+    // evalEnvironment without differentials (envmap.cpp:380-392, 408-409); the EWA branch returns the same value
+    // whenever the footprint is below one texel (mipmap.h:694-710)
+    V3 eval(V3 dWorld) const {
+        V3 v = xf(toLocal, dWorld);
+        P2 uv{std::atan2(v.x, -v.z) * kInvTwoPi, std::acos(std::min(1.0f, std::max(-1.0f, v.y))) * kInvPi};
+        return evalBilinear(uv) * scale;
+    }
+    static V3 xf(const float *m, V3 v) {
+        return V3(m[0] * v.x + m[1] * v.y + m[2] * v.z, m[4] * v.x + m[5] * v.y + m[6] * v.z, m[8] * v.x + m[9] * v.y + m[10] * v.z);
+    }
+};
+
 struct Scene {
     MtsbSceneDesc sd;            // pointers refer to the owned copies below
     std::vector<MtsbShape> shapes;
@@ -87,6 +238,7 @@ struct Scene {
     std::vector<Pmf> areaPdf;                  // per shape that is an emitter (trimesh.cpp:388-403)
     std::vector<float> invArea;                // per shape
     int envEmitter;
+    Envmap envmap;                             // envmap.cpp (when the environment emitter is an image)
     V3 bsphereC; float bsphereR;               // constant.cpp:67-71
     // sensor (closed form of perspective.cpp:127-150)
     float nearX, nearY;                        // near*tan(xfov/2), same / aspect
@@ -195,6 +347,21 @@ inline V3 emitterSampleDirect(const Scene &sc, int ei, DRec &dRec, P2 u) {
         dRec.d *= invDist;
         dRec.n = V3(0.0f);
         return rgb(e.radiance) * (invDist * invDist);
+    } else if (e.type == MTSB_EMITTER_ENVMAP) {
+        // envmap.cpp:516-543
+        V3 dl, value; float pdf;
+        sc.envmap.sampleDirection(u, dl, value, pdf);
+        V3 d = Envmap::xf(sc.envmap.toWorld, dl);
+        float nearT, farT;
+        if (isZero(value) || pdf == 0 || !bsphereIntersect(sc.bsphereC, sc.bsphereR, dRec.ref, d, nearT, farT) || nearT >= 0 || farT <= 0) {
+            dRec.pdf = 0.0f;
+            return V3(0.0f);
+        }
+        dRec.pdf = pdf;
+        dRec.p = dRec.ref + d * farT;
+        dRec.n = normalize(sc.bsphereC - dRec.p);
+        dRec.dist = farT; dRec.d = d; dRec.measure = kSolidAngle;
+        return value / pdf;
     } else {
         // constant.cpp:173-215
         V3 d; float pdf;
@@ -232,6 +399,10 @@ inline float emitterPdfDirect(const Scene &sc, int ei, const DRec &dRec) {
         return 0.0f;
     } else if (e.type == MTSB_EMITTER_POINT) {
         return dRec.measure == kDiscrete ? 1.0f : 0.0f;                 // point.cpp:149-151
+    } else if (e.type == MTSB_EMITTER_ENVMAP) {
+        // envmap.cpp:545-556
+        float pdfSA = sc.envmap.pdfDirection(Envmap::xf(sc.envmap.toLocal, dRec.d));
+        return dRec.measure == kSolidAngle ? pdfSA : 0.0f;
     } else {
         // constant.cpp:217-232
         float pdfSA;
@@ -239,6 +410,12 @@ inline float emitterPdfDirect(const Scene &sc, int ei, const DRec &dRec) {
         else pdfSA = kInvFourPi;
         return dRec.measure == kSolidAngle ? pdfSA : 0.0f;
     }
+}
+
+// Scene::evalEnvironment (scene.h:914-917)
+inline V3 evalEnvironment(const Scene &sc, V3 d) {
+    const MtsbEmitter &e = sc.emitters[sc.envEmitter];
+    return e.type == MTSB_EMITTER_ENVMAP ? sc.envmap.eval(d) : rgb(e.radiance);       // envmap.cpp:380-410 / constant.cpp:242-244
 }
 
 // Scene::sampleEmitterDirect scene.cpp:828-855 (visibility test done by the caller so that the

@@ -28,6 +28,7 @@
 #include <mutex>
 #include "src/bsdfs/microfacet.h"
 #include <mitsuba/core/qmc.h>
+#include <mitsuba/core/half.h>
 #include "src/samplers/faure.h"
 #include "src/samplers/sobolseq.h"
 #include "../include/mtsb200.h"
@@ -304,5 +305,10 @@ float ref_sobol_sample(uint64_t index, uint32_t dimension, uint64_t scramble) { 
 uint64_t ref_sobol_look_up(uint32_t m, uint32_t frame, uint32_t px, uint32_t py, uint64_t scramble) { return sobol::look_up(m, frame, px, py, scramble); }
 uint32_t ref_sobol_matrix32(uint32_t dimension, uint32_t column) { return sobol::Matrices::matrices32[dimension * sobol::Matrices::size + column]; }
 uint64_t ref_sobol_vdc(uint32_t m, uint32_t column, int inverse) { return inverse ? sobol::Matrices::vdc_sobol_matrices_inv[m - 1][column] : sobol::Matrices::vdc_sobol_matrices[m - 1][column]; }
+
+// ---- half precision (src/libcore/half.cpp, include/mitsuba/core/half.h): storage type of the environment map ----
+uint16_t ref_float_to_half(float f) { half h(f); return h.bits(); }
+float ref_half_to_float(uint16_t bits) { half h; h.setBits(bits); return (float) h; }
+void ref_square_to_tent(const float *u2, float *out2) { Point2 p = warp::squareToTent(Point2(u2[0], u2[1])); out2[0] = p.x; out2[1] = p.y; }
 
 }  // extern "C"

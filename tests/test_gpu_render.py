@@ -284,3 +284,31 @@ def test_halton_partition_is_exact(gpu_lib):
         sc.render(spp=3, seed=3, spp_offset=5, tile_index=r, tile_count=2, keep_film=True)
     assert np.allclose(sc.film_download().astype(np.float64), whole, rtol=1e-4, atol=1e-4)
     sc.close()
+
+
+# ---- envmap emitter ----------------------------------------------------------------------------
+
+def _sky_scene(**kw):
+    b = scenes.scene_10m(nu=24, nv=12, n_obj=12, **kw)
+    b.emitters = [e for e in b.emitters if e.type != abi.EMITTER_CONSTANT]
+    rot = np.array([[0.8, 0, 0.6, 0], [0, 1, 0, 0], [-0.6, 0, 0.8, 0], [0, 0, 0, 1]], np.float64)
+    b.add_envmap(scenes.synthetic_sky(128, 64), to_world=rot, scale=0.6)
+    return b
+
+
+def test_same_stream_envmap(gpu_lib, oracle_mod):
+    """Environment lookups on escaped rays (first segment and MIS'd BSDF rays), importance-sampled sky + sun as an
+    emitter next to area lights: films equal the oracle's with the same random numbers."""
+    b = _sky_scene(width=96, height=54, spp=4)
+    check_same_stream(gpu_lib, oracle_mod, b, 4, "mixed + envmap")
+
+
+def test_envmap_halton_same_sequence(gpu_lib, oracle_mod):
+    b = _sky_scene(width=96, height=54, spp=4)
+    b.set_sampler("halton", sample_count=4)
+    check_same_sequence(gpu_lib, oracle_mod, b, 4, "mixed + envmap, halton")
+
+
+def test_envmap_independent_streams(gpu_lib, oracle_mod):
+    b = _sky_scene(width=64, height=36, spp=32)
+    check_render(gpu_lib, oracle_mod, b, 32, 256, "mixed + envmap")

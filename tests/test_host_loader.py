@@ -342,3 +342,84 @@ def test_sampler_plugins():
     assert (hs.desc.sampler.type, hs.desc.sampler.scramble, hs.desc.integrator.sample_count) == (abi.SAMPLER_SOBOL, 3, 9)
     hs = hostlib.HostScene.load_string(base % '<sampler type="independent"/>', "mem.xml")
     assert hs.desc.sampler.type == abi.SAMPLER_INDEPENDENT
+
+
+def _write_pfm(path, img, big_endian=False, scale=1.0):
+    h, w, _ = img.shape
+    with open(path, "wb") as f:
+        f.write(b"PF\n%d %d\n%s\n" % (w, h, (b"%g" % scale) if big_endian else (b"-%g" % scale)))
+        f.write(img[::-1].astype(">f4" if big_endian else "<f4").tobytes())
+
+
+def _write_rgbe(path, img, rle=True):
+    """Radiance RGBE writer for the test (flat or run-length encoded scanlines)."""
+    h, w, _ = img.shape
+    m = img.max(-1)
+    e = np.where(m > 1e-32, np.floor(np.log2(np.maximum(m, 1e-38))) + 1, 0).astype(np.int32)
+    mant = np.where((m > 1e-32)[..., None], img / np.exp2(e - 8.0)[..., None], 0).astype(np.int32).clip(0, 255)
+    rgbe = np.concatenate([mant, np.where(m > 1e-32, e + 128, 0)[..., None]], -1).astype(np.uint8)
+    with open(path, "wb") as f:
+        f.write(b"#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n-Y %d +X %d\n" % (h, w))
+        for y in range(h):
+            if not rle:
+                f.write(rgbe[y].tobytes())
+                continue
+            f.write(bytes([2, 2, w >> 8, w & 255]))
+            for c in range(4):
+                row, i = rgbe[y, :, c], 0
+                while i < w:
+                    run = 1
+                    while i + run < w and run < 127 and row[i + run] == row[i]:
+                        run += 1
+                    if run >= 4:
+                        f.write(bytes([128 + run, int(row[i])]))
+                        i += run
+                    else:
+                        j = i
+                        while j < w and j - i < 128 and not (j + 3 < w and row[j] == row[j + 1] == row[j + 2] == row[j + 3]):
+                            j += 1
+                        j = max(j, i + 1)
+                        f.write(bytes([j - i]) + row[i:j].tobytes())
+                        i = j
+    # what a reader must return (RGBE_ToFloat, bitmap.cpp:3522-3530)
+    return np.where(rgbe[..., 3:4] > 0, rgbe[..., :3].astype(np.float32) * np.exp2(rgbe[..., 3:4].astype(np.float32) - 136.0), 0).astype(np.float32)
+
+
+def _envmap_rgb(hs):
+    em = hs.desc.envmap.contents
+    return np.ctypeslib.as_array(em.rgb, shape=(em.height, em.width, 3)).copy(), em
+
+
+def test_envmap_plugin_reads_pfm_and_rgbe(tmp_path):
+    """envmap.cpp:105-189 through the loader: filename relative to the scene file, `scale`, `toWorld`; PFM (either byte
+    order, bottom row first: bitmap.cpp:3764-3814) and Radiance RGBE, flat and run-length encoded (:3590-3690)."""
+    from mitsuba_b200 import scenes
+    img = scenes.synthetic_sky(24, 12)
+    _write_pfm(tmp_path / "le.pfm", img)
+    _write_pfm(tmp_path / "be.pfm", img, big_endian=True, scale=2.0)
+    want_rle = _write_rgbe(tmp_path / "sky.hdr", img)
+    want_flat = _write_rgbe(tmp_path / "flat.rgbe", img, rle=False)
+    body = ('<emitter type="envmap"><string name="filename" value="%s"/><float name="scale" value="2.5"/>'
+            '<transform name="toWorld"><rotate y="1" angle="90"/></transform></emitter>')
+    def load_scene(fn):
+        p = tmp_path / ("scene_%s.xml" % fn)
+        p.write_text(HEAD + body % fn + "</scene>")
+        return hostlib.HostScene.load_file(str(p))
+    hs = load_scene("le.pfm")
+    rgb, em = _envmap_rgb(hs)
+    assert np.array_equal(rgb, img) and (em.width, em.height) == (24, 12) and em.scale == 2.5
+    tw = np.array(em.to_world[:]).reshape(4, 4)
+    tl = np.array(em.to_local[:]).reshape(4, 4)
+    assert np.allclose(tw[:3, :3], [[0, 0, 1], [0, 1, 0], [-1, 0, 0]], atol=1e-6) and np.allclose(tw @ tl, np.eye(4), atol=1e-6)
+    assert [e.type for e in hs.emitters()] == [abi.EMITTER_ENVMAP]
+    assert np.array_equal(_envmap_rgb(load_scene("be.pfm"))[0], img * np.float32(2.0))
+    assert np.array_equal(_envmap_rgb(load_scene("sky.hdr"))[0], want_rle)
+    assert np.array_equal(_envmap_rgb(load_scene("flat.rgbe"))[0], want_flat)
+    assert np.abs(want_rle - img).max() <= img.max() / 128
+    for fn, msg in (("missing.pfm", "could not be found"), ("scene_le.pfm.xml", "unsupported image format")):
+        with pytest.raises(MtsbError) as ei:
+            load_scene(fn)
+        assert msg in str(ei.value)
+    with pytest.raises(MtsbError) as ei:
+        hostlib.HostScene.load_string(HEAD + '<emitter type="constant"/>' + body % str(tmp_path / "le.pfm") + "</scene>", "mem.xml")
+    assert "one environment emitter" in str(ei.value)
