@@ -586,6 +586,121 @@ __global__ void __launch_bounds__(256) k_splat(SceneView sc, PathBuffers pb, Pas
     if ((threadIdx.x & 31) == 0 && n_bad) atomicAdd(bad, n_bad);
 }
 
+// The same gather for reconstruction filters whose footprint spans at most five pixels per axis (radius <= 2.5: the
+// default gaussian, box, ...).  A sample that lies inside its own pixel (px, py) only reaches columns px-2 .. px+2, so the
+// staging pass evaluates its five column weights and five row weights ONCE (ImageBlock::put's separable table lookups,
+// imageblock.h:170-183; zero outside the sample's pixel range) and the gather is a fixed 5x5 stencil of
+// weight products without range tests or float->int conversions: about a quarter of the instructions of k_splat.
+#define MTSB_SPLAT5_OWN 6          /* ceil(36 * 36 / 256) bordered pixels per thread (border <= 2) */
+#define MTSB_SPLAT5_SMEM ((size_t) MTSB_TILE * MTSB_TILE * (sizeof(float4) + 10 * sizeof(float)))
+__global__ void __launch_bounds__(256) k_splat5(SceneView sc, PathBuffers pb, PassInfo ps, unsigned long long *bad) {
+    extern __shared__ float4 s_stage[];                 // [1024] value (rgb, alpha); then wx[5][1024], wy[5][1024]
+    __shared__ float s_filter[32];
+    if (threadIdx.x < 32) s_filter[threadIdx.x] = sc.filter_table[threadIdx.x];
+    __syncthreads();
+    const float f_scale = sc.filter_scale;
+    constexpr int NPIX = MTSB_TILE * MTSB_TILE;
+    float4 *s_val = s_stage;
+    float *s_wx = reinterpret_cast<float *>(s_stage + NPIX);
+    float *s_wy = s_wx + 5 * NPIX;
+    const int b = sc.film_border;
+    const int tile = pb.tiles[ps.tile_first + blockIdx.x];
+    const int ox = (tile % (int) ps.tiles_x) * MTSB_TILE, oy = (tile / (int) ps.tiles_x) * MTSB_TILE;
+    const int bw = min(MTSB_TILE, sc.film_w - ox), bh = min(MTSB_TILE, sc.film_h - oy);
+    const int sx = bw + 2 * b, sy = bh + 2 * b;
+    const uint32_t per_tile = NPIX * ps.spp_pass;
+    const uint32_t slot0 = blockIdx.x * per_tile;
+    const float r = sc.filter_radius;
+    const int fsx = sc.film_w + 2 * b;
+    unsigned long long n_bad = 0;
+    float acc[MTSB_SPLAT5_OWN][5];
+#pragma unroll
+    for (int q = 0; q < MTSB_SPLAT5_OWN; ++q) { acc[q][0] = acc[q][1] = acc[q][2] = acc[q][3] = acc[q][4] = 0.0f; }
+    for (uint32_t c0 = blockIdx.y; c0 < ps.spp_pass; c0 += gridDim.y) {
+        // ---- stage one sample per pixel: value + separable weights ----
+        for (int pix = threadIdx.x; pix < NPIX; pix += blockDim.x) {
+            const uint32_t slot = slot0 + (uint32_t) pix * ps.spp_pass + c0;
+            const uint32_t fl = __float_as_uint(pb.refn_flags[slot].w);
+            const int x = (int) compact1by1((uint32_t) pix), y = (int) compact1by1((uint32_t) pix >> 1);
+            const int j = y * MTSB_TILE + x;
+            float4 val = make_float4(0, 0, 0, 0);
+            float wx[5] = {0, 0, 0, 0, 0}, wy[5] = {0, 0, 0, 0, 0};
+            if (fl & PF_VALID) {
+                const float4 lb = pb.L_bpdf[slot];
+                if (isfinite(lb.x) && isfinite(lb.y) && isfinite(lb.z)) {               // imageblock.h:147-153
+                    val = make_float4(lb.x, lb.y, lb.z, (fl & PF_ALPHA) ? 1.0f : 0.0f);
+                    const float2 sp = pb.spos[slot];
+                    const float posx = sp.x - 0.5f - (float) (ox - b), posy = sp.y - 0.5f - (float) (oy - b);
+                    const float fx = sp.x - (float) (ox + x), fy = sp.y - (float) (oy + y);
+                    if (!(fx >= 0.0f && fx < 1.0f && fy >= 0.0f && fy < 1.0f)) {
+                        // outside its own pixel (see k_splat): ImageBlock::put's scatter form, clipped to the block
+                        const int x0 = max((int) ceilf(posx - r), 0), x1 = min((int) floorf(posx + r), sx - 1);
+                        const int y0 = max((int) ceilf(posy - r), 0), y1 = min((int) floorf(posy + r), sy - 1);
+                        for (int Y = y0; Y <= y1; ++Y)
+                            for (int X = x0; X <= x1; ++X) {
+                                const float w = s_filter[min((int) fabsf(((float) X - posx) * f_scale), 31)] *
+                                                s_filter[min((int) fabsf(((float) Y - posy) * f_scale), 31)];
+                                float *dest = sc.film + ((size_t) (oy + Y) * fsx + (ox + X)) * 5;
+                                atomicAdd(dest, w * val.x); atomicAdd(dest + 1, w * val.y); atomicAdd(dest + 2, w * val.z);
+                                atomicAdd(dest + 3, w * val.w); atomicAdd(dest + 4, w);
+                            }
+                        val = make_float4(0, 0, 0, 0);
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < 5; ++k) {
+                            // bordered column / row k-2 away from the sample's pixel; inside the pixel range of the sample
+                            // (ceil(pos - r) .. floor(pos + r), tested without rounding as in k_splat) its table weight
+                            const float Xf = (float) (x + b + k - 2), Yf = (float) (y + b + k - 2);
+                            if (!(Xf < posx - r || Xf > posx + r)) wx[k] = s_filter[min((int) fabsf((Xf - posx) * f_scale), 31)];
+                            if (!(Yf < posy - r || Yf > posy + r)) wy[k] = s_filter[min((int) fabsf((Yf - posy) * f_scale), 31)];
+                        }
+                    }
+                } else ++n_bad;
+            }
+            s_val[j] = val;
+#pragma unroll
+            for (int k = 0; k < 5; ++k) { s_wx[k * NPIX + j] = wx[k]; s_wy[k * NPIX + j] = wy[k]; }
+        }
+        __syncthreads();
+        // ---- gather: every thread owns up to MTSB_SPLAT5_OWN bordered pixels for the whole pass and keeps their sums in
+        // registers (one film atomic per pixel and CTA at the end instead of one per staging round) ----
+#pragma unroll
+        for (int q = 0; q < MTSB_SPLAT5_OWN; ++q) {
+            const int p = (int) threadIdx.x + q * 256;
+            if (p >= sx * sy) break;
+            const int X = p % sx, Y = p / sx;
+            const int tx = X - b, ty = Y - b;               // tile pixel under this bordered pixel (may be outside the tile)
+#pragma unroll
+            for (int dy = -2; dy <= 2; ++dy) {
+                const int yy = ty + dy;
+                if (yy < 0 || yy >= bh) continue;
+#pragma unroll
+                for (int dx = -2; dx <= 2; ++dx) {
+                    const int xx = tx + dx;
+                    if (xx < 0 || xx >= bw) continue;
+                    const int j = yy * MTSB_TILE + xx;
+                    // the sample of tile pixel (xx, yy) sees this pixel as its column 2 - dx and row 2 - dy
+                    const float w = s_wx[(2 - dx) * NPIX + j] * s_wy[(2 - dy) * NPIX + j];
+                    const float4 val = s_val[j];
+                    acc[q][0] += w * val.x; acc[q][1] += w * val.y; acc[q][2] += w * val.z; acc[q][3] += w * val.w; acc[q][4] += w;
+                }
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int q = 0; q < MTSB_SPLAT5_OWN; ++q) {
+        const int p = (int) threadIdx.x + q * 256;
+        if (p >= sx * sy) break;
+        const int X = p % sx, Y = p / sx;
+        float *dest = sc.film + ((size_t) (oy + Y) * fsx + (ox + X)) * 5;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) if (acc[q][k] != 0.0f) atomicAdd(dest + k, acc[q][k]);
+    }
+    for (int o = 16; o; o >>= 1) n_bad += __shfl_xor_sync(0xFFFFFFFFu, n_bad, o);
+    if ((threadIdx.x & 31) == 0 && n_bad) atomicAdd(bad, n_bad);
+}
+
 // ---- host side ---------------------------------------------------------------------------
 static void free_buffers(PathBuffers *pb) {
     if (!pb) return;
@@ -762,7 +877,12 @@ static void lane_finish(Scene *s, Lane &L, size_t splat_smem) {
         const uint32_t want = (uint32_t) device_sm_count() * 8u;
         uint32_t split = (want + L.pass.ps.n_tiles - 1) / L.pass.ps.n_tiles;
         split = std::max(1u, std::min(std::min(split, rounds), 64u));
-        k_splat<<<dim3(L.pass.ps.n_tiles, split), 256, splat_smem, L.st>>>(s->v, *L.pb, L.pass.ps, s->d_film_bad);
+        // filters reaching at most five pixels per axis take the precomputed-weight gather (floor(r + 0.5) <= 2)
+        static const bool force_generic = getenv("MTSB_SPLAT_GENERIC") != nullptr;
+        if (s->v.filter_radius < 2.5f && s->v.film_border <= 2 && !force_generic)
+            k_splat5<<<dim3(L.pass.ps.n_tiles, split), 256, MTSB_SPLAT5_SMEM, L.st>>>(s->v, *L.pb, L.pass.ps, s->d_film_bad);
+        else
+            k_splat<<<dim3(L.pass.ps.n_tiles, split), 256, splat_smem, L.st>>>(s->v, *L.pb, L.pass.ps, s->d_film_bad);
     }
     s->launches += 2;
     L.timer->end();
@@ -856,6 +976,7 @@ extern "C" int mtsb_render(mtsb_scene_t scene, const MtsbRenderParams *params, M
     rcst.strict_normals = v.integrator.strict_normals; rcst.hide_emitters = v.integrator.hide_emitters;
     const size_t splat_smem = (size_t) MTSB_SPLAT_CHUNK * MTSB_TILE * MTSB_TILE * (sizeof(float4) + sizeof(float2));
     MTSB_CUDA(cudaFuncSetAttribute(k_splat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) splat_smem));
+    MTSB_CUDA(cudaFuncSetAttribute(k_splat5, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) MTSB_SPLAT5_SMEM));
 
     cudaEvent_t ev0, ev1; cudaEventCreate(&ev0); cudaEventCreate(&ev1);
     cudaEventRecord(ev0, s->stream);

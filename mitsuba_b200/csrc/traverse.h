@@ -117,6 +117,7 @@ template <class Stack> struct Traversal {
     Stack stack;
 #if !MTSB_DEVICE_CODE
     uint32_t steps = 0;           // nodes visited      (emulation statistics only)
+    uint32_t sparse_steps = 0;    // ... of which leaf-only nodes with <= 4 children
     uint32_t tri_tests = 0;       // triangle tests
     uint32_t last_batch = 0;      // triangles queued by the last node visit
 #endif
@@ -136,7 +137,7 @@ template <class Stack> struct Traversal {
         stack.reset();
         tg = 0; tri_base = 0; tg2 = 0; tri_base2 = 0;
 #if !MTSB_DEVICE_CODE
-        steps = 0; last_batch = 0;
+        steps = 0; sparse_steps = 0; last_batch = 0;
 #endif
     }
 
@@ -167,6 +168,11 @@ template <class Stack> struct Traversal {
         const U4 n0 = ld16(np), n1 = ld16(np + 1), n2 = ld16(np + 2), n3 = ld16(np + 3), n4 = ld16(np + 4);
 #if !MTSB_DEVICE_CODE
         ++steps;
+        {   // emulation statistics: visits of leaf-only nodes with at most four children
+            int nchild = 0;
+            for (int j = 0; j < 4; ++j) { if ((n1.z >> (8 * j)) & 0xffu) ++nchild; if ((n1.w >> (8 * j)) & 0xffu) ++nchild; }
+            if ((n0.w >> 24) == 0 && nchild <= 4) ++sparse_steps;
+        }
 #endif
 
         const uint32_t e_imask = n0.w;

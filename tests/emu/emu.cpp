@@ -86,6 +86,10 @@ extern "C" void *emu_build(const float *positions, const uint32_t *indices, uint
     return s;
 }
 
+extern "C" void emu_nodes(void *h, Node8 *out) {
+    EmuScene *s = static_cast<EmuScene *>(h);
+    std::memcpy(out, s->nodes.data(), s->nodes.size() * sizeof(Node8));
+}
 extern "C" void emu_destroy(void *h) { delete static_cast<EmuScene *>(h); }
 
 extern "C" void emu_info(void *h, uint32_t *n_nodes, float *tight6, float *enlarged6) {
@@ -94,7 +98,8 @@ extern "C" void emu_info(void *h, uint32_t *n_nodes, float *tight6, float *enlar
     for (int k = 0; k < 3; ++k) { tight6[k] = s->tight_lo[k]; tight6[3 + k] = s->tight_hi[k]; enlarged6[k] = s->box_lo[k]; enlarged6[3 + k] = s->box_hi[k]; }
 }
 
-static uint64_t g_tri_tests = 0;
+static uint64_t g_tri_tests = 0, g_sparse_steps = 0;
+extern "C" uint64_t emu_sparse_steps(void) { uint64_t v = g_sparse_steps; g_sparse_steps = 0; return v; }
 extern "C" uint64_t emu_tri_tests(void) { uint64_t v = g_tri_tests; g_tri_tests = 0; return v; }
 // returns the total number of node visits (traversal statistics)
 extern "C" uint64_t emu_trace(void *h, const RayIn *rays, size_t n, int mode, HitOut *hits) {
@@ -109,7 +114,7 @@ extern "C" uint64_t emu_trace(void *h, const RayIn *rays, size_t n, int mode, Hi
             tr.begin(rays[i], mint, maxt);
             if (mode == 1) { while (!tr.step<true>(nodes, tris)) {} }
             else { while (!tr.step<false>(nodes, tris)) {} }
-            out = tr.hit; steps += tr.steps; g_tri_tests += tr.tri_tests;
+            out = tr.hit; steps += tr.steps; g_tri_tests += tr.tri_tests; g_sparse_steps += tr.sparse_steps;
         }
         hits[i] = out;
     }
