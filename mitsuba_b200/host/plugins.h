@@ -111,6 +111,7 @@ private:
 void loadOBJ(const std::string &path, const Transform &toWorld, bool flipTexCoords, bool collapse, int shapeIndex,
              std::vector<Mesh> &out);
 void loadPLY(const std::string &path, const Transform &toWorld, std::vector<Mesh> &out);
+void loadSerialized(const std::string &path, const Transform &toWorld, int shapeIndex, std::vector<Mesh> &out);   // serializedio.cpp
 // trimesh.cpp:608-681
 void computeNormals(Mesh &m, bool faceNormals, bool flipNormals);
 

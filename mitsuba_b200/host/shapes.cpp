@@ -144,6 +144,16 @@ Shape::Shape(const Properties &p, const std::string &baseDir) : ConfigurableObje
         p.getBoolean("srgb", true);                       // vertex colours are not used by the path
         if (p.hasProperty("maxSmoothAngle")) error("ply: 'maxSmoothAngle' (topology rebuild) is not part of the B200 path.");
         loadPLY(resolvePath(baseDir, p.getString("filename")), p.getTransform("toWorld", Transform()), m_meshes);
+    } else if (type == "serialized") {
+        // serialized.cpp:148-210
+        const int shapeIndex = p.getInteger("shapeIndex", 0);
+        m_faceNormals = p.getBoolean("faceNormals", false);
+        m_flipNormals = p.getBoolean("flipNormals", false);
+        if (p.hasProperty("maxSmoothAngle")) {
+            if (m_faceNormals) error("The properties 'maxSmoothAngle' and 'faceNormals' can't be specified at the same time!");
+            error("serialized: 'maxSmoothAngle' (topology rebuild) is not part of the B200 path.");
+        }
+        loadSerialized(resolvePath(baseDir, p.getString("filename")), p.getTransform("toWorld", Transform()), shapeIndex, m_meshes);
     } else if (type == "rectangle") {
         m_meshes.push_back(makeRectangle(p));
     } else if (type == "cube") {
@@ -151,11 +161,11 @@ Shape::Shape(const Properties &p, const std::string &baseDir) : ConfigurableObje
         m_flipNormals = p.getBoolean("flipNormals", false);
         m_meshes.push_back(makeCube(p));
     } else if (type == "sphere" || type == "disk" || type == "cylinder" || type == "hair" || type == "heightfield") {
-        error("Shape plugin \"" + type + "\" is an analytic primitive; the B200 path intersects triangle meshes (obj, ply, rectangle, cube).");
+        error("Shape plugin \"" + type + "\" is an analytic primitive; the B200 path intersects triangle meshes (obj, ply, serialized, rectangle, cube).");
     } else if (type == "instance" || type == "shapegroup") {
         error("Shape plugin \"" + type + "\": instancing is flattened by the exporter; it is not part of the B200 path.");
     } else {
-        error("Plugin \"" + type + "\" not found -- the B200 path implements the shapes obj, ply, rectangle and cube.");
+        error("Plugin \"" + type + "\" not found -- the B200 path implements the shapes obj, ply, serialized, rectangle and cube.");
     }
 }
 

@@ -181,3 +181,73 @@ def test_include_merges_the_child_scene(tmp_path):
     # ids defined in the included file are visible afterwards (shared NamedObjectMap, scenehandler.cpp:675)
     assert list(d.materials[sh[2].material].reflectance) == pytest.approx([0.3] * 3)
     assert sh[1].material == sh[2].material
+
+
+def _serialized_blob(version, pos, idx, nrm=None, uv=None, col=None, double=False, name="m"):
+    """One mesh of a .serialized container (TriMesh::serialize, src/librender/trimesh.cpp:838-905)."""
+    import zlib
+    flags = (0x2000 if double else 0x1000) | (1 if nrm is not None else 0) | (2 if uv is not None else 0) | (8 if col is not None else 0)
+    ft = "<f8" if double else "<f4"
+    body = struct.pack("<I", flags)
+    if version == 4:
+        body += name.encode() + b"\0"
+    body += struct.pack("<QQ", pos.shape[0], idx.shape[0]) + pos.astype(ft).tobytes()
+    for a in (nrm, uv, col):
+        if a is not None:
+            body += a.astype(ft).tobytes()
+    body += idx.astype("<u4").tobytes()
+    return struct.pack("<HH", 0x041C, version) + zlib.compress(body)
+
+
+def _write_serialized(path, version, blobs):
+    offsets, data = [], b""
+    for b in blobs:
+        offsets.append(len(data))
+        data += b
+    data += b"".join(struct.pack("<Q" if version == 4 else "<I", o) for o in offsets) + struct.pack("<I", len(blobs))
+    path.write_bytes(data)
+
+
+@pytest.mark.parametrize("version,double", [(3, False), (4, False), (4, True)])
+def test_serialized_container(tmp_path, version, double):
+    """`serialized` shape plugin (serialized.cpp:148-210, trimesh.cpp:175-298): both container versions, float and double
+    payloads, the shape dictionary at the end of the file, toWorld incl. the handedness flip, optional arrays."""
+    rng = np.random.default_rng(version * 2 + double)
+    meshes = []
+    for k in range(3):
+        nv, nt = 5 + 3 * k, 4 + k
+        pos = rng.normal(size=(nv, 3)).astype(np.float32)
+        idx = np.stack([rng.permutation(nv)[:3] for _ in range(nt)]).astype(np.uint32)
+        nrm = rng.normal(size=(nv, 3)).astype(np.float32)
+        nrm /= np.linalg.norm(nrm, axis=1, keepdims=True)
+        uv = rng.random((nv, 2)).astype(np.float32)
+        meshes.append((pos, idx, nrm if k != 1 else None, uv if k != 2 else None, rng.random((nv, 3)).astype(np.float32) if k == 0 else None))
+    _write_serialized(tmp_path / "m.serialized", version,
+                      [_serialized_blob(version, p, i, n, u, c, double, "mesh%d" % k) for k, (p, i, n, u, c) in enumerate(meshes)])
+    for k, (p, i, n, u, c) in enumerate(meshes):
+        hs = load_dir(tmp_path, '<shape type="serialized"><string name="filename" value="m.serialized"/><integer name="shapeIndex" value="%d"/></shape>' % k)
+        pos, nrm, uv, idx = hs.arrays()
+        assert np.array_equal(pos, p) and np.array_equal(idx, i)
+        sh = hs.shapes()[0]
+        assert sh.has_texcoords == (u is not None)
+        if u is not None:
+            assert np.array_equal(uv, u)
+        if n is not None:
+            assert np.allclose(nrm, n, atol=1e-6)
+        else:                              # no normals in the file: smooth normals are generated (trimesh.cpp:446-530)
+            assert sh.has_normals and np.allclose(np.linalg.norm(nrm, axis=1), 1, atol=1e-5)
+    # mirrored toWorld: positions transformed, winding swapped (serialized.cpp:197-202)
+    hs = load_dir(tmp_path, '<shape type="serialized"><string name="filename" value="m.serialized"/>'
+                            '<transform name="toWorld"><scale x="-2"/><translate y="1"/></transform></shape>')
+    pos, nrm, uv, idx = hs.arrays()
+    p, i = meshes[0][0], meshes[0][1]
+    assert np.allclose(pos, p * [-2, 1, 1] + [0, 1, 0], atol=1e-6)
+    assert np.array_equal(idx, i[:, [1, 0, 2]])
+    for body, msg in (('<integer name="shapeIndex" value="7"/>', "shape index is out of range"), ('<integer name="shapeIndex" value="-1"/>', "nonnegative")):
+        with pytest.raises(MtsbError) as ei:
+            load_dir(tmp_path, '<shape type="serialized"><string name="filename" value="m.serialized"/>%s</shape>' % body)
+        assert msg in str(ei.value)
+    (tmp_path / "bad.serialized").write_bytes(struct.pack("<HH", 0x1C04, 3) + b"xx")
+    with pytest.raises(MtsbError) as ei:
+        load_dir(tmp_path, '<shape type="serialized"><string name="filename" value="bad.serialized"/></shape>')
+    assert "old version of Mitsuba" in str(ei.value)
