@@ -39,7 +39,7 @@
 extern "C" {
 #endif
 
-#define MTSB_ABI_VERSION 4
+#define MTSB_ABI_VERSION 5
 
 /* ---- status codes ---------------------------------------------------- */
 enum {
@@ -74,8 +74,36 @@ typedef struct MtsbMaterial {
     float    cond_eta[3];     /* roughconductor eta/extEta (roughconductor.cpp:189)   */
     float    cond_k[3];       /* roughconductor k/extEta                              */
     float    spec_weight;     /* plastic: m_specularSamplingWeight (plastic.cpp:199-204) */
-    float    _pad1[3];
+    uint32_t tex_reflectance; /* 1 + index into MtsbSceneDesc::textures of the texture that replaces `reflectance`, 0 = constant */
+    uint32_t tex_transmittance; /* same for `transmittance`                            */
+    uint32_t _pad1;
 } MtsbMaterial;              /* 96 bytes */
+
+/* ---- textures (reference: src/textures/{bitmap,checkerboard,gridtexture,scale}.cpp, src/librender/texture.cpp) ----
+ * A texture replaces a constant spectrum of a material and is evaluated at the hit's uv (Texture2D::eval,
+ * texture.cpp:112-121): uv' = uv * uv_scale + uv_offset.  `scale` plugins are folded into `scale`.
+ * bitmap: texels are kept in half precision as the reference keeps them (bitmap.cpp:172-177); filter NEAREST /
+ * BILINEAR look up level 0 (mipmap.h:565-596); TRILINEAR / EWA use the Lanczos-2 MIP pyramid (mipmap.h:248-276,
+ * built at scene creation) with the uv partials of the camera ray on the first hit (intersection.cpp:5-98,
+ * mipmap.h:628-716) and the level-0 bilinear lookup on every later hit (bitmap.cpp:431-453).                */
+enum { MTSB_TEX_BITMAP = 0, MTSB_TEX_CHECKERBOARD = 1, MTSB_TEX_GRID = 2 };
+enum { MTSB_TEXFILTER_NEAREST = 0, MTSB_TEXFILTER_BILINEAR = 1, MTSB_TEXFILTER_TRILINEAR = 2, MTSB_TEXFILTER_EWA = 3 }; /* mipmap.h:54-63 */
+enum { MTSB_WRAP_CLAMP = 0, MTSB_WRAP_REPEAT = 1, MTSB_WRAP_MIRROR = 2, MTSB_WRAP_ZERO = 3, MTSB_WRAP_ONE = 4 };  /* rfilter.h:53-64 EBoundaryCondition, same numbering */
+
+typedef struct MtsbTexture {
+    uint32_t type;                  /* MTSB_TEX_*                                        */
+    uint32_t filter;                /* bitmap: MTSB_TEXFILTER_*                          */
+    uint32_t wrap_u, wrap_v;        /* bitmap: MTSB_WRAP_*                               */
+    float    uv_scale[2];           /* Texture2D `uscale`/`vscale` (texture.cpp:87-91)   */
+    float    uv_offset[2];          /* `uoffset`/`voffset`                               */
+    float    color0[3], color1[3];  /* checkerboard.cpp:46-47 / gridtexture.cpp:47-48    */
+    float    line_width;            /* gridtexture `lineWidth`                           */
+    float    scale[3];              /* product of the enclosing `scale` textures (scale.cpp:70), 1 = none */
+    float    max_anisotropy;        /* bitmap `maxAnisotropy` (bitmap.cpp:232-235)       */
+    int32_t  width, height;         /* bitmap: level-0 size, < 65536 each                */
+    int32_t  channels;              /* bitmap: 1 (luminance) or 3 (linear RGB)           */
+    const float *texels;            /* bitmap: width*height*channels linear values, row-major, row 0 = v 0 */
+} MtsbTexture;                      /* 96 bytes */
 
 /* ---- shapes: every shape is a triangle mesh (createTriMesh'd on the host) */
 typedef struct MtsbShape {
@@ -169,6 +197,9 @@ typedef struct MtsbSceneDesc {
     MtsbIntegrator  integrator;
     MtsbSampler     sampler;        /* zero-initialised = independent                  */
     const MtsbEnvmap *envmap;       /* required iff an emitter has type MTSB_EMITTER_ENVMAP, else NULL */
+    const MtsbTexture *textures;    /* n_textures records, NULL when there are none     */
+    uint32_t n_textures;
+    uint32_t _pad;
 } MtsbSceneDesc;
 
 /* ---- rays and hit records (cfg 4 and the parity tests) ---------------- */

@@ -8,7 +8,7 @@ import ctypes as C
 
 import numpy as np
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 OK, ERR_INVALID, ERR_NO_DEVICE, ERR_CUDA, ERR_CANCELLED, ERR_IO, ERR_PARSE = range(7)
 BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_ROUGHDIELECTRIC, BSDF_NULL, BSDF_DIELECTRIC, BSDF_CONDUCTOR, BSDF_PLASTIC = range(7)
@@ -20,13 +20,17 @@ TRACE_CLOSEST, TRACE_ANY = 0, 1
 NO_HIT = 0xFFFFFFFF
 RENDER_KEEP_FILM = 1
 SAMPLER_INDEPENDENT, SAMPLER_LDSAMPLER, SAMPLER_HALTON, SAMPLER_SOBOL = 0, 1, 2, 3
+TEX_BITMAP, TEX_CHECKERBOARD, TEX_GRID = 0, 1, 2
+TEXFILTER_NEAREST, TEXFILTER_BILINEAR, TEXFILTER_TRILINEAR, TEXFILTER_EWA = 0, 1, 2, 3
+WRAP_CLAMP, WRAP_REPEAT, WRAP_MIRROR, WRAP_ZERO, WRAP_ONE = 0, 1, 2, 3, 4
 
 
 class Material(C.Structure):
     _fields_ = [("type", C.c_uint32), ("flags", C.c_uint32), ("distribution", C.c_uint32), ("back", C.c_int32),
                 ("alpha_u", C.c_float), ("alpha_v", C.c_float), ("eta", C.c_float), ("fdr_int", C.c_float),
                 ("reflectance", C.c_float * 3), ("transmittance", C.c_float * 3),
-                ("cond_eta", C.c_float * 3), ("cond_k", C.c_float * 3), ("spec_weight", C.c_float), ("_pad1", C.c_float * 3)]
+                ("cond_eta", C.c_float * 3), ("cond_k", C.c_float * 3), ("spec_weight", C.c_float),
+                ("tex_reflectance", C.c_uint32), ("tex_transmittance", C.c_uint32), ("_pad1", C.c_uint32)]
 
 
 class Shape(C.Structure):
@@ -61,6 +65,13 @@ class Envmap(C.Structure):
                 ("to_local", C.c_float * 16), ("scale", C.c_float), ("_pad", C.c_uint32 * 3)]
 
 
+class Texture(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("filter", C.c_uint32), ("wrap_u", C.c_uint32), ("wrap_v", C.c_uint32),
+                ("uv_scale", C.c_float * 2), ("uv_offset", C.c_float * 2), ("color0", C.c_float * 3), ("color1", C.c_float * 3),
+                ("line_width", C.c_float), ("scale", C.c_float * 3), ("max_anisotropy", C.c_float),
+                ("width", C.c_int32), ("height", C.c_int32), ("channels", C.c_int32), ("texels", C.POINTER(C.c_float))]
+
+
 class SceneDesc(C.Structure):
     _fields_ = [("abi_version", C.c_uint32), ("n_shapes", C.c_uint32), ("n_materials", C.c_uint32),
                 ("n_emitters", C.c_uint32), ("n_vertices", C.c_uint64), ("n_tris", C.c_uint64),
@@ -68,7 +79,7 @@ class SceneDesc(C.Structure):
                 ("positions", C.POINTER(C.c_float)), ("normals", C.POINTER(C.c_float)),
                 ("texcoords", C.POINTER(C.c_float)), ("indices", C.POINTER(C.c_uint32)),
                 ("sensor", Sensor), ("integrator", Integrator), ("sampler", Sampler),
-                ("envmap", C.POINTER(Envmap))]
+                ("envmap", C.POINTER(Envmap)), ("textures", C.POINTER(Texture)), ("n_textures", C.c_uint32), ("_pad", C.c_uint32)]
 
 
 class RenderParams(C.Structure):

@@ -6,6 +6,7 @@
 #include "scene.h"
 #include "trace.cuh"
 #include "qmc_host.h"
+#include "texture_host.h"
 #include <map>
 #include <mutex>
 #include <cmath>
@@ -182,6 +183,16 @@ static int validate(const MtsbSceneDesc *d) {
     for (uint32_t i = 0; i < d->n_materials; ++i) {
         const MtsbMaterial &m = d->materials[i];
         if (m.type > MTSB_BSDF_PLASTIC || m.distribution > MTSB_DISTR_GGX || m.back >= (int32_t) d->n_materials) { set_error("bad material record"); return MTSB_ERR_INVALID; }
+        if (m.tex_reflectance > d->n_textures || m.tex_transmittance > d->n_textures) { set_error("material refers to a missing texture"); return MTSB_ERR_INVALID; }
+    }
+    if (d->n_textures && !d->textures) { set_error("scene description: NULL texture array"); return MTSB_ERR_INVALID; }
+    for (uint32_t i = 0; i < d->n_textures; ++i) {
+        const MtsbTexture &t = d->textures[i];
+        if (t.type > MTSB_TEX_GRID) { set_error("bad texture type"); return MTSB_ERR_INVALID; }
+        if (t.type == MTSB_TEX_BITMAP) {
+            if (t.filter > MTSB_TEXFILTER_EWA || t.wrap_u > MTSB_WRAP_ONE || t.wrap_v > MTSB_WRAP_ONE) { set_error("bitmap texture: bad filter type / wrap mode"); return MTSB_ERR_INVALID; }
+            if (!t.texels || t.width <= 0 || t.height <= 0 || t.width > 0xFFFF || t.height > 0xFFFF || (t.channels != 1 && t.channels != 3)) { set_error("bitmap texture: bad image"); return MTSB_ERR_INVALID; }
+        }
     }
     int n_env = 0;
     for (uint32_t i = 0; i < d->n_emitters; ++i) {
@@ -207,7 +218,7 @@ static int validate(const MtsbSceneDesc *d) {
 static float rfilter_eval(const MtsbSensor &se, float x) {
     if (se.rfilter == MTSB_RFILTER_GAUSSIAN) {      // gaussian.cpp:50-55
         float alpha = -1.0f / (2.0f * se.rfilter_stddev * se.rfilter_stddev);
-        return std::max(0.0f, std::exp(alpha * x * x) - std::exp(alpha * se.rfilter_radius * se.rfilter_radius));
+        return std::max(0.0f, (float) std::exp((double) (alpha * x * x)) - (float) std::exp((double) (alpha * se.rfilter_radius * se.rfilter_radius)));   // math::fastexp (math.h:175-199)
     }
     return std::fabs(x) <= se.rfilter_radius ? 1.0f : 0.0f;   // box.cpp:36-50
 }
@@ -335,6 +346,36 @@ extern "C" int mtsb_scene_create(const MtsbSceneDesc *d, mtsb_scene_t *out) {
         if ((rc = dev_upload(s, &ev.cdf_cols, cdf_cols.data(), cdf_cols.size()))) return fail(rc);
         if ((rc = dev_upload(s, &ev.row_weights, row_w.data(), row_w.size()))) return fail(rc);
         if ((rc = dev_upload(s, &v.envmap, &ev, 1))) return fail(rc);
+    }
+    v.textures = nullptr; v.n_textures = d->n_textures;
+    if (d->n_textures) {
+        // texture records; a bitmap brings its MIP pyramid (texture_host.h) in half precision and, for EWA, the Gaussian
+        // weight table of mipmap.h:296-302 (shared by all textures)
+        std::vector<TextureView> tvs(d->n_textures);
+        std::vector<HalfTexel> texels;
+        float lut[MTSB_MIPMAP_LUT_SIZE];
+        for (int i = 0; i < MTSB_MIPMAP_LUT_SIZE; ++i) {
+            const float r2 = (float) i / (float) (MTSB_MIPMAP_LUT_SIZE - 1);
+            lut[i] = (float) std::exp((double) (-2.0f * r2)) - (float) std::exp((double) -2.0f);     // math::fastexp, math.h:175-199
+        }
+        const float *d_lut = nullptr;
+        if ((rc = dev_upload(s, &d_lut, lut, (size_t) MTSB_MIPMAP_LUT_SIZE))) return fail(rc);
+        for (uint32_t i = 0; i < d->n_textures; ++i) {
+            const MtsbTexture &t = d->textures[i];
+            TextureView &tv = tvs[i];
+            std::memset(&tv, 0, sizeof(tv));
+            tv.type = t.type; tv.filter = t.filter; tv.wrap_u = t.wrap_u; tv.wrap_v = t.wrap_v;
+            for (int k = 0; k < 2; ++k) { tv.uv_scale[k] = t.uv_scale[k]; tv.uv_offset[k] = t.uv_offset[k]; }
+            for (int k = 0; k < 3; ++k) { tv.color0[k] = t.color0[k]; tv.color1[k] = t.color1[k]; tv.scale[k] = t.scale[k]; }
+            tv.line_width = t.line_width;
+            tv.max_anisotropy = t.filter == MTSB_TEXFILTER_EWA ? t.max_anisotropy : 1.0f;       // bitmap.cpp:232-235
+            tv.weight_lut = d_lut;
+            if (t.type == MTSB_TEX_BITMAP) build_texture_levels(t, tv, texels);
+        }
+        const HalfTexel *d_texels = nullptr;
+        if (!texels.empty() && (rc = dev_upload(s, &d_texels, texels.data(), texels.size()))) return fail(rc);
+        for (TextureView &tv : tvs) tv.texels = d_texels;
+        if ((rc = dev_upload(s, &v.textures, tvs.data(), tvs.size()))) return fail(rc);
     }
     {   // sample generator tables (halton: primes + digit permutations, halton.cpp:139-149, faure.cpp:22-84)
         const char *err = "";

@@ -93,6 +93,7 @@ MTSB_HD float lengthSquared(V3 a) { return dot(a, a); }
 MTSB_HD float length(V3 a) { return fsqrt(dot(a, a)); }
 MTSB_HD V3 normalize(V3 a) { return a / length(a); }
 MTSB_HD bool isZero(V3 a) { return a.x == 0 && a.y == 0 && a.z == 0; }
+MTSB_HD float comp(V3 a, int i) { return i == 0 ? a.x : i == 1 ? a.y : a.z; }
 MTSB_HD float maxComp(V3 a) { return fmaxf(a.x, fmaxf(a.y, a.z)); }
 MTSB_HD V3 vmin(V3 a, V3 b) { return V3(fminf(a.x, b.x), fminf(a.y, b.y), fminf(a.z, b.z)); }
 MTSB_HD V3 vmax(V3 a, V3 b) { return V3(fmaxf(a.x, b.x), fmaxf(a.y, b.y), fmaxf(a.z, b.z)); }
@@ -104,6 +105,7 @@ struct P2 { float x, y; };
 
 // include/mitsuba/core/constants.h:28-31,62-68 (single precision build of the reference)
 #define MTSB_EPSILON 1e-4f
+#define MTSB_RCPOVERFLOW 2.93873587705571876e-39f   /* constants.h:53 */
 #define MTSB_SHADOW_EPSILON 1e-3f
 #define MTSB_PI 3.14159265358979323846f
 #define MTSB_INV_PI 0.31830988618379067154f

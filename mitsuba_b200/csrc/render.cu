@@ -183,7 +183,11 @@ __host__ __device__ inline int queue_of_material(const MtsbMaterial *mats, int m
     if (mat < 0) return Q_NULL;
     const MtsbMaterial &m = mats[mat];
     const int q = queue_of_type(m.type);
-    if ((m.flags & MTSB_MAT_TWOSIDED) && m.back >= 0 && queue_of_type(mats[m.back].type) != q) return Q_GENERIC;
+    if (m.tex_reflectance | m.tex_transmittance) return Q_TEXTURED;
+    if ((m.flags & MTSB_MAT_TWOSIDED) && m.back >= 0) {
+        if (mats[m.back].tex_reflectance | mats[m.back].tex_transmittance) return Q_TEXTURED;
+        if (queue_of_type(mats[m.back].type) != q) return Q_GENERIC;
+    }
     return q;
 }
 #define MTSB_SORT_BLOCK 512
@@ -216,7 +220,7 @@ __global__ void __launch_bounds__(MTSB_SORT_BLOCK) k_sort(SceneView sc, PathBuff
 struct RenderConst { int max_depth, rr_depth, strict_normals, hide_emitters; };
 
 template <int Q> __device__ __forceinline__ V3 eval_q(const MtsbMaterial *mats, int id, V3 wi, V3 wo) {
-    if (Q == Q_GENERIC) return bsdf_eval(mats, id, wi, wo);
+    if (Q == Q_GENERIC || Q == Q_TEXTURED) return bsdf_eval(mats, id, wi, wo);
     const MtsbMaterial &m = resolve_twosided_eval(mats, mats[id], wi, wo);
     if (Q == Q_DIFFUSE) return diffuse_eval(m, wi, wo);
     if (Q == Q_CONDUCTOR) return roughconductor_eval(m, wi, wo);
@@ -224,7 +228,7 @@ template <int Q> __device__ __forceinline__ V3 eval_q(const MtsbMaterial *mats, 
     return V3(0.0f);
 }
 template <int Q> __device__ __forceinline__ float pdf_q(const MtsbMaterial *mats, int id, V3 wi, V3 wo) {
-    if (Q == Q_GENERIC) return bsdf_pdf(mats, id, wi, wo);
+    if (Q == Q_GENERIC || Q == Q_TEXTURED) return bsdf_pdf(mats, id, wi, wo);
     const MtsbMaterial &m = resolve_twosided_eval(mats, mats[id], wi, wo);
     if (Q == Q_DIFFUSE) return diffuse_pdf(wi, wo);
     if (Q == Q_CONDUCTOR) return roughconductor_pdf(m, wi, wo);
@@ -232,7 +236,7 @@ template <int Q> __device__ __forceinline__ float pdf_q(const MtsbMaterial *mats
     return 0.0f;
 }
 template <int Q> __device__ __forceinline__ bool sample_q(const MtsbMaterial *mats, int id, V3 wi, P2 u, float u1, BsdfSample &s) {
-    if (Q == Q_GENERIC) return bsdf_sample(mats, id, wi, u, u1, s);
+    if (Q == Q_GENERIC || Q == Q_TEXTURED) return bsdf_sample(mats, id, wi, u, u1, s);
     const MtsbMaterial *m = &mats[id];
     bool flip = false;
     if ((m->flags & MTSB_MAT_TWOSIDED) && cosTheta(wi) < 0) { wi.z *= -1; flip = true; if (m->back >= 0) m = &mats[m->back]; }
@@ -244,6 +248,39 @@ template <int Q> __device__ __forceinline__ bool sample_q(const MtsbMaterial *ma
     else ok = false;
     if (flip && ok && !isZero(s.weight) && s.pdf != 0) s.wo.z *= -1;
     return ok;
+}
+
+// Q_TEXTURED: the record(s) a hit shades with -- the shape's material (and the back side of a twosided adapter) with every
+// textured spectrum replaced by the texture's value at the hit (diffuse.cpp:118 m_reflectance->eval(bRec.its), ...).
+// Camera-ray hits on a BSDF that usesRayDifferentials() (a bitmap texture: bitmap.cpp:547-549) carry uv partials
+// (records.inl:82-90, intersection.cpp:5-98); every later hit is looked up unfiltered.
+__device__ __noinline__ void resolve_textured(const SceneView &sc, int mat, const Its &its, bool first, float2 spos, V3 cam, MtsbMaterial *lm) {
+    lm[0] = sc.materials[mat];
+    int n = 1;
+    if ((lm[0].flags & MTSB_MAT_TWOSIDED) && lm[0].back >= 0) { lm[1] = sc.materials[lm[0].back]; lm[0].back = 1; n = 2; }
+    UVPartials pt; pt.has = false; pt.dudx = pt.dvdx = pt.dudy = pt.dvdy = 0.0f;
+    if (first) {
+        bool bitmap = false;
+        for (int i = 0; i < n; ++i) {
+            if (lm[i].tex_reflectance) bitmap |= sc.textures[lm[i].tex_reflectance - 1].type == MTSB_TEX_BITMAP;
+            if (lm[i].tex_transmittance) bitmap |= sc.textures[lm[i].tex_transmittance - 1].type == MTSB_TEX_BITMAP;
+        }
+        if (bitmap) {
+            V3 rxd, ryd;
+            sensor_ray_differentials(sc.sensor, sc.near_x, sc.near_y, spos.x, spos.y, sc.integrator.sample_count, rxd, ryd);
+            pt = compute_partials(its.p, its.sh.n, its.dpdu, its.dpdv, cam, rxd, ryd);
+        }
+    }
+    for (int i = 0; i < n; ++i) {
+        if (lm[i].tex_reflectance) {
+            const V3 c = texture_eval(sc.textures[lm[i].tex_reflectance - 1], its.uv, pt);
+            lm[i].reflectance[0] = c.x; lm[i].reflectance[1] = c.y; lm[i].reflectance[2] = c.z;
+        }
+        if (lm[i].tex_transmittance) {
+            const V3 c = texture_eval(sc.textures[lm[i].tex_transmittance - 1], its.uv, pt);
+            lm[i].transmittance[0] = c.x; lm[i].transmittance[1] = c.y; lm[i].transmittance[2] = c.z;
+        }
+    }
 }
 
 template <int Q, bool QMC>
@@ -325,10 +362,17 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBu
                 int px, py; uint32_t s_local; slot_pixel(sc, pb, ps, slot, px, py, s_local);
                 const SampleStream ss = slot_stream(sc, ps, px, py, s_local);
                 ss.block4((uint32_t) depth, 0, u);
-                const MtsbMaterial &m0 = sc.materials[mat];
+                MtsbMaterial lm[Q == Q_TEXTURED ? 2 : 1];
+                const MtsbMaterial *mats = sc.materials;
+                int mid = mat;
+                if (Q == Q_TEXTURED) {
+                    resolve_textured(sc, mat, its, first, first ? pb.spos[slot] : make_float2(0.0f, 0.0f), V3(ray.ox, ray.oy, ray.oz), lm);
+                    mats = lm; mid = 0;
+                }
+                const MtsbMaterial &m0 = mats[mid];
                 if (!bsdf_has_back_or_transmission(m0)) dRec.refN = its.sh.n;              // records.inl:175-179
                 // ---- direct illumination (path.cpp:174-202): only for BSDFs with a smooth component (:176-177) ----
-                const bool smooth = Q == Q_DELTA ? false : Q == Q_GENERIC ? bsdf_is_smooth(sc.materials, m0) : true;
+                const bool smooth = Q == Q_DELTA ? false : (Q == Q_GENERIC || Q == Q_TEXTURED) ? bsdf_is_smooth(mats, m0) : true;
                 const bool qmc = QMC;
                 if (qmc && smooth) {             // path.cpp:178: the emitter sample is drawn only for smooth BSDFs
                     const QmcDraw qd = qmc_draw(sc.sampler, ps.seed, px + sc.sensor.crop_x, py + sc.sensor.crop_y, ps.s_first + s_local, fl, 2, u[0], u[1]);
@@ -340,11 +384,11 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBu
                 if (smooth) value = sample_emitter_direct(sc, dRec, ue);
                 if (dRec.pdf != 0 && !isZero(value)) {
                     const V3 wo = its.sh.toLocal(dRec.d);
-                    const V3 bsdfVal = eval_q<Q>(sc.materials, mat, its.wi, wo);
+                    const V3 bsdfVal = eval_q<Q>(mats, mid, its.wi, wo);
                     if (!isZero(bsdfVal) && (!rc.strict_normals || dot(its.geoN, dRec.d) * cosTheta(wo) > 0)) {
                         const MtsbEmitter &em = sc.emitters[dRec.emitter];
                         const bool onSurface = em.type != MTSB_EMITTER_POINT;
-                        const float bp = (onSurface && dRec.measure == MTSB_MEASURE_SOLID_ANGLE) ? pdf_q<Q>(sc.materials, mat, its.wi, wo) : 0.0f;
+                        const float bp = (onSurface && dRec.measure == MTSB_MEASURE_SOLID_ANGLE) ? pdf_q<Q>(mats, mid, its.wi, wo) : 0.0f;
                         const V3 contrib = thr * value * bsdfVal * mi_weight(dRec.pdf, bp);
                         // shadow segment of Scene::sampleEmitterDirect (scene.cpp:840-846)
                         RayIn sr; sr.ox = dRec.ref.x; sr.oy = dRec.ref.y; sr.oz = dRec.ref.z; sr.dx = dRec.d.x; sr.dy = dRec.d.y; sr.dz = dRec.d.z;
@@ -361,9 +405,9 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBu
                     const QmcDraw qd = qmc_draw(sc.sampler, ps.seed, px + sc.sensor.crop_x, py + sc.sensor.crop_y, ps.s_first + s_local, fl, 2, u[2], u[3]);
                     u[2] = qd.a; u[3] = qd.b; fl = qd.fl;
                 }
-                if (Q == Q_DIELECTRIC || Q == Q_GENERIC) {
+                if (Q == Q_DIELECTRIC || Q == Q_GENERIC || Q == Q_TEXTURED) {
                     bool need = (Q == Q_DIELECTRIC);
-                    if (Q == Q_GENERIC) need = sc.materials[bsdf_effective_material(sc.materials, mat, its.wi.z)].type == MTSB_BSDF_ROUGHDIELECTRIC;
+                    if (Q == Q_GENERIC || Q == Q_TEXTURED) need = mats[bsdf_effective_material(mats, mid, its.wi.z)].type == MTSB_BSDF_ROUGHDIELECTRIC;
                     if (need) {
                         float v[4]; ss.block4((uint32_t) depth, 1, v); u1 = v[0];
                         if (qmc) {               // roughdielectric.cpp:554
@@ -374,7 +418,7 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBu
                 }
                 BsdfSample bs;
                 P2 ub; ub.x = u[2]; ub.y = u[3];
-                const bool ok = sample_q<Q>(sc.materials, mat, its.wi, ub, u1, bs);
+                const bool ok = sample_q<Q>(mats, mid, its.wi, ub, u1, bs);
                 if (ok && !isZero(bs.weight)) {
                     fl |= PF_SCATTERED;
                     const V3 wo = its.sh.toWorld(bs.wo);
@@ -386,7 +430,7 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBu
                         spawn_slot = slot;
                         thr *= bs.weight; eta *= bs.eta;
                         pb.thr_eta[slot] = make_float4(thr.x, thr.y, thr.z, eta);
-                        const bool delta = (Q == Q_DELTA || Q == Q_GENERIC) && bs.delta;
+                        const bool delta = (Q == Q_DELTA || Q == Q_GENERIC || Q == Q_TEXTURED) && bs.delta;
                         pb.L_bpdf[slot] = make_float4(L.x, L.y, L.z, delta ? -bs.pdf : bs.pdf);
                         fl = (fl & ~(PF_DEPTH_MASK | PF_FIRST)) | ((uint32_t) depth & PF_DEPTH_MASK);
                         pb.refn_flags[slot] = make_float4(dRec.refN.x, dRec.refN.y, dRec.refN.z, __uint_as_float(fl));
@@ -843,6 +887,7 @@ static int lane_bounce(Scene *s, Lane &L, const RenderConst &rcst, int sm_count)
     if (qm & (1u << Q_CONDUCTOR))  { if (qmc) k_shade<Q_CONDUCTOR, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_CONDUCTOR, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
     if (qm & (1u << Q_DIELECTRIC)) { if (qmc) k_shade<Q_DIELECTRIC, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_DIELECTRIC, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
     if (qm & (1u << Q_NULL))       { if (qmc) k_shade<Q_NULL, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_NULL, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
+    if (qm & (1u << Q_TEXTURED))   { if (qmc) k_shade<Q_TEXTURED, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_TEXTURED, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
     if (qm & (1u << Q_GENERIC))    { if (qmc) k_shade<Q_GENERIC, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_GENERIC, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
     if (qm & (1u << Q_DELTA))      { if (qmc) k_shade<Q_DELTA, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_DELTA, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
     k_miss<<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, rcst, L.cur);

@@ -7,8 +7,9 @@ namespace mtsb {
 
 // Shading queues: one per scattering model so that every k_shade instance runs one code path.
 // Q_CONDUCTOR / Q_DIELECTRIC are the rough (microfacet) models, Q_DELTA the smooth `dielectric` and
-// `conductor` (Dirac lobes: no emitter sampling), Q_GENERIC twosided wrappers that mix two models.
-enum { Q_DIFFUSE = 0, Q_CONDUCTOR = 1, Q_DIELECTRIC = 2, Q_NULL = 3, Q_GENERIC = 4, Q_DELTA = 5, Q_MISS = 6, Q_COUNT = 7 };
+// `conductor` (Dirac lobes: no emitter sampling), Q_GENERIC twosided wrappers that mix two models,
+// Q_TEXTURED materials whose spectra come from a texture (evaluated at the hit, then shaded like Q_GENERIC).
+enum { Q_DIFFUSE = 0, Q_CONDUCTOR = 1, Q_DIELECTRIC = 2, Q_NULL = 3, Q_GENERIC = 4, Q_DELTA = 5, Q_TEXTURED = 6, Q_MISS = 7, Q_COUNT = 8 };
 
 // path flags (stored as float bits in refn_flags.w)
 #define PF_DEPTH_MASK 0xFFFFu

@@ -4,6 +4,7 @@
 #include "bvh.h"
 #include "qmc.h"
 #include "envmap.h"
+#include "texture.h"
 
 namespace mtsb {
 
@@ -24,6 +25,8 @@ struct SceneView {
     const float *inv_area;                  // per shape
     int env_emitter;                        // index of the environment emitter (`constant` or `envmap`) or -1
     const EnvmapView *envmap;               // device copy of the `envmap` tables, or NULL
+    const TextureView *textures;            // device copies of the texture records (src/textures), or NULL
+    uint32_t n_textures;
     float bsphere_c[3], bsphere_r;          // constant.cpp:67-71
     // sensor (perspective.cpp:127-150, 286-317)
     MtsbSensor sensor; float near_x, near_y;

@@ -1,6 +1,6 @@
 // sensor.h -- PerspectiveCamera::sampleRayDifferential (reference: src/sensors/perspective.cpp:286-317,
-// projection set-up :127-150, sensor.cpp:225-309).  Ray differentials are not produced: every
-// texture on this path is constant.
+// projection set-up :127-150, sensor.cpp:225-309).  The offset rays of the differential (perspective.cpp:160-163,
+// 310-314) are recomputed from the stored sample position where a bitmap texture needs them (sensor_ray_differentials).
 #pragma once
 #include "../../include/mtsb200.h"
 #include "traverse.h"
@@ -37,6 +37,23 @@ MTSB_HD void sensor_ray(const MtsbSensor &se, float near_x, float near_y, float 
     float a = fdiv(fadd(px, (float) se.crop_x), (float) se.film_width);
     float b = fdiv(fadd(py, (float) se.crop_y), (float) se.film_height);
     sensor_ray_frac(se, near_x, near_y, a, b, ray);
+}
+
+// Directions of the two offset rays of a camera ray (both start at the camera position): perspective.cpp:312-313 with
+// m_dx / m_dy = one pixel on the near plane (:160-163), then RayDifferential::scaleDifferential(1 / sqrt(sampleCount))
+// (ray.h:174-179, integrator.cpp:200-201, 237).
+MTSB_HD void sensor_ray_differentials(const MtsbSensor &se, float near_x, float near_y, float px, float py, int sample_count,
+                                      V3 &rxd, V3 &ryd) {
+    const float a = fdiv(fadd(px, (float) se.crop_x), (float) se.film_width);
+    const float b = fdiv(fadd(py, (float) se.crop_y), (float) se.film_height);
+    const V3 nearP(fmul(fsub(1.0f, fmul(2.0f, a)), near_x), fmul(fsub(1.0f, fmul(2.0f, b)), near_y), se.near_clip);
+    const float dxx = fdiv(fmul(-2.0f, near_x), (float) se.film_width), dyy = fdiv(fmul(-2.0f, near_y), (float) se.film_height);
+    const V3 d = xform_vec(se.to_world, normalize(nearP));
+    const V3 rx = xform_vec(se.to_world, normalize(V3(fadd(nearP.x, dxx), nearP.y, nearP.z)));
+    const V3 ry = xform_vec(se.to_world, normalize(V3(nearP.x, fadd(nearP.y, dyy), nearP.z)));
+    const float amount = fdiv(1.0f, fsqrt((float) (sample_count > 1 ? sample_count : 1)));
+    rxd = d + (rx - d) * amount;
+    ryd = d + (ry - d) * amount;
 }
 
 }  // namespace mtsb

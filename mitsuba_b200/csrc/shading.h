@@ -33,6 +33,7 @@ MTSB_HD void coordinateSystem(V3 a, V3 &b, V3 &c) {
 
 struct Its {
     V3 p, geoN; Frame3 sh; P2 uv; V3 wi; uint32_t shape;
+    V3 dpdu, dpdv;          // position partials (skdtree.h:373-380): uv tangents where the mesh has texture coordinates
 };
 
 MTSB_HD void fill_intersection(const SceneView &sc, V3 ray_d, uint32_t prim, float hu, float hv, Its &its) {
@@ -57,11 +58,22 @@ MTSB_HD void fill_intersection(const SceneView &sc, V3 ray_d, uint32_t prim, flo
     if (sh.has_texcoords && sc.texcoords) {
         const float *t0 = sc.texcoords + 2 * (size_t) i0, *t1 = sc.texcoords + 2 * (size_t) i1, *t2 = sc.texcoords + 2 * (size_t) i2;
         its.uv.x = t0[0] * b.x + t1[0] * b.y + t2[0] * b.z; its.uv.y = t0[1] * b.x + t1[1] * b.y + t2[1] * b.z;
-    } else { its.uv.x = b.y; its.uv.y = b.z; }
+        // TriMesh::computeUVTangents (trimesh.cpp:683-735): this fork's TriMesh::configure always builds the tangents of a
+        // mesh that has texture coordinates (trimesh.cpp:383-385), and fillIntersectionRecord then takes dpdu / dpdv from them
+        const float d1x = t1[0] - t0[0], d1y = t1[1] - t0[1], d2x = t2[0] - t0[0], d2y = t2[1] - t0[1];
+        const float determinant = d1x * d2y - d1y * d2x;
+        if (len == 0) { its.dpdu = V3(0.0f); its.dpdv = V3(0.0f); }
+        else if (determinant == 0) coordinateSystem(cross(side1, side2) / len, its.dpdu, its.dpdv);
+        else {
+            const float invDet = 1.0f / determinant;
+            its.dpdu = (side1 * d2y - side2 * d1y) * invDet;
+            its.dpdv = (side1 * -d2x + side2 * d1x) * invDet;
+        }
+    } else { its.uv.x = b.y; its.uv.y = b.z; its.dpdu = side1; its.dpdv = side2; }
     its.shape = s;
-    // computeShadingFrame(n, dpdu): Gram-Schmidt on dpdu = p1 - p0 (util.cpp:603-608)
+    // computeShadingFrame(n, dpdu): Gram-Schmidt on dpdu (util.cpp:603-608)
     its.sh.n = shN;
-    its.sh.s = normalize(side1 - shN * dot(shN, side1));
+    its.sh.s = normalize(its.dpdu - shN * dot(shN, its.dpdu));
     its.sh.t = cross(shN, its.sh.s);
     its.wi = its.sh.toLocal(-ray_d);
 }

@@ -343,6 +343,52 @@ class SceneBuilder:
         self.emitters.append(e)
 
     # -- convenience geometry --------------------------------------------------
+    # -- textures (src/textures; the returned handle goes into Material.tex_reflectance / tex_transmittance) --------
+    def _add_texture(self, t, uscale, vscale, uoffset, voffset, scale, keep=None):
+        t.uv_scale = (C.c_float * 2)(float(uscale), float(vscale))
+        t.uv_offset = (C.c_float * 2)(float(uoffset), float(voffset))
+        t.scale = _f3(scale)
+        t.max_anisotropy = t.max_anisotropy or 20.0
+        if not hasattr(self, "textures"):
+            self.textures, self._texture_keep = [], []
+        self.textures.append(t)
+        self._texture_keep.append(keep)
+        return len(self.textures)
+
+    def add_checkerboard(self, color0=0.4, color1=0.2, uscale=1.0, vscale=1.0, uoffset=0.0, voffset=0.0, scale=1.0):
+        """`checkerboard` texture (src/textures/checkerboard.cpp:44-69); `scale` folds an enclosing `scale` plugin."""
+        t = abi.Texture()
+        t.type, t.color0, t.color1 = abi.TEX_CHECKERBOARD, _f3(color0), _f3(color1)
+        return self._add_texture(t, uscale, vscale, uoffset, voffset, scale)
+
+    def add_gridtexture(self, color0=0.2, color1=0.4, line_width=0.01, uscale=1.0, vscale=1.0, uoffset=0.0, voffset=0.0,
+                        scale=1.0):
+        """`gridtexture` (src/textures/gridtexture.cpp:45-79)."""
+        t = abi.Texture()
+        t.type, t.color0, t.color1, t.line_width = abi.TEX_GRID, _f3(color0), _f3(color1), float(line_width)
+        return self._add_texture(t, uscale, vscale, uoffset, voffset, scale)
+
+    def add_bitmap(self, image, filter_type="ewa", wrap_mode="repeat", wrap_mode_u=None, wrap_mode_v=None,
+                   max_anisotropy=20.0, uscale=1.0, vscale=1.0, uoffset=0.0, voffset=0.0, scale=1.0):
+        """`bitmap` texture (src/textures/bitmap.cpp:179-303): `image` is (height, width) luminance or
+        (height, width, 3) linear RGB, row 0 = v 0."""
+        img = np.ascontiguousarray(np.asarray(image, dtype=np.float32))
+        if img.ndim == 2:
+            img = img[:, :, None]
+        if img.ndim != 3 or img.shape[2] not in (1, 3):
+            raise ValueError("bitmap: expected (h, w) or (h, w, 3)")
+        filt = {"nearest": abi.TEXFILTER_NEAREST, "bilinear": abi.TEXFILTER_BILINEAR, "trilinear": abi.TEXFILTER_TRILINEAR,
+                "ewa": abi.TEXFILTER_EWA}
+        wrap = {"repeat": abi.WRAP_REPEAT, "clamp": abi.WRAP_CLAMP, "mirror": abi.WRAP_MIRROR, "zero": abi.WRAP_ZERO,
+                "black": abi.WRAP_ZERO, "one": abi.WRAP_ONE, "white": abi.WRAP_ONE}
+        t = abi.Texture()
+        t.type, t.filter = abi.TEX_BITMAP, filt[filter_type]
+        t.wrap_u, t.wrap_v = wrap[wrap_mode_u or wrap_mode], wrap[wrap_mode_v or wrap_mode]
+        t.max_anisotropy = float(max_anisotropy)
+        t.height, t.width, t.channels = img.shape
+        t.texels = abi.ptr(img, C.c_float)
+        return self._add_texture(t, uscale, vscale, uoffset, voffset, scale, keep=img)
+
     def add_quad(self, p0, p1, p2, p3, material, **kw):
         """Two triangles (p0,p1,p2), (p0,p2,p3)."""
         return self.add_mesh(np.array([p0, p1, p2, p3], np.float32), np.array([[0, 1, 2], [0, 2, 3]], np.uint32),
@@ -385,5 +431,9 @@ class SceneBuilder:
         d.sampler = self.sampler
         if getattr(self, "envmap", None) is not None:
             d.envmap = C.pointer(self.envmap)
-        keep = (pos, nrm, uv, idx, shapes, mats, ems)
+        texs = None
+        if getattr(self, "textures", None):
+            texs = (abi.Texture * len(self.textures))(*self.textures)
+            d.textures, d.n_textures = texs, len(self.textures)
+        keep = (pos, nrm, uv, idx, shapes, mats, ems, texs)
         return d, keep

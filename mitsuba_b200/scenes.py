@@ -11,7 +11,7 @@ src/samplers/independent.cpp:58).
 """
 import numpy as np
 
-from .scenedesc import SceneBuilder, diffuse, look_at, roughconductor, roughdielectric
+from .scenedesc import SceneBuilder, diffuse, look_at, plastic, roughconductor, roughdielectric
 
 SEED = 1004
 
@@ -71,6 +71,73 @@ def cbox(width=512, height=512, spp=64, max_depth=8, rr_depth=5, twosided=False,
         pos = np.concatenate([np.asarray(f, np.float32) for f in block])
         idx = np.concatenate([np.array([[0, 1, 2], [0, 2, 3]], np.uint32) + 4 * k for k in range(5)])
         b.add_mesh(pos, idx, m)
+    p, i = _quad([(343, 548.75, 227), (343, 548.75, 332), (213, 548.75, 332), (213, 548.75, 227)])
+    b.add_mesh(p, i, light, area_radiance=[18.4, 15.6, 8.0])
+    return b
+
+
+def pattern_image(width=64, height=64, seed=3):
+    """A linear RGB test image with structure at every scale (stripes, blobs, noise), values in [0, 0.95]."""
+    rng = np.random.default_rng(seed)
+    y, x = np.mgrid[0:height, 0:width].astype(np.float64)
+    u, v = x / width, y / height
+    img = np.stack([0.5 + 0.45 * np.sin(2 * np.pi * (3 * u + v)), 0.5 + 0.45 * np.cos(2 * np.pi * (5 * v - 2 * u)),
+                    0.25 + 0.7 * ((np.floor(8 * u) + np.floor(8 * v)) % 2)], -1)
+    img = 0.8 * img + 0.2 * rng.random((height, width, 3))
+    return np.clip(img, 0.0, 0.95).astype(np.float32)
+
+
+def cbox_textured(width=96, height=72, spp=4, max_depth=6, rr_depth=5, tex_res=64):
+    """The Cornell box with every kind of texture this path implements (src/textures): checkerboard floor, EWA-filtered
+    bitmap on the back wall (minified at this resolution), gridtexture / nearest bitmap on the side walls, a plastic block
+    with a trilinear bitmap and a twosided block (textured roughconductor over a scaled checkerboard)."""
+    b = SceneBuilder()
+    b.set_integrator(max_depth=max_depth, rr_depth=rr_depth, sample_count=spp)
+    b.set_sensor(look_at([278, 273, -800], [278, 273, -799], [0, 1, 0]), 39.3077, width, height, near_clip=10.0, far_clip=2800.0)
+    img = pattern_image(tex_res, tex_res)
+    grey = pattern_image(tex_res // 2, tex_res, seed=5)[:, :, 1]
+
+    def textured(m, refl=0, trans=0):
+        m.tex_reflectance, m.tex_transmittance = refl, trans
+        return m
+    white = b.add_material(diffuse([0.725, 0.71, 0.68]))
+    floor = b.add_material(textured(diffuse(0.5), b.add_checkerboard([0.7, 0.7, 0.65], [0.15, 0.2, 0.3], uscale=4, vscale=4)))
+    back = b.add_material(textured(diffuse(0.5), b.add_bitmap(img, "ewa", "repeat", uscale=3, vscale=3, max_anisotropy=8.0)))
+    right = b.add_material(textured(diffuse(0.5), b.add_gridtexture([0.14, 0.45, 0.091], [0.9, 0.9, 0.2], 0.04, uscale=5, vscale=5, uoffset=0.3)))
+    left = b.add_material(textured(diffuse(0.5), b.add_bitmap(img, "nearest", "mirror", uscale=1.5, vscale=1.5, scale=[0.9, 0.3, 0.25])))
+    light = b.add_material(diffuse(0.0))
+    uv4 = np.float32([[0, 0], [1, 0], [1, 1], [0, 1]])
+    walls = [
+        ([(552.8, 0, 0), (0, 0, 0), (0, 0, 559.2), (549.6, 0, 559.2)], floor),
+        ([(556, 548.8, 0), (556, 548.8, 559.2), (0, 548.8, 559.2), (0, 548.8, 0)], white),
+        ([(549.6, 0, 559.2), (0, 0, 559.2), (0, 548.8, 559.2), (556, 548.8, 559.2)], back),
+        ([(0, 0, 559.2), (0, 0, 0), (0, 548.8, 0), (0, 548.8, 559.2)], right),
+        ([(552.8, 0, 0), (549.6, 0, 559.2), (556, 548.8, 559.2), (556, 548.8, 0)], left),
+    ]
+    for pts, m in walls:
+        p, i = _quad(pts)
+        b.add_mesh(p, i, m, texcoords=uv4)
+    short = [
+        [(130, 165, 65), (82, 165, 225), (240, 165, 272), (290, 165, 114)],
+        [(290, 0, 114), (290, 165, 114), (240, 165, 272), (240, 0, 272)],
+        [(130, 0, 65), (130, 165, 65), (290, 165, 114), (290, 0, 114)],
+        [(82, 0, 225), (82, 165, 225), (130, 165, 65), (130, 0, 65)],
+        [(240, 0, 272), (240, 165, 272), (82, 165, 225), (82, 0, 225)],
+    ]
+    tall = [
+        [(423, 330, 247), (265, 330, 296), (314, 330, 456), (472, 330, 406)],
+        [(423, 0, 247), (423, 330, 247), (472, 330, 406), (472, 0, 406)],
+        [(472, 0, 406), (472, 330, 406), (314, 330, 456), (314, 0, 456)],
+        [(314, 0, 456), (314, 330, 456), (265, 330, 296), (265, 0, 296)],
+        [(265, 0, 296), (265, 330, 296), (423, 330, 247), (423, 0, 247)],
+    ]
+    m_short = b.add_material(textured(plastic(diffuse_reflectance=0.5), b.add_bitmap(grey, "trilinear", "clamp", uscale=2, vscale=2)))
+    front = textured(roughconductor([0.2, 0.92, 1.1], [3.9, 2.45, 2.14], alpha=0.15), b.add_bitmap(img, "bilinear", "repeat", scale=0.95))
+    m_tall = b.add_twosided(front, textured(diffuse(0.5), b.add_checkerboard(0.8, 0.1, uscale=2, vscale=2, scale=[0.5, 1.0, 0.5])))
+    for block, m in ((short, m_short), (tall, m_tall)):
+        pos = np.concatenate([np.asarray(f, np.float32) for f in block])
+        idx = np.concatenate([np.array([[0, 1, 2], [0, 2, 3]], np.uint32) + 4 * k for k in range(5)])
+        b.add_mesh(pos, idx, m, texcoords=np.tile(uv4, (5, 1)))
     p, i = _quad([(343, 548.75, 227), (343, 548.75, 332), (213, 548.75, 332), (213, 548.75, 227)])
     b.add_mesh(p, i, light, area_radiance=[18.4, 15.6, 8.0])
     return b

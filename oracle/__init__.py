@@ -57,6 +57,15 @@ def lib():
         L.orc_render.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_int, C.c_int, C.POINTER(OrcStats)]
         L.orc_render2.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_int, C.c_int, C.POINTER(OrcStats), C.c_int, C.c_int]
         L.orc_li.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p]
+        L.orc_texture_create.restype = C.c_void_p
+        L.orc_texture_create.argtypes = [C.POINTER(abi.Texture)]
+        L.orc_texture_destroy.argtypes = [C.c_void_p]
+        L.orc_texture_levels.argtypes = [C.c_void_p]
+        L.orc_texture_level_size.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.orc_texture_level.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.orc_texture_eval.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_compute_partials.argtypes = [C.c_size_t, C.c_void_p, C.c_void_p]
+        L.orc_sensor_differentials.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
         L.orc_scene_bounds.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_triaccel.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
         L.orc_erf.argtypes = [C.c_float]

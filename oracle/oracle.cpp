@@ -95,7 +95,7 @@ inline MtsbRay makeRay(V3 o, V3 d, float mint, float maxt) {
 }
 
 // MIPathTracer::Li, path.cpp:121-296.  rRec.type starts as ERadiance (all bits), medium-free.
-V3 Li(const Scene &sc, const MtsbRay &primary, Rng &rng, Counters &cnt, float &alpha) {
+V3 Li(const Scene &sc, const MtsbRay &primary, Rng &rng, Counters &cnt, float &alpha, const V3 *rxd = nullptr, const V3 *ryd = nullptr) {
     const MtsbIntegrator &ig = sc.sd.integrator;
     const int maxDepth = ig.max_depth, rrDepth = ig.rr_depth;
     const bool strictNormals = ig.strict_normals != 0, hideEmitters = ig.hide_emitters != 0;
@@ -118,8 +118,16 @@ V3 Li(const Scene &sc, const MtsbRay &primary, Rng &rng, Counters &cnt, float &a
             break;
         }
         const MtsbShape &shape = sc.shapes[its.shape];
-        const int mat = shape.material;
+        const int matId = shape.material;
         V3 rd(ray.d[0], ray.d[1], ray.d[2]);
+        // its.getBSDF(ray) (records.inl:82-90): uv partials only for the camera ray, the only one that carries differentials
+        if (depth == 1 && !scattered && rxd && matId >= 0 && sc.shapeNeedsPartials[its.shape]) {
+            const UVPartials pt = computePartials(its.p, its.baseN, its.dpdu, its.dpdv, V3(primary.o[0], primary.o[1], primary.o[2]), *rxd, *ryd);
+            its.hasUVPartials = true; its.dudx = pt.dudx; its.dvdx = pt.dvdx; its.dudy = pt.dudy; its.dvdy = pt.dvdy;
+        }
+        MtsbMaterial lm[2];
+        const int mat = matId >= 0 ? resolveMaterials(sc, matId, its, lm) : -1;
+        const MtsbMaterial *mats = lm;
         if (shape.emitter >= 0 && emittedRadiance && (!hideEmitters || scattered))
             L += throughput * areaEval(sc.emitters[shape.emitter], its.sh.n, -rd);     // its.Le(-ray.d)
 
@@ -131,9 +139,9 @@ V3 Li(const Scene &sc, const MtsbRay &primary, Rng &rng, Counters &cnt, float &a
         DRec dRec;
         dRec.ref = its.p; dRec.refN = V3(0.0f);
         const bool haveMat = mat >= 0;
-        if (haveMat && !bsdf_has_back_or_transmission(sc.materials[mat])) dRec.refN = its.sh.n;   // records.inl:175-179
+        if (haveMat && !bsdf_has_back_or_transmission(mats[mat])) dRec.refN = its.sh.n;   // records.inl:175-179
         dRec.emitter = -1;
-        if (haveMat && bsdf_is_smooth(sc.materials.data(), sc.materials[mat])) {
+        if (haveMat && bsdf_is_smooth(mats, mats[mat])) {
             V3 value = sampleEmitterDirectNoVis(sc, dRec, rng.emitter2D(depth));
             if (dRec.pdf != 0) {
                 // scene.cpp:840-846
@@ -143,11 +151,11 @@ V3 Li(const Scene &sc, const MtsbRay &primary, Rng &rng, Counters &cnt, float &a
             }
             if (!isZero(value)) {
                 V3 wo = its.toLocal(dRec.d);
-                const V3 bsdfVal = bsdf_eval(sc.materials.data(), mat, its.wi, wo);
+                const V3 bsdfVal = bsdf_eval(mats, mat, its.wi, wo);
                 if (!isZero(bsdfVal) && (!strictNormals || dot(its.geoN, dRec.d) * cosTheta(wo) > 0)) {
                     const MtsbEmitter &em = sc.emitters[dRec.emitter];
                     bool onSurface = em.type != MTSB_EMITTER_POINT;
-                    float bsdfPdf = (onSurface && dRec.measure == kSolidAngle) ? bsdf_pdf(sc.materials.data(), mat, its.wi, wo) : 0;
+                    float bsdfPdf = (onSurface && dRec.measure == kSolidAngle) ? bsdf_pdf(mats, mat, its.wi, wo) : 0;
                     float weight = miWeight(dRec.pdf, bsdfPdf);
                     L += throughput * value * bsdfVal * weight;
                 }
@@ -160,11 +168,11 @@ V3 Li(const Scene &sc, const MtsbRay &primary, Rng &rng, Counters &cnt, float &a
         P2 u2 = rng.bsdf2D(depth);
         float u1 = 0.0f;
         {   // roughdielectric draws one more number inside sample() (roughdielectric.cpp:554)
-            const MtsbMaterial *m = &sc.materials[mat];
-            if ((m->flags & MTSB_MAT_TWOSIDED) && cosTheta(its.wi) < 0 && m->back >= 0) m = &sc.materials[m->back];
+            const MtsbMaterial *m = &mats[mat];
+            if ((m->flags & MTSB_MAT_TWOSIDED) && cosTheta(its.wi) < 0 && m->back >= 0) m = &mats[m->back];
             if (m->type == MTSB_BSDF_ROUGHDIELECTRIC) u1 = rng.extra1D(depth);
         }
-        bool ok = bsdf_sample(sc.materials.data(), mat, its.wi, u2, u1, bs);
+        bool ok = bsdf_sample(mats, mat, its.wi, u2, u1, bs);
         if (!ok || isZero(bs.weight)) break;
         scattered = true;
         const V3 wo = its.toWorld(bs.wo);
@@ -240,6 +248,21 @@ int orc_scene_create(const MtsbSceneDesc *d, void **out) {
     sc->sd.shapes = sc->shapes.data(); sc->sd.materials = sc->materials.data(); sc->sd.emitters = sc->emitters.data();
     sc->sd.positions = sc->positions.data(); sc->sd.normals = sc->normals.data();
     sc->sd.texcoords = sc->texcoords.empty() ? nullptr : sc->texcoords.data(); sc->sd.indices = sc->indices.data();
+    sc->textures.resize(d->n_textures);
+    for (uint32_t i = 0; i < d->n_textures; ++i) sc->textures[i].build(d->textures[i]);
+    sc->sd.textures = nullptr;
+    {   // BSDF::usesRayDifferentials(): true when one of its textures is a bitmap (bitmap.cpp:547-549; twosided.cpp:98-99)
+        auto bitmapTex = [&](const MtsbMaterial &m) {
+            return (m.tex_reflectance && sc->textures[m.tex_reflectance - 1].rec.type == MTSB_TEX_BITMAP) ||
+                   (m.tex_transmittance && sc->textures[m.tex_transmittance - 1].rec.type == MTSB_TEX_BITMAP); };
+        sc->shapeNeedsPartials.assign(d->n_shapes, false);
+        for (uint32_t s = 0; s < d->n_shapes; ++s) {
+            const int m = sc->shapes[s].material;
+            if (m < 0) continue;
+            const MtsbMaterial &mm = sc->materials[m];
+            sc->shapeNeedsPartials[s] = bitmapTex(mm) || ((mm.flags & MTSB_MAT_TWOSIDED) && mm.back >= 0 && bitmapTex(sc->materials[mm.back]));
+        }
+    }
     sc->triShape.resize(d->n_tris);
     sc->areaPdf.resize(d->n_shapes); sc->invArea.assign(d->n_shapes, 0.0f);
     for (uint32_t s = 0; s < d->n_shapes; ++s) {
@@ -479,8 +502,9 @@ int orc_render2(void *h, int spp, uint64_t seed, int nthreads, int max_blocks, O
                         P2 u = rng.pixel2D();
                         P2 samplePos{(float) (ox + x) + u.x, (float) (oy + y) + u.y};
                         MtsbRay ray; sensorRay(*sc, samplePos, ray);
+                        V3 rxd, ryd; sensorRayDifferentials(*sc, samplePos, rxd, ryd);
                         float alpha;
-                        V3 L = Li(*sc, ray, rng, cnt, alpha);
+                        V3 L = Li(*sc, ray, rng, cnt, alpha, &rxd, &ryd);
                         ++cnt.samples;
                         float v[5] = {L.x, L.y, L.z, alpha, 1.0f};
                         if (!blockPut(f, buf.data(), ox, oy, bw, bh, samplePos, v)) bad++;
@@ -523,7 +547,8 @@ int orc_li(void *h, const float *samplePos, size_t n, uint64_t seed, float *rgba
     for (size_t i = 0; i < n; ++i) {
         Rng rng(seed + i);
         MtsbRay ray; sensorRay(*sc, P2{samplePos[2 * i], samplePos[2 * i + 1]}, ray);
-        float alpha; V3 L = Li(*sc, ray, rng, cnt, alpha);
+        V3 rxd, ryd; sensorRayDifferentials(*sc, P2{samplePos[2 * i], samplePos[2 * i + 1]}, rxd, ryd);
+        float alpha; V3 L = Li(*sc, ray, rng, cnt, alpha, &rxd, &ryd);
         rgba[4 * i] = L.x; rgba[4 * i + 1] = L.y; rgba[4 * i + 2] = L.z; rgba[4 * i + 3] = alpha;
     }
     return MTSB_OK;
@@ -648,6 +673,40 @@ int orc_envmap_query(void *h, int kind, const float *in, size_t n, float *out) {
         } else o[6] = sc->envmap.pdfDirection(V3(q[0], q[1], q[2]));
     }
     return MTSB_OK;
+}
+
+// ---- textures (orc_texture.h) ----------------------------------------------------------------------------------
+void *orc_texture_create(const MtsbTexture *t) { orc::Texture *x = new orc::Texture(); x->build(*t); return x; }
+void orc_texture_destroy(void *h) { delete static_cast<orc::Texture *>(h); }
+int orc_texture_levels(void *h) { return static_cast<orc::Texture *>(h)->mip.levels(); }
+void orc_texture_level_size(void *h, int level, int *wh) { const orc::MipMap &m = static_cast<orc::Texture *>(h)->mip; wh[0] = m.w[level]; wh[1] = m.h[level]; }
+// level texels as w*h*3 floats (the half-precision values widened)
+void orc_texture_level(void *h, int level, float *out) { const orc::MipMap &m = static_cast<orc::Texture *>(h)->mip; std::copy(m.pyr[level].begin(), m.pyr[level].end(), out); }
+// Texture2D::eval(its, filter): uv = hit uv (2 per query); partials = dudx, dvdx, dudy, dvdy per query or NULL (unfiltered)
+void orc_texture_eval(void *h, size_t n, const float *uv, const float *partials, float *rgb) {
+    const orc::Texture *t = static_cast<orc::Texture *>(h);
+    for (size_t i = 0; i < n; ++i) {
+        orc::UVPartials pt;
+        if (partials) { pt.has = true; pt.dudx = partials[4 * i]; pt.dvdx = partials[4 * i + 1]; pt.dudy = partials[4 * i + 2]; pt.dvdy = partials[4 * i + 3]; }
+        V3 v = t->eval(P2{uv[2 * i], uv[2 * i + 1]}, pt);
+        rgb[3 * i] = v.x; rgb[3 * i + 1] = v.y; rgb[3 * i + 2] = v.z;
+    }
+}
+// in: p(3) n(3) dpdu(3) dpdv(3) o(3) rxd(3) ryd(3) per query; out: dudx dvdx dudy dvdy
+void orc_compute_partials(size_t n, const float *in, float *out) {
+    for (size_t i = 0; i < n; ++i) {
+        const float *q = in + 21 * i;
+        auto v = [&](int k) { return V3(q[3 * k], q[3 * k + 1], q[3 * k + 2]); };
+        const orc::UVPartials r = orc::computePartials(v(0), v(1), v(2), v(3), v(4), v(5), v(6));
+        out[4 * i] = r.dudx; out[4 * i + 1] = r.dvdx; out[4 * i + 2] = r.dudy; out[4 * i + 3] = r.dvdy;
+    }
+}
+// sensor ray differential directions (rxd, ryd) for sample positions of a scene
+void orc_sensor_differentials(void *h, size_t n, const float *pos, float *out6) {
+    for (size_t i = 0; i < n; ++i) {
+        V3 rx, ry; sensorRayDifferentials(*S(h), P2{pos[2 * i], pos[2 * i + 1]}, rx, ry);
+        float *o = out6 + 6 * i; o[0] = rx.x; o[1] = rx.y; o[2] = rx.z; o[3] = ry.x; o[4] = ry.y; o[5] = ry.z;
+    }
 }
 
 }  // extern "C"

@@ -23,6 +23,9 @@ struct Its {
     P2 uv;
     V3 wi;            // local
     uint32_t shape, prim;   // prim = global primitive index
+    V3 dpdu, dpdv;          // skdtree.h:373-380
+    V3 baseN;               // baseFrame.n (the shading normal before any BSDF-side perturbation)
+    bool hasUVPartials; float dudx, dvdx, dudy, dvdy;      // shape.h:175-184
     V3 toWorld(V3 v) const { return sh.toWorld(v); }
     V3 toLocal(V3 v) const { return sh.toLocal(v); }
 };
@@ -112,6 +115,10 @@ inline float halfToFloat(uint16_t h) {            // half.cpp:50-75 (the table t
     x.i = ((uint32_t) s << 31) | ((uint32_t) e << 23) | (uint32_t) m;
     return x.f;
 }
+}  // namespace orc
+#include "orc_texture.h"
+namespace orc {
+
 struct Envmap {
     int w = 0, h = 0;
     std::vector<uint16_t> texels;             // 3 per texel
@@ -239,6 +246,8 @@ struct Scene {
     std::vector<float> invArea;                // per shape
     int envEmitter;
     Envmap envmap;                             // envmap.cpp (when the environment emitter is an image)
+    std::vector<Texture> textures;             // src/textures (bitmap, checkerboard, gridtexture; scale folded in)
+    std::vector<bool> shapeNeedsPartials;      // the shape's BSDF usesRayDifferentials() (a bitmap texture: bitmap.cpp:547-549)
     V3 bsphereC; float bsphereR;               // constant.cpp:67-71
     // sensor (closed form of perspective.cpp:127-150)
     float nearX, nearY;                        // near*tan(xfov/2), same / aspect
@@ -276,7 +285,7 @@ inline void fillIntersection(const Scene &sc, const MtsbRay &ray, const MtsbHit 
     V3 faceNormal = cross(side1, side2);
     float len = length(faceNormal);
     if (!isZero(faceNormal)) faceNormal = faceNormal / len;
-    V3 dpdu = side1;
+    V3 dpdu = side1, dpdv = side2;
     V3 shN;
     if (sh.has_normals) {
         V3 n0 = sc.nrm(ix[0]), n1 = sc.nrm(ix[1]), n2 = sc.nrm(ix[2]);
@@ -287,8 +296,25 @@ inline void fillIntersection(const Scene &sc, const MtsbRay &ray, const MtsbHit 
     if (sh.has_texcoords && !sc.texcoords.empty()) {
         P2 t0 = sc.tex(ix[0]), t1 = sc.tex(ix[1]), t2 = sc.tex(ix[2]);
         its.uv = P2{t0.x * b.x + t1.x * b.y + t2.x * b.z, t0.y * b.x + t1.y * b.y + t2.y * b.z};
+        // TriMesh::computeUVTangents (trimesh.cpp:683-735); this fork computes them for every mesh with texture
+        // coordinates (TriMesh::configure, trimesh.cpp:383-385) and skdtree.h:373-376 then reads dpdu / dpdv from them
+        V3 dP1 = p1 - p0, dP2 = p2 - p0;
+        P2 dUV1{t1.x - t0.x, t1.y - t0.y}, dUV2{t2.x - t0.x, t2.y - t0.y};
+        V3 n = cross(dP1, dP2);
+        float nlen = length(n);
+        if (nlen == 0) { dpdu = V3(0.0f); dpdv = V3(0.0f); }
+        else {
+            float determinant = dUV1.x * dUV2.y - dUV1.y * dUV2.x;
+            if (determinant == 0) coordinateSystem(n / nlen, dpdu, dpdv);
+            else {
+                float invDet = 1.0f / determinant;
+                dpdu = (dP1 * dUV2.y - dP2 * dUV1.y) * invDet;
+                dpdv = (dP1 * -dUV2.x + dP2 * dUV1.x) * invDet;
+            }
+        }
     } else its.uv = P2{b.y, b.z};
     its.shape = s; its.prim = hit.prim;
+    its.dpdu = dpdu; its.dpdv = dpdv; its.baseN = shN; its.hasUVPartials = false;
     its.sh = shadingFrame(shN, dpdu);
     its.wi = its.toLocal(-V3(ray.d[0], ray.d[1], ray.d[2]));
 }
@@ -457,12 +483,43 @@ inline void sensorRay(const Scene &sc, P2 samplePos, MtsbRay &ray) {
     ray.d[0] = wd.x; ray.d[1] = wd.y; ray.d[2] = wd.z;
 }
 
+// offset-ray directions of the camera ray (perspective.cpp:160-163, 310-314) after RayDifferential::scaleDifferential
+// (ray.h:174-179) with diffScaleFactor = 1/sqrt(sampleCount) (integrator.cpp:200-201, 237)
+inline void sensorRayDifferentials(const Scene &sc, P2 samplePos, V3 &rxd, V3 &ryd) {
+    const MtsbSensor &se = sc.sd.sensor;
+    float a = (samplePos.x + (float) se.crop_x) / (float) se.film_width;
+    float b = (samplePos.y + (float) se.crop_y) / (float) se.film_height;
+    V3 nearP((1.0f - 2.0f * a) * sc.nearX, (1.0f - 2.0f * b) * sc.nearY, se.near_clip);
+    V3 dx(-2.0f * sc.nearX / (float) se.film_width, 0.0f, 0.0f), dy(0.0f, -2.0f * sc.nearY / (float) se.film_height, 0.0f);
+    V3 d = xformVec(se.to_world, normalize(nearP));
+    V3 rx = xformVec(se.to_world, normalize(nearP + dx)), ry = xformVec(se.to_world, normalize(nearP + dy));
+    float amount = 1.0f / std::sqrt((float) std::max(1, sc.sd.integrator.sample_count));
+    rxd = d + (rx - d) * amount;
+    ryd = d + (ry - d) * amount;
+}
+
+// The material table a hit shades with: the shape's record (and the back side of a twosided adapter) with every textured
+// spectrum replaced by the texture's value at the hit (e.g. diffuse.cpp:118: m_reflectance->eval(bRec.its)).
+// Returns the index of the front record inside `lm`.
+inline int resolveMaterials(const Scene &sc, int mat, const Its &its, MtsbMaterial lm[2]) {
+    UVPartials pt;
+    if (its.hasUVPartials) { pt.has = true; pt.dudx = its.dudx; pt.dvdx = its.dvdx; pt.dudy = its.dudy; pt.dvdy = its.dvdy; }
+    lm[0] = sc.materials[mat];
+    int n = 1;
+    if ((lm[0].flags & MTSB_MAT_TWOSIDED) && lm[0].back >= 0) { lm[1] = sc.materials[lm[0].back]; lm[0].back = 1; n = 2; }
+    for (int i = 0; i < n; ++i) {
+        if (lm[i].tex_reflectance) { V3 v = sc.textures[lm[i].tex_reflectance - 1].eval(its.uv, pt); lm[i].reflectance[0] = v.x; lm[i].reflectance[1] = v.y; lm[i].reflectance[2] = v.z; }
+        if (lm[i].tex_transmittance) { V3 v = sc.textures[lm[i].tex_transmittance - 1].eval(its.uv, pt); lm[i].transmittance[0] = v.x; lm[i].transmittance[1] = v.y; lm[i].transmittance[2] = v.z; }
+    }
+    return 0;
+}
+
 // ---- film: ReconstructionFilter::configure rfilter.cpp:36-55; GaussianFilter::eval gaussian.cpp:50-55;
 //      BoxFilter box.cpp:36-50; ImageBlock::put imageblock.h:143-206 --------------------------------
 inline float rfilterEval(const MtsbSensor &se, float x) {
     if (se.rfilter == MTSB_RFILTER_GAUSSIAN) {
         float alpha = -1.0f / (2.0f * se.rfilter_stddev * se.rfilter_stddev);
-        return std::max(0.0f, std::exp(alpha * x * x) - std::exp(alpha * se.rfilter_radius * se.rfilter_radius));
+        return std::max(0.0f, (float) std::exp((double) (alpha * x * x)) - (float) std::exp((double) (alpha * se.rfilter_radius * se.rfilter_radius)));   // math::fastexp (math.h:175-199)
     }
     return std::fabs(x) <= se.rfilter_radius ? 1.0f : 0.0f;
 }

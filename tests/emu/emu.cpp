@@ -11,6 +11,7 @@
 #include "../../mitsuba_b200/csrc/rng.h"
 #include "../../mitsuba_b200/csrc/qmc.h"
 #include "../../mitsuba_b200/csrc/qmc_host.h"
+#include "../../mitsuba_b200/csrc/texture_host.h"
 #include <vector>
 #include <algorithm>
 #include <numeric>
@@ -339,3 +340,57 @@ extern "C" void emu_trace_profile(void *h, const RayIn *rays, size_t n, int mode
         lens[i] = len < max_len ? len : max_len;
     }
 }
+
+// ---- textures: csrc/texture.h evaluated on the host, pyramid from csrc/texture_host.h ---------------------------------
+struct EmuTexture { TextureView tv; std::vector<HalfTexel> texels; float lut[MTSB_MIPMAP_LUT_SIZE]; };
+extern "C" void *emu_texture_create(const MtsbTexture *t) {
+    EmuTexture *e = new EmuTexture();
+    TextureView &tv = e->tv;
+    std::memset(&tv, 0, sizeof(tv));
+    tv.type = t->type; tv.filter = t->filter; tv.wrap_u = t->wrap_u; tv.wrap_v = t->wrap_v;
+    for (int k = 0; k < 2; ++k) { tv.uv_scale[k] = t->uv_scale[k]; tv.uv_offset[k] = t->uv_offset[k]; }
+    for (int k = 0; k < 3; ++k) { tv.color0[k] = t->color0[k]; tv.color1[k] = t->color1[k]; tv.scale[k] = t->scale[k]; }
+    tv.line_width = t->line_width;
+    tv.max_anisotropy = t->filter == MTSB_TEXFILTER_EWA ? t->max_anisotropy : 1.0f;
+    for (int i = 0; i < MTSB_MIPMAP_LUT_SIZE; ++i) { const float r2 = (float) i / (float) (MTSB_MIPMAP_LUT_SIZE - 1); e->lut[i] = (float) std::exp((double) (-2.0f * r2)) - (float) std::exp((double) -2.0f); }   // math::fastexp, math.h:175-199
+    tv.weight_lut = e->lut;
+    if (t->type == MTSB_TEX_BITMAP) build_texture_levels(*t, tv, e->texels);
+    tv.texels = e->texels.data();
+    return e;
+}
+extern "C" void emu_texture_destroy(void *h) { delete static_cast<EmuTexture *>(h); }
+extern "C" int emu_texture_levels(void *h) { return static_cast<EmuTexture *>(h)->tv.levels; }
+extern "C" void emu_texture_level_size(void *h, int level, int *wh) { const TextureView &tv = static_cast<EmuTexture *>(h)->tv; wh[0] = tv.lw[level]; wh[1] = tv.lh[level]; }
+extern "C" void emu_texture_level(void *h, int level, float *out) {
+    const TextureView &tv = static_cast<EmuTexture *>(h)->tv;
+    for (int y = 0; y < tv.lh[level]; ++y)
+        for (int x = 0; x < tv.lw[level]; ++x) {
+            const V3 v = tex_texel(tv, level, x, y);
+            float *o = out + 3 * ((size_t) y * tv.lw[level] + x); o[0] = v.x; o[1] = v.y; o[2] = v.z;
+        }
+}
+extern "C" void emu_texture_eval(void *h, size_t n, const float *uv, const float *partials, float *rgb) {
+    const TextureView &tv = static_cast<EmuTexture *>(h)->tv;
+    for (size_t i = 0; i < n; ++i) {
+        UVPartials pt; pt.has = partials != nullptr; pt.dudx = pt.dvdx = pt.dudy = pt.dvdy = 0.0f;
+        if (partials) { pt.dudx = partials[4 * i]; pt.dvdx = partials[4 * i + 1]; pt.dudy = partials[4 * i + 2]; pt.dvdy = partials[4 * i + 3]; }
+        P2 q; q.x = uv[2 * i]; q.y = uv[2 * i + 1];
+        const V3 v = texture_eval(tv, q, pt);
+        rgb[3 * i] = v.x; rgb[3 * i + 1] = v.y; rgb[3 * i + 2] = v.z;
+    }
+}
+extern "C" void emu_compute_partials(size_t n, const float *in, float *out) {
+    for (size_t i = 0; i < n; ++i) {
+        const float *q = in + 21 * i;
+        auto v = [&](int k) { return V3(q[3 * k], q[3 * k + 1], q[3 * k + 2]); };
+        const UVPartials r = compute_partials(v(0), v(1), v(2), v(3), v(4), v(5), v(6));
+        out[4 * i] = r.dudx; out[4 * i + 1] = r.dvdx; out[4 * i + 2] = r.dudy; out[4 * i + 3] = r.dvdy;
+    }
+}
+extern "C" void emu_sensor_differentials(const MtsbSensor *se, float near_x, float near_y, int sample_count, size_t n, const float *pos, float *out6) {
+    for (size_t i = 0; i < n; ++i) {
+        V3 rx, ry; sensor_ray_differentials(*se, near_x, near_y, pos[2 * i], pos[2 * i + 1], sample_count, rx, ry);
+        float *o = out6 + 6 * i; o[0] = rx.x; o[1] = rx.y; o[2] = rx.z; o[3] = ry.x; o[4] = ry.y; o[5] = ry.z;
+    }
+}
+extern "C" uint32_t emu_float_to_half(float f) { return float_to_half_bits(f); }

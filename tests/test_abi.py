@@ -31,6 +31,7 @@ def test_library_exports_every_symbol():
 
 def test_struct_sizes_match_header():
     assert C.sizeof(abi.Material) == 96 and C.sizeof(abi.Shape) == 32 and C.sizeof(abi.Emitter) == 48
+    assert C.sizeof(abi.Texture) == 96 and abi.Material.tex_reflectance.offset == 84
     assert abi.RAY_DTYPE.itemsize == 32 and abi.HIT_DTYPE.itemsize == 16
 
 

@@ -312,3 +312,31 @@ def test_envmap_halton_same_sequence(gpu_lib, oracle_mod):
 def test_envmap_independent_streams(gpu_lib, oracle_mod):
     b = _sky_scene(width=64, height=36, spp=32)
     check_render(gpu_lib, oracle_mod, b, 32, 256, "mixed + envmap")
+
+
+# ---- textures: checkerboard / gridtexture / bitmap (nearest, bilinear, trilinear, EWA) -------------
+def test_same_stream_textured_cbox(gpu_lib, oracle_mod):
+    """Every texture kind on every material slot that takes one; the back wall's bitmap is minified (EWA over several
+    MIP levels on camera-ray hits, level-0 bilinear on every later hit), the left wall's is magnified."""
+    b = scenes.cbox_textured(width=96, height=72, spp=4, max_depth=6)
+    check_same_stream(gpu_lib, oracle_mod, b, 4, "textured cbox")
+
+
+def test_textured_cbox_halton_same_sequence_and_passes(gpu_lib, oracle_mod):
+    b = scenes.cbox_textured(width=80, height=60, spp=6, max_depth=5, tex_res=128)
+    b.set_sampler("halton", sample_count=6)
+    check_same_sequence(gpu_lib, oracle_mod, b, 6, "textured cbox halton", spp_per_pass=4)
+
+
+def test_textured_cbox_independent_streams(gpu_lib, oracle_mod):
+    b = scenes.cbox_textured(width=64, height=48, spp=64, max_depth=6)
+    check_render(gpu_lib, oracle_mod, b, 64, 256, "textured cbox")
+
+
+def test_texture_filtering_depends_on_the_sample_count(gpu_lib, oracle_mod):
+    """The camera ray's differentials are scaled by 1/sqrt(sampleCount) (integrator.cpp:200-201): the same texture seen
+    with a different sampler sample count is filtered differently, on the GPU exactly as in the oracle."""
+    for count in (1, 64):
+        b = scenes.cbox_textured(width=64, height=48, spp=2, max_depth=2, tex_res=256)
+        b.set_integrator(max_depth=2, rr_depth=5, sample_count=count)
+        check_same_stream(gpu_lib, oracle_mod, b, 2, "textured cbox sampleCount=%d" % count)
