@@ -36,6 +36,8 @@ WORKLOADS = {
     "cfg1_1m": ("scene_1m", dict(width=1920, height=1080, spp=256, max_depth=10), "1M", 720, 708),
     "cfg0_cbox": ("cbox", dict(width=512, height=512, spp=64, max_depth=8), "32", 400, 388),
     "cfg2_10m": ("scene_10m", dict(width=1920, height=1080, spp=512, max_depth=10), "10M", 880, 868),
+    # BASELINE configs[4]: the 10M scene at 4K / 1024 spp, meant for 2/4/8 GPUs (tile partition + one film reduce)
+    "cfg4_4k": ("scene_10m", dict(width=3840, height=2160, spp=1024, max_depth=10), "10M", 880, 868),
 }
 SHADE_BYTES = 276      # per shade event
 

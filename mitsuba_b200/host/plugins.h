@@ -10,6 +10,7 @@
 //   ConfigurableObject (core/cobject.h)         ConfigurableObject
 //   PluginManager::createObject (plugin.cpp)    createObject()
 //   BSDF: diffuse/roughconductor/roughdielectric/twosided   Bsdf
+//   Texture: bitmap/checkerboard/gridtexture/scale          Texture
 //   Emitter: area/point/constant                Emitter
 //   Shape: obj/ply/rectangle/cube/(trimesh)     Shape (always holds triangle meshes)
 //   Sensor perspective + Film hdrfilm + rfilter + Sampler independent
@@ -43,6 +44,39 @@ protected:
 };
 typedef std::shared_ptr<ConfigurableObject> ObjRef;
 
+// ---- textures ----------------------------------------------------------------------------------
+struct Image {              // linear RGB, row 0 on top
+    int width = 0, height = 0;
+    std::vector<float> rgb;
+    bool luminance = false; // the file held one channel (replicated into r, g, b)
+};
+// imageio.cpp: PFM, Radiance RGBE, PNG (8/16 bit, sRGB -> linear as Bitmap::convert does).  `what` names the consumer in error texts.
+Image readImage(const std::string &path, const char *what = "Environment map");
+
+// src/textures/{bitmap,checkerboard,gridtexture,scale}.cpp + Texture2D (src/librender/texture.cpp:81-96)
+class Texture : public ConfigurableObject {
+public:
+    Texture(const Properties &p, const std::string &baseDir);
+    EClass getClass() const override { return CTexture; }
+    void addChild(const std::string &name, const ObjRef &child) override;   // scale.cpp:84-89
+    void configure() override;                                                // scale.cpp:79-82
+    bool isConstant() const;                        // a `scale` around a constant `value` (scale.cpp:55-57, 112-114)
+    Vec3 constantValue() const;                     // its value, scales applied
+    Vec3 getMaximum() const;                        // component-wise, scales applied (ensureEnergyConservation's input)
+    Vec3 getAverage() const;
+    // the leaf record with the product of the enclosing scales (and `extra`) folded into MtsbTexture::scale;
+    // `texels` points into this object
+    MtsbTexture record(const Vec3 &extra) const;
+private:
+    enum Kind { KBitmap, KChecker, KGrid, KScale } m_kind;
+    MtsbTexture m_rec;
+    Image m_image; std::vector<float> m_lum;        // bitmap payload (m_lum: one channel per texel for luminance images)
+    Vec3 m_scale{1, 1, 1};                          // KScale
+    bool m_hasValue = false; Vec3 m_value{0, 0, 0}; // KScale with a constant `value`
+    Vec3 m_max{0, 0, 0}, m_avg{0, 0, 0};            // leaf statistics
+    std::shared_ptr<Texture> m_nested;
+};
+
 // ---- BSDFs -------------------------------------------------------------------------------------
 class Bsdf : public ConfigurableObject {
 public:
@@ -52,21 +86,20 @@ public:
     void configure() override;
     bool hasTransmission() const { return m_rec.type == MTSB_BSDF_ROUGHDIELECTRIC || m_rec.type == MTSB_BSDF_DIELECTRIC; }
     bool isTwosided() const { return m_twosided; }
-    // appends this BSDF's record(s) to `out` (twosided with two children: back first), returns its index
-    int flatten(std::vector<MtsbMaterial> &out) const;
+    // appends this BSDF's record(s) to `out` (twosided with two children: back first), returns its index;
+    // textures the records refer to are appended to `tex`
+    int flatten(std::vector<MtsbMaterial> &out, std::vector<MtsbTexture> &tex) const;
 private:
+    MtsbMaterial record(std::vector<MtsbTexture> &tex) const;
     MtsbMaterial m_rec;
+    // textures given as children: slot 0 replaces MtsbMaterial::reflectance, slot 1 ::transmittance
+    std::shared_ptr<Texture> m_tex[2];
+    Vec3 m_texScale[2] = {Vec3{1, 1, 1}, Vec3{1, 1, 1}};      // ensureEnergyConservation's factor
     bool m_twosided = false;
     std::vector<std::shared_ptr<Bsdf>> m_nested;
 };
 
 // ---- emitters ----------------------------------------------------------------------------------
-struct Image {              // linear RGB, row 0 on top
-    int width = 0, height = 0;
-    std::vector<float> rgb;
-};
-Image readImage(const std::string &path);     // imageio.cpp: PFM, Radiance RGBE
-
 class Emitter : public ConfigurableObject {
 public:
     explicit Emitter(const Properties &p, const std::string &baseDir = std::string());
@@ -169,6 +202,7 @@ struct FlatScene {          // owns the buffers MtsbSceneDesc points into
     std::vector<MtsbShape> shapes;
     std::vector<MtsbMaterial> materials;
     std::vector<MtsbEmitter> emitters;
+    std::vector<MtsbTexture> textures;          // `texels` point into the Texture objects of the Scene
     std::vector<float> positions, normals, texcoords;
     std::vector<uint32_t> indices;
     MtsbEnvmap envmap;          // valid when an emitter has type MTSB_EMITTER_ENVMAP (points into the Emitter object)

@@ -19,9 +19,7 @@ ObjRef createObject(EClass expected, const Properties &props, const std::string 
         case CShape: return std::make_shared<Shape>(props, baseDir);
         case CBsdf: return std::make_shared<Bsdf>(props);
         case CEmitter: return std::make_shared<Emitter>(props, baseDir);
-        case CTexture:
-            error("Textures are not part of the B200 path: give constant <rgb>/<spectrum>/<float> values (plugin \"" +
-                  props.getPluginName() + "\").");
+        case CTexture: return std::make_shared<Texture>(props, baseDir);
     }
     error("createObject: unknown class");
 }
@@ -51,6 +49,7 @@ void Scene::addChild(const std::string &name, const ObjRef &child) {
             for (auto &s : inc->shapes) shapes.push_back(s);
             break;
         }
+        case CTexture:          // a named top-level texture that BSDFs <ref>erence
         case CBsdf: break;      // a named top-level BSDF that shapes <ref>erence; the scene itself ignores it (scene.cpp:612)
         default: ConfigurableObject::addChild(name, child);
     }
@@ -79,7 +78,7 @@ void Scene::flatten(FlatScene &f) const {
     for (auto &s : shapes) {
         const Bsdf *b = s->bsdf().get();
         auto it = matIndex.find(b);
-        int mat = it != matIndex.end() ? it->second : (matIndex[b] = b->flatten(f.materials));
+        int mat = it != matIndex.end() ? it->second : (matIndex[b] = b->flatten(f.materials, f.textures));
         for (auto &m : s->meshes()) {
             MtsbShape rec;
             rec.first_vertex = (uint32_t) (f.positions.size() / 3);
@@ -132,6 +131,8 @@ void Scene::flatten(FlatScene &f) const {
     d.integrator.sample_count = sensor->sampler->sampleCount;
     d.envmap = nullptr;
     for (auto &e : emitters) if (e->isEnvmap()) { f.envmap = e->envmapRecord(); d.envmap = &f.envmap; }
+    d.textures = f.textures.empty() ? nullptr : f.textures.data();
+    d.n_textures = (uint32_t) f.textures.size();
     d.sampler.type = sensor->sampler->kind; d.sampler.dimension = sensor->sampler->dimension; d.sampler.scramble = sensor->sampler->scramble; d.sampler._pad = 0;
     f.seed = sensor->sampler->seed;
 }

@@ -61,3 +61,40 @@ def test_command_line_tool_writes_a_pfm(tmp_path):
     # errors come back on stderr with a non-zero status, like the reference binary
     r = subprocess.run([hostlib.CLI_PATH, "-Dspp=0", CBOX], capture_output=True, text=True, timeout=60)
     assert r.returncode != 0 and "sampleCount" in r.stderr
+
+
+def test_textured_xml_scene_matches_oracle_same_stream(gpu_lib, oracle_mod, tmp_path):
+    """Texture plugins through the loader (bitmap EWA / nearest, checkerboard, gridtexture, scale; PFM input): the GPU
+    render of the flattened scene equals the oracle's under the same counter-based streams."""
+    from tests.test_host_textures import write_pfm
+    write_pfm(tmp_path / "t.pfm", scenes.pattern_image(64, 64))
+    xml = """<scene version="0.5.0"><integrator type="path"><integer name="maxDepth" value="5"/></integrator>
+<sensor type="perspective"><transform name="toWorld"><lookat origin="0 1.2 5" target="0 0.4 0" up="0 1 0"/></transform><float name="fov" value="42"/>
+  <sampler type="independent"><integer name="sampleCount" value="4"/></sampler>
+  <film type="hdrfilm"><integer name="width" value="64"/><integer name="height" value="48"/></film></sensor>
+<shape type="rectangle"><transform name="toWorld"><rotate x="1" angle="-90"/><scale value="3"/></transform>
+  <bsdf type="diffuse"><texture type="bitmap" name="reflectance"><string name="filename" value="%(f)s"/><float name="uvscale" value="8"/></texture></bsdf></shape>
+<shape type="rectangle"><transform name="toWorld"><scale value="3"/><translate z="-3" y="3"/></transform>
+  <bsdf type="diffuse"><texture type="checkerboard" name="reflectance"><float name="uvscale" value="6"/></texture></bsdf></shape>
+<shape type="cube"><transform name="toWorld"><scale value=".6"/><rotate y="1" angle="30"/><translate x="-1" y=".6"/></transform>
+  <bsdf type="plastic"><texture type="scale" name="diffuseReflectance"><rgb name="scale" value=".9 .5 .4"/>
+    <texture type="bitmap"><string name="filename" value="%(f)s"/><string name="filterType" value="nearest"/><string name="wrapMode" value="mirror"/></texture></texture></bsdf></shape>
+<shape type="cube"><transform name="toWorld"><scale value=".5"/><rotate y="1" angle="-20"/><translate x="1.1" y=".5"/></transform>
+  <bsdf type="twosided"><bsdf type="diffuse"><texture type="gridtexture" name="reflectance"><float name="uvscale" value="3"/><float name="lineWidth" value=".08"/></texture></bsdf></bsdf></shape>
+<shape type="rectangle"><transform name="toWorld"><rotate x="1" angle="90"/><translate y="2.9"/></transform><emitter type="area"><rgb name="radiance" value="12 11 9"/></emitter></shape>
+</scene>""" % dict(f=tmp_path / "t.pfm")
+    hs = hostlib.HostScene.load_string(xml, "textured.xml")
+    assert hs.desc.n_textures == 4
+    sc = gpu_lib.Scene(hs.desc_pair())
+    st = sc.render(spp=4, seed=3)
+    fg = sc.film_download().astype(np.float64)
+    orc = oracle_mod.Oracle(hs.desc_pair())
+    ost = orc.render(spp=4, seed=3, counter_rng=True)
+    fo = orc.film_download().astype(np.float64)
+    assert st.samples == ost.samples and st.bad_samples == 0
+    assert abs(int(st.closest_rays) - int(ost.closest_rays)) <= 2e-4 * ost.closest_rays
+    assert fo[..., :3].max() > 0.05
+    denom = np.maximum(np.abs(fo), 1e-3)
+    bad = np.abs(fg - fo) / denom > 1e-3
+    assert bad.any(axis=-1).mean() < 2e-3
+    sc.close()
