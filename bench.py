@@ -3,12 +3,14 @@
 
 Own arm (default):  python bench.py [--gpus N] [--steps K] [--warmup W]
   One "step" = one full render of the workload (every pixel, every sample) through mtsb_render.
-  N = 1: configs[1] -- synthetic 1M-triangle scene, GGX roughconductor + diffuse, 1920x1080,
-         256 spp, maxDepth 10 (the configuration the metric is quoted on).
-  N > 1: launched by torchrun, one rank per GPU.  The image is partitioned by interleaved
-         32x32 tiles (tile % N == rank) and every rank renders N x 256 spp of its tiles, so the
-         per-GPU work is fixed ("weak" scaling); one NCCL reduce of the film to rank 0 ends a step.
-  value   = path samples of all ranks / device time (CUDA events inside mtsb_render, max over ranks)
+  Workload (every N): BASELINE.json configs[2] -- the synthetic 10M-triangle flattened-instance scene, mixed
+         diffuse / roughdielectric / roughconductor, constant environment + 4 area lights, 1920x1080, 512 spp,
+         maxDepth 10: the configuration north_star states the >=100x target on.  (--workload cfg1_1m / cfg0_cbox /
+         cfg4_4k select configs[1] / [0] / [4].)
+  N > 1: launched by torchrun, one rank per GPU.  ONE frame of the same size is partitioned by interleaved
+         32x32 tiles (tile % N == rank): every rank renders all 512 spp of its tiles ("strong" scaling, the default)
+         and one NCCL reduce of the film to rank 0 ends a step.  --scaling weak renders N x 512 spp instead.
+  value   = path samples of all ranks / device time (CUDA events inside mtsb_render + the reduce, max over ranks)
   e2e     = same metric through the C ABI with HOST buffers: scene description in host memory ->
             mtsb_scene_create (H2D + BVH build) -> mtsb_render -> mtsb_film_develop (D2H), every step.
 Reference arm:      python bench.py --impl reference ...
@@ -48,7 +50,8 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="cfg1_1m", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="cfg2_10m", choices=sorted(WORKLOADS))
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"], help="N>1: one frame split over the GPUs (strong) or N x spp (weak)")
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (testing only; the JSON line says so)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
@@ -115,6 +118,8 @@ class CpuReference:
     def __init__(self, builder, threads=0):
         import oracle                                     # checker / CPU baseline only (never on the product path)
         oracle.build(ref=os.path.isdir("/root/reference/include/mitsuba"))
+        # the TIMED build: the reference's release flags at the host's -march (oracle/Makefile FASTFLAGS); parity uses the strict one
+        self.flags = oracle.use_timed_build()
         self.use_ref = oracle.ref_available()
         t0 = time.time()
         self.orc = oracle.Oracle(builder, use_ref_kdtree=self.use_ref)
@@ -139,6 +144,25 @@ class CpuReference:
                      else "CPU restatement (oracle/) with its own BVH"))
         return st.samples / st.seconds, int(st.threads), sample, st
 
+    def record(self, value, cores, sample):
+        return {"value": value, "unit": UNIT, "cores": cores, "kind": self.kind, "sample": sample,
+                "detail": "kd-tree build/traversal + TriAccel are the reference's own code (compiled from /root/reference); "
+                          "Li, BSDFs, emitters, film are the CPU restatement (oracle/): the full mitsuba binary is unbuildable here",
+                "flags": self.flags, "kd_build_s": round(self.build_s, 2)}
+
+
+L2_NOTE = "GPU arm: L2 flushed between steps (160 MB write); per-step working set >> L2"
+
+
+def workload_config(args, kw, builder, world):
+    """The workload-defining keys, identical in both arms (the driver compares them)."""
+    strong = args.scaling == "strong"
+    total_spp = kw["spp"] if strong else kw["spp"] * world
+    tris = int(builder._nt)
+    return {"workload": args.workload, **kw, "triangles": tris, "spp_total": total_spp,
+            "partition": "tile %% %d == rank, %d spp per rank-tile" % (world, total_spp), "l2": L2_NOTE,
+            "spp_override": bool(args.spp)}, total_spp
+
 
 def run_reference_arm(args):
     if int(os.environ.get("RANK", "0")) != 0:
@@ -154,14 +178,24 @@ def run_reference_arm(args):
             vals.append(v)
             secs.append(st.seconds)
     value = float(np.sum([v * s for v, s in zip(vals, secs)]) / np.sum(secs))
+    world = max(1, args.gpus)
+    config, _ = workload_config(args, kw, builder, world)
     out = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-           "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(secs)), "higher_is_better": True, "scaling": "weak",
-           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": {"workload": args.workload, **kw, "note": "reference CPU path on the host cores; each step is a bounded sample"},
-           "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": ref.kind, "sample": sample,
-                            "kd_build_s": round(ref.build_s, 2)},
+           "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(secs)), "higher_is_better": True,
+           "scaling": args.scaling if world > 1 else "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+           "note": "reference CPU path on the host cores; each step is a bounded sample of the workload (see cpu_baseline.sample)",
+           "cpu_baseline": ref.record(value, cores, sample),
            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(out), flush=True)
+
+
+def trace_source_hash():
+    import hashlib
+    h = hashlib.sha256()
+    for f in ("traverse.h", "trace.cuh", "bvh.h", "trace.cu"):
+        h.update(open(os.path.join(ROOT, "mitsuba_b200", "csrc", f), "rb").read())
+    return h.hexdigest()[:16]
 
 
 def host_bytes(builder):
@@ -186,8 +220,8 @@ def run_b200_arm(args):
     lib.init(local)
 
     builder, kw = make_builder(args)
-    spp = kw["spp"]
-    total_spp = spp * world                     # weak scaling: N x spp of the same image, tiles interleaved over ranks
+    # strong (default): ONE frame, tiles interleaved over ranks; weak: N x spp of the same image
+    config, total_spp = workload_config(args, kw, builder, world)
     scene = lib.Scene(builder)
     info = scene.info()
     film_t = mdist.film_tensor(scene) if world > 1 else None
@@ -284,35 +318,35 @@ def run_b200_arm(args):
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         achieved = closest * b_c / (ms_closest * 1e-3) / 1e9 if ms_closest > 0 else 0.0
-        # measured DRAM traffic of the same kernel (one ncu --set full capture, profiles/r01_traffic.json), per launch
-        traffic, n_closest_launches = None, 0
+        # measured DRAM traffic of the same kernel: only when an ncu --set full capture of THIS kernel source and workload
+        # is committed (profiles/r02_traffic.json records the hash of the traversal sources it was taken on)
+        traffic, traffic_note = None, "no ncu capture of this kernel build / workload committed"
         try:
-            tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
-            bpr = tj.get(args.workload, {}).get("dram_bytes_per_ray_closest")
-            n_closest_launches = max(1, (launches_all // world) // 11)        # 11 kernels per bounce, one of them k_trace<closest>
-            if bpr:
-                traffic = bpr * closest / n_closest_launches
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r02_traffic.json")))
+            ent = tj.get(args.workload)
+            if ent and ent.get("trace_src_sha16") == trace_source_hash():
+                n_launch = max(1, int(sum(s.closest_launches for s in stats)))
+                traffic = ent["dram_bytes_per_ray_closest"] * closest / n_launch
+                traffic_note = ("DRAM bytes per k_trace<closest> launch = measured bytes/ray (%s) x mean rays per launch; algorithmic bytes/ray = %d"
+                                % (ent.get("source", "ncu --set full"), b_c))
         except Exception:
             pass
+        n_closest_launches = max(1, int(sum(s.closest_launches for s in stats)))
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": max_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, **kw, "triangles": int(info.n_tris), "spp_total": total_spp,
-                       "partition": "tile %% %d, %d spp per rank-tile" % (world, total_spp), "bvh_nodes": int(info.n_bvh_nodes),
-                       "bvh_build_ms": round(float(info.build_ms), 2), "l2": "flushed between steps (160 MB write); per-step working set >> L2",
-                       "spp_override": bool(args.spp)},
+            "ms_per_step": max_ms / args.steps, "higher_is_better": True, "scaling": args.scaling if world > 1 else "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+            "detail": {"bvh_nodes": int(info.n_bvh_nodes), "bvh_build_ms": round(float(info.build_ms), 2)},
             "mrays_per_s": rays_all / (max_ms * 1e-3) / 1e6,
             "rays_per_sample": rays_all / samples_all,
             "wall_s_timed_region": wall_s,
             "stage_ms_last_step": {"raygen": s0.ms_raygen, "trace_closest": s0.ms_trace_closest, "shade": s0.ms_shade,
                                    "trace_any": s0.ms_trace_any, "splat": s0.ms_splat, "total": s0.ms_total, "passes": s0.n_passes},
             "roofline": {"bound": "hbm", "kernel": "k_trace<closest>", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic,
-                         "traffic_note": "DRAM bytes per k_trace<closest> launch = measured bytes/ray (ncu, profiles/r01_traffic.json) x mean rays per launch; "
-                                         "algorithmic bytes/ray = %d, so the BVH is served by L2 and the kernel is issue/L1-bound, not HBM-bound" % b_c,
+                         "frac": achieved / peak, "traffic": traffic, "traffic_note": traffic_note,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
-                         "bytes_per_ray": b_c},
+                         "bytes_per_ray": b_c, "launches": n_closest_launches, "avg_launch_ms": ms_closest / n_closest_launches,
+                         "rays_per_launch": closest / n_closest_launches},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": host_bytes(builder), "d2h_bytes_per_step": d2h,
                     "includes": "mtsb_scene_create (H2D + GPU BVH build) + mtsb_render + film reduce + mtsb_film_develop (D2H) per step",
                     "wall_ms_per_step": {k: round(v, 2) for k, v in e2e_split.items()}},
@@ -321,8 +355,7 @@ def run_b200_arm(args):
         if not args.no_cpu_baseline and world == 1:
             ref = CpuReference(builder)
             v, cores, sample, _ = ref.step(args.cpu_seconds)
-            out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": ref.kind, "sample": sample,
-                                   "kd_build_s": round(ref.build_s, 2)}
+            out["cpu_baseline"] = ref.record(v, cores, sample)
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -22,6 +22,8 @@
  *                          MIPathTracer::Li             src/integrators/path/path.cpp:121-296
  *   mtsb_film_develop   <- HDRFilm::develop             src/films/hdrfilm.cpp:481-
  *   mtsb_cancel         <- Integrator::cancel           src/librender/integrator.cpp:90-93
+ *   mtsb_multi_render   <- RenderJob / BlockedRenderProcess: one frame's blocks over several workers, merged film
+ *                          src/librender/renderproc.cpp:149-156, src/librender/imageproc.cpp:43-78
  *
  * Conventions: plain C types only, opaque handles, `int` status (0 = ok),
  * error text through mtsb_last_error().  No exception crosses this boundary.
@@ -39,7 +41,7 @@
 extern "C" {
 #endif
 
-#define MTSB_ABI_VERSION 5
+#define MTSB_ABI_VERSION 6
 
 /* ---- status codes ---------------------------------------------------- */
 enum {
@@ -76,7 +78,9 @@ typedef struct MtsbMaterial {
     float    spec_weight;     /* plastic: m_specularSamplingWeight (plastic.cpp:199-204) */
     uint32_t tex_reflectance; /* 1 + index into MtsbSceneDesc::textures of the texture that replaces `reflectance`, 0 = constant */
     uint32_t tex_transmittance; /* same for `transmittance`                            */
-    uint32_t _pad1;
+    uint32_t tex_alpha;       /* same for the roughness `alpha` of roughconductor / roughdielectric: the texture's channel
+                                 average replaces alpha_u and alpha_v at the hit (roughconductor.cpp:379-384,
+                                 roughdielectric.cpp:300-305), clamped to >= 1e-4 as MicrofacetDistribution does */
 } MtsbMaterial;              /* 96 bytes */
 
 /* ---- textures (reference: src/textures/{bitmap,checkerboard,gridtexture,scale}.cpp, src/librender/texture.cpp) ----
@@ -256,6 +260,14 @@ typedef struct MtsbStats {
     float    ms_trace_closest, ms_trace_any, ms_shade, ms_raygen, ms_splat;
     float    ms_h2d, ms_d2h;
     uint32_t n_passes;
+    uint32_t closest_launches;      /* k_trace<closest> launches that had rays (speculative empty launches excluded) */
+    uint32_t any_launches;          /* k_trace<any> launches that had rays                 */
+    uint32_t n_devices;             /* GPUs that took part (mtsb_multi_render; 1 otherwise) */
+    float    ms_reduce;             /* mtsb_multi_render: NCCL reduce of the film (device time on device 0) */
+    uint32_t _pad;
+    /* rays in flight per bounce, summed over the passes of the call: [b] = closest-hit rays of bounce b
+     * (b = 0: camera rays), shadow rays generated at bounce b; bounces >= 15 add to the last entry */
+    uint64_t closest_rays_bounce[16], shadow_rays_bounce[16];
 } MtsbStats;
 
 typedef struct MtsbSceneInfo {
@@ -310,6 +322,22 @@ int  mtsb_film_develop(mtsb_scene_t scene, float *rgb);
 /* Render: generate, trace, shade, splat. Film stays on the device. */
 int  mtsb_render(mtsb_scene_t scene, const MtsbRenderParams *params, MtsbStats *stats);
 int  mtsb_cancel(mtsb_scene_t scene);
+
+/* ---- several GPUs of one node inside the library (reference: the block scheduler hands the blocks of ONE frame to
+ * its workers and merges them into one film: src/librender/renderproc.cpp:149-156, imageproc.cpp:43-78).
+ * mtsb_multi_create replicates the scene on n_devices GPUs (one host thread per GPU uploads it and builds its BVH) and
+ * opens an NCCL communicator over them; mtsb_multi_render renders the 32x32 tiles t with t % n_devices == i on device i
+ * (every sample of those tiles; params->tile_index / tile_count must be 0) and sums the bordered per-device films onto
+ * device_ids[0] with ONE ncclReduce over NVLink; the film calls below then act on that device.  NCCL is loaded at run
+ * time (libnccl.so.2) by mtsb_multi_create only; with n_devices == 1 no NCCL is needed.  stats are summed over the
+ * devices, times are the maximum over devices.                                                                      */
+typedef struct mtsb_multi_s *mtsb_multi_t;
+int  mtsb_multi_create(const MtsbSceneDesc *desc, int n_devices, const int *device_ids /* NULL: 0..n-1 */, mtsb_multi_t *out);
+int  mtsb_multi_render(mtsb_multi_t m, const MtsbRenderParams *params, MtsbStats *stats);
+int  mtsb_multi_cancel(mtsb_multi_t m);
+mtsb_scene_t mtsb_multi_scene(mtsb_multi_t m, int i);   /* scene on the i-th device (i = 0 holds the reduced film) */
+int  mtsb_multi_device_count(mtsb_multi_t m);
+void mtsb_multi_destroy(mtsb_multi_t m);
 
 /* Synthetic workload generators used by bench.py / tests (device-side ray sets of cfg 4). */
 int  mtsb_gen_rays_device(mtsb_scene_t scene, int kind /*0 camera-coherent, 1 bsphere chords*/,

@@ -8,6 +8,8 @@
  *   mtsbh_scene_desc                    <- Scene::initialize flattening src/librender/scene.cpp:322-384
  *   mtsbh_render                        <- RenderJob::run               src/librender/renderjob.cpp:91-150
  *                                          (preprocess -> render -> film develop)
+ *   mtsbh_render_multi                  <- the same job with the scheduler's workers = the GPUs of the node
+ *                                          (Scheduler / BlockedRenderProcess, src/librender/renderproc.cpp:149-156)
  *   mtsbh_write_pfm                     <- Bitmap::write(EPFM)          src/libcore/bitmap.cpp (PFM writer)
  *
  * The library (libmtsb200host.so) is plain C++ and links against libmtsb200.so; it never computes
@@ -44,6 +46,10 @@ const char *mtsbh_warning(mtsbh_scene_t scene, int i);
  * (<=0: the sampler's sampleCount) with mtsb_render, develops the film into
  * rgb[crop_height*crop_width*3]. `stats` may be NULL. */
 int  mtsbh_render(mtsbh_scene_t scene, int spp, float *rgb, MtsbStats *stats);
+/* The same job on `n_devices` GPUs of this node (device ids 0..n-1): the blocks of the frame are distributed over the
+ * GPUs and merged into one film, as the reference's scheduler distributes them over its workers
+ * (mtsb_multi_create / mtsb_multi_render; src/librender/renderproc.cpp:149-156).  n_devices <= 0: every GPU present. */
+int  mtsbh_render_multi(mtsbh_scene_t scene, int spp, int n_devices, float *rgb, MtsbStats *stats);
 
 /* Little-endian colour PFM, bottom row first as the format requires. */
 int  mtsbh_write_pfm(const char *path, const float *rgb, int width, int height);

@@ -8,7 +8,7 @@ import ctypes as C
 
 import numpy as np
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 OK, ERR_INVALID, ERR_NO_DEVICE, ERR_CUDA, ERR_CANCELLED, ERR_IO, ERR_PARSE = range(7)
 BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_ROUGHDIELECTRIC, BSDF_NULL, BSDF_DIELECTRIC, BSDF_CONDUCTOR, BSDF_PLASTIC = range(7)
@@ -30,7 +30,7 @@ class Material(C.Structure):
                 ("alpha_u", C.c_float), ("alpha_v", C.c_float), ("eta", C.c_float), ("fdr_int", C.c_float),
                 ("reflectance", C.c_float * 3), ("transmittance", C.c_float * 3),
                 ("cond_eta", C.c_float * 3), ("cond_k", C.c_float * 3), ("spec_weight", C.c_float),
-                ("tex_reflectance", C.c_uint32), ("tex_transmittance", C.c_uint32), ("_pad1", C.c_uint32)]
+                ("tex_reflectance", C.c_uint32), ("tex_transmittance", C.c_uint32), ("tex_alpha", C.c_uint32)]
 
 
 class Shape(C.Structure):
@@ -93,7 +93,10 @@ class Stats(C.Structure):
                 ("shade_events", C.c_uint64), ("path_length_sum", C.c_uint64), ("kernel_launches", C.c_uint64),
                 ("bad_samples", C.c_uint64), ("ms_total", C.c_float), ("ms_trace_closest", C.c_float),
                 ("ms_trace_any", C.c_float), ("ms_shade", C.c_float), ("ms_raygen", C.c_float),
-                ("ms_splat", C.c_float), ("ms_h2d", C.c_float), ("ms_d2h", C.c_float), ("n_passes", C.c_uint32)]
+                ("ms_splat", C.c_float), ("ms_h2d", C.c_float), ("ms_d2h", C.c_float), ("n_passes", C.c_uint32),
+                ("closest_launches", C.c_uint32), ("any_launches", C.c_uint32), ("n_devices", C.c_uint32),
+                ("ms_reduce", C.c_float), ("_pad", C.c_uint32),
+                ("closest_rays_bounce", C.c_uint64 * 16), ("shadow_rays_bounce", C.c_uint64 * 16)]
 
 
 class SceneInfo(C.Structure):

@@ -15,7 +15,10 @@
 namespace mtsb {
 
 static thread_local std::string g_error;
-static int g_device = -1;
+// The device a thread creates its scenes on: set per THREAD by mtsb_init (mtsb_multi_create runs one host thread per
+// GPU); a thread that never called mtsb_init inherits the device of the last mtsb_init of the process.
+static thread_local int g_device = -1;
+static std::atomic<int> g_default_device{-1};
 static int g_sm_count = 0;
 
 void set_error(const std::string &s) { g_error = s; }
@@ -29,7 +32,7 @@ int cuda_fail(cudaError_t e, const char *what, const char *file, int line) {
 
 static int ensure_device() {
     if (g_device >= 0) return MTSB_OK;
-    return mtsb_init(-1);
+    return mtsb_init(g_default_device.load());
 }
 
 // ring of work counters for the persistent kernels
@@ -159,7 +162,7 @@ extern "C" int mtsb_init(int device) {
     cudaDeviceProp prop;
     MTSB_CUDA(cudaGetDeviceProperties(&prop, device));
     if (prop.major < 10) { set_error(std::string("device is not sm_100-class: ") + prop.name); return MTSB_ERR_NO_DEVICE; }
-    g_device = device; g_sm_count = prop.multiProcessorCount;
+    g_device = device; g_default_device.store(device); g_sm_count = prop.multiProcessorCount;
     MTSB_CUDA(cudaFree(0));
     return MTSB_OK;
 }
@@ -407,6 +410,7 @@ extern "C" int mtsb_scene_create(const MtsbSceneDesc *d, mtsb_scene_t *out) {
         if ((rc = dev_upload(s, &v.sampler, &sv, 1))) return fail(rc);
     }
     if ((rc = build_bvh(s, v.positions, v.indices, d->n_tris))) return fail(rc);
+    if ((rc = pack_shading_records(s, d->n_tris))) return fail(rc);
     {   // Scene::m_aabb -> bounding sphere of the environment emitter (scene.cpp:388-414, constant.cpp:67-71)
         float lo[3], hi[3];
         for (int k = 0; k < 3; ++k) { lo[k] = d->n_tris ? v.box_lo[k] : 0.0f; hi[k] = d->n_tris ? v.box_hi[k] : 0.0f; }

@@ -24,6 +24,13 @@ typedef uint4 U4;
 struct alignas(16) U4 { uint32_t x, y, z, w; };
 #endif
 
+// 128-bit read-only load
+#if MTSB_DEVICE_CODE
+MTSB_HD U4 ld16(const U4 *p) { return __ldg(p); }
+#else
+MTSB_HD U4 ld16(const U4 *p) { return *p; }
+#endif
+
 // 48-byte triangle record (Wald projection coefficients, triaccel.h:37-62)
 struct alignas(16) TriRec {
     uint32_t k; float n_u, n_v, n_d;
@@ -32,14 +39,17 @@ struct alignas(16) TriRec {
 };
 
 // 80-byte wide node.  Child boxes are quantised to 8 bits relative to (p, 2^e).
-//   meta[i] == 0                : empty slot
-//   meta[i] == 001sssss (s>=24) : inner child; s-24 is the slot, node = child_base + rank in imask
-//   meta[i] == uuuooooo         : leaf; uuu = unary triangle count (001,011,111), ooooo = offset from tri_base
+//   imask bit s            : slot s holds an inner child; its node = child_base + rank of s in imask
+//   counts bits 2s, 2s+1   : slot s holds a leaf with 1..3 triangles (0: empty or inner); the leaf's triangles start at
+//                            tri_base + (sum of the counts of the slots below s), i.e. they are stored in slot order
+// Slot s is the octant (sign pattern) of the child relative to the node centre, so a ray visits the children of a
+// node in the order of decreasing s ^ octinv (traverse.h) without looking at the boxes.
 struct alignas(16) Node8 {
     float px, py, pz;
     uint8_t ex, ey, ez, imask;
     uint32_t child_base, tri_base;
-    uint8_t meta[8];
+    uint16_t counts, pad0;
+    uint32_t pad1;
     uint8_t qlox[8], qloy[8], qloz[8];
     uint8_t qhix[8], qhiy[8], qhiz[8];
 };
@@ -304,12 +314,11 @@ MTSB_HD void wide_node_build(uint32_t w, const WideBuildArgs &a, bool tiny) {
     nd.px = nlo[0]; nd.py = nlo[1]; nd.pz = nlo[2];
     nd.ex = quant_exponent(nhi[0] - nlo[0]); nd.ey = quant_exponent(nhi[1] - nlo[1]); nd.ez = quant_exponent(nhi[2] - nlo[2]);
     const float sx = u2f((uint32_t) nd.ex << 23), sy = u2f((uint32_t) nd.ey << 23), sz = u2f((uint32_t) nd.ez << 23);
-    nd.imask = 0; nd.child_base = child_base; nd.tri_base = tri_base;
+    nd.imask = 0; nd.child_base = child_base; nd.tri_base = tri_base; nd.counts = 0; nd.pad0 = 0; nd.pad1 = 0;
     uint32_t inner_rank = 0, tri_off = 0;
     for (int s = 0; s < 8; ++s) {
         int c = child_in_slot[s];
         if (c < 0) {
-            nd.meta[s] = 0;
             nd.qlox[s] = nd.qloy[s] = nd.qloz[s] = 255; nd.qhix[s] = nd.qhiy[s] = nd.qhiz[s] = 0;
             continue;
         }
@@ -322,13 +331,11 @@ MTSB_HD void wide_node_build(uint32_t w, const WideBuildArgs &a, bool tiny) {
         nd.qhiz[s] = (uint8_t) fminf(fmaxf(qhz, 0.0f), 255.0f);
         if (cleaf[c]) {
             uint32_t cnt = csize[c];
-            uint32_t unary = cnt == 1 ? 1u : (cnt == 2 ? 3u : 7u);
-            nd.meta[s] = (uint8_t) ((unary << 5) | tri_off);
+            nd.counts |= (uint16_t) (cnt << (2 * s));
             for (uint32_t j = 0; j < cnt; ++j)
                 a.tri_out[(size_t) tri_base + tri_off + j] = a.tri_in[a.sorted_prim[cfirst[c] + j]];
             tri_off += cnt;
         } else {
-            nd.meta[s] = (uint8_t) ((1u << 5) | (24u + (uint32_t) s));
             nd.imask |= (uint8_t) (1u << s);
             a.wbin[child_base + inner_rank] = cand[c];
             ++inner_rank;

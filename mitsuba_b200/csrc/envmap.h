@@ -86,6 +86,9 @@ MTSB_HD V3 envmap_eval(const EnvmapView &ev, V3 d) {
     return value * ev.scale;
 }
 
+// PLACEHOLDER until the MIP pyramid of the map is built (texture.h): unfiltered
+MTSB_HD V3 envmap_eval_filtered(const EnvmapView &ev, V3 d, V3 rxd, V3 ryd) { (void) rxd; (void) ryd; return envmap_eval(ev, d); }
+
 // EnvironmentMap::sampleReuse (envmap.cpp:655-661): std::lower_bound on a float CDF
 MTSB_HD uint32_t envmap_sample_reuse(const float *cdf, uint32_t size, float &sample) {
     uint32_t lo = 0, n = size + 1;

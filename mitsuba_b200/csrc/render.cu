@@ -5,15 +5,19 @@
 // pixel of a set of 32x32 tiles.  Per bounce the stages are separate kernels over queues:
 //
 //   k_trace<closest>   rays[cur]            -> hits                      (trace.cuh)
-//   k_sort             hits                 -> one queue per BSDF model (+ miss queue)
+//   k_sort             hits                 -> one queue per BSDF model; rays that left the scene
+//                                              get their environment term here and are finished
 //   k_shade<MODEL>     queue[MODEL]         -> emitter hit + MIS, Russian roulette, emitter
 //                                              sampling + BSDF eval (-> shadow queue),
 //                                              BSDF sampling (-> rays[1-cur])
-//   k_miss             queue[MISS]          -> environment term
 //   k_trace<any>       shadow queue         -> adds the pending contribution when unoccluded
 //
 // and at the end of the pass k_splat accumulates every tile in shared memory and adds it to
 // the film (ImageBlock::put + the overlap-add of BlockedRenderProcess::processResult).
+//
+// Every kernel takes its work size from device counters (a ring of per-bounce sets, render.cuh), so the
+// host enqueues the bounces of a pass back to back without waiting for the device; it only polls the
+// queue sizes, asynchronously, to stop enqueueing once a pass has run out of rays.
 //
 // Loop restructuring with respect to path.cpp: the reference traces the BSDF ray inside
 // iteration k and then finishes iteration k (emitter hit with MIS :259-266, break on miss
@@ -125,8 +129,9 @@ __device__ __noinline__ QmcDraw qmc_draw(const SamplerView *svp, uint64_t seed, 
 
 __global__ void k_pass_begin(PathBuffers pb, uint32_t n_slots) {
     Counters *c = pb.ctr;
-    c->n_rays[0] = n_slots; c->n_rays[1] = 0; c->n_shadow = 0;          // k_raygen fills queue entry `slot` for every slot
-    for (int i = 0; i < Q_COUNT; ++i) c->n_q[i] = 0;
+    for (int r = threadIdx.x; r < MTSB_CTR_RING * 16; r += blockDim.x) reinterpret_cast<uint32_t *>(c->b)[r] = 0;
+    __syncthreads();
+    if (threadIdx.x == 0) c->b[0].n_rays = n_slots;          // k_raygen fills queue entry `slot` for every slot
 }
 
 // integrator.cpp:218-241: pixel offset from the sampler, sensor ray, new radiance query
@@ -162,38 +167,83 @@ __global__ void k_raygen(SceneView sc, PathBuffers pb, PassInfo ps, uint32_t n_s
     }
 }
 
-// n_count: rays of this bounce that count as traced (the primary queue also holds the dead rays of edge tiles)
-__global__ void k_bounce_prepare(PathBuffers pb, int cur, uint32_t n_count) {
+// sums the shadow rays of the last bounce that was launched
+__global__ void k_pass_end(PathBuffers pb, int last_bounce) {
     Counters *c = pb.ctr;
-    c->closest += n_count ? n_count : c->n_rays[cur];
-    c->shadow += c->n_shadow;
-    c->n_shadow = 0; c->n_rays[1 - cur] = 0;
-    for (int i = 0; i < Q_COUNT; ++i) c->n_q[i] = 0;
+    const uint32_t n = c->b[last_bounce % MTSB_CTR_RING].n_shadow;
+    c->shadow += n; if (n) c->launches_any++;
+    c->shadow_bounce[min(last_bounce, MTSB_BOUNCE_STATS - 1)] += n;
 }
-__global__ void k_pass_end(PathBuffers pb) { Counters *c = pb.ctr; c->shadow += c->n_shadow; c->n_shadow = 0; }
 
-// bins the hits of this bounce by scattering model.  Queue space is reserved once per BLOCK and queue
-// (shared-memory counts, one global atomic per non-empty queue): per-warp atomics on a single counter
-// run at ~1 G/s on this part and were a visible share of the stage.
-__host__ __device__ inline int queue_of_type(uint32_t t) {
-    return t == MTSB_BSDF_DIFFUSE ? Q_DIFFUSE : t == MTSB_BSDF_ROUGHCONDUCTOR ? Q_CONDUCTOR : t == MTSB_BSDF_ROUGHDIELECTRIC ? Q_DIELECTRIC
-         : (t == MTSB_BSDF_DIELECTRIC || t == MTSB_BSDF_CONDUCTOR) ? Q_DELTA : t == MTSB_BSDF_PLASTIC ? Q_GENERIC : Q_NULL;
-}
-__host__ __device__ inline int queue_of_material(const MtsbMaterial *mats, int mat) {
-    if (mat < 0) return Q_NULL;
-    const MtsbMaterial &m = mats[mat];
-    const int q = queue_of_type(m.type);
-    if (m.tex_reflectance | m.tex_transmittance) return Q_TEXTURED;
-    if ((m.flags & MTSB_MAT_TWOSIDED) && m.back >= 0) {
-        if (mats[m.back].tex_reflectance | mats[m.back].tex_transmittance) return Q_TEXTURED;
-        if (queue_of_type(mats[m.back].type) != q) return Q_GENERIC;
+struct RenderConst { int max_depth, rr_depth, strict_normals, hide_emitters; };
+
+// a ray that left the scene: environment term (path.cpp:138-145 first segment; :237-246, 259-266 afterwards); returns the
+// path length of the finished sample
+__device__ __forceinline__ uint32_t finish_escaped(const SceneView &sc, const PathBuffers &pb, const RenderConst &rc, int cur, uint32_t q) {
+    const uint32_t slot = pb.ray_slot[cur][q];
+    float4 lb = pb.L_bpdf[slot];
+    const float4 rf = pb.refn_flags[slot];
+    const uint32_t fl = __float_as_uint(rf.w);
+    if (!(fl & PF_VALID)) return 0;                                            // dead ray of an edge tile
+    if (sc.env_emitter >= 0) {
+        const float4 te = pb.thr_eta[slot];
+        const V3 thr(te.x, te.y, te.z);
+        RayIn ray;
+        if (!(fl & PF_FIRST) || sc.envmap) ray = load_ray(pb.rays[cur], q);     // a constant environment needs no direction
+        else { ray.ox = ray.oy = ray.oz = ray.dx = ray.dy = 0.0f; ray.dz = 1.0f; ray.mint = ray.maxt = 0.0f; }
+        V3 value;
+        if ((fl & PF_FIRST) && sc.envmap) {
+            // envmap.cpp:380-410: a camera ray carries differentials, so the lookup is filtered (MIPMap::eval)
+            V3 rxd, ryd;
+            const float2 sp = pb.spos[slot];
+            sensor_ray_differentials(sc.sensor, sc.near_x, sc.near_y, sp.x, sp.y, sc.integrator.sample_count, rxd, ryd);
+            value = environment_eval_filtered(sc, V3(ray.dx, ray.dy, ray.dz), rxd, ryd);
+        } else value = environment_eval(sc, V3(ray.dx, ray.dy, ray.dz));        // constant.cpp:242-244 / envmap.cpp:380-410 without differentials
+        if (fl & PF_FIRST) {
+            if (!rc.hide_emitters) { lb.x += thr.x * value.x; lb.y += thr.y * value.y; lb.z += thr.z * value.z; }
+        } else {
+            // fillDirectSamplingRecord (constant.cpp:246-260): the ray must start inside the bounding sphere
+            float nearT, farT;
+            const V3 o(ray.ox, ray.oy, ray.oz), d(ray.dx, ray.dy, ray.dz);
+            if (bsphere_intersect(sc.bsphere_c, sc.bsphere_r, o, d, nearT, farT) && !(nearT > 0 || farT < 0)) {
+                DRec dRec; dRec.ref = o; dRec.refN = V3(rf.x, rf.y, rf.z); dRec.p = o; dRec.n = V3(0.0f); dRec.d = d; dRec.dist = farT;
+                dRec.measure = MTSB_MEASURE_SOLID_ANGLE; dRec.emitter = sc.env_emitter;
+                const float w = mi_weight(lb.w, lb.w < 0 ? 0.0f : pdf_emitter_direct(sc, dRec));
+                lb.x += thr.x * value.x * w; lb.y += thr.y * value.y * w; lb.z += thr.z * value.z * w;
+            }
+        }
     }
-    return q;
+    lb.w = 0.0f;
+    pb.L_bpdf[slot] = lb;
+    return fl & PF_DEPTH_MASK;
 }
+
+// Bins the hits of bounce `bounce` by scattering model and finishes the rays that left the scene.  Queue space is
+// reserved once per BLOCK and queue (shared-memory counts, one global atomic per non-empty queue): per-warp atomics
+// on a single counter run at ~1 G/s on this part and were a visible share of the stage.  The queue of a triangle
+// comes from a byte table (10 MB for 10 M triangles, L2 resident) instead of the chain prim -> shape -> material.
+// Block 0 also does the bookkeeping of the counter ring: ray totals of this bounce, shadow-ray total of the
+// previous one, and it clears the set that bounce + MTSB_CTR_RING / 2 will use.
+// n_count: rays of this bounce that count as traced (the primary queue also holds the dead rays of edge tiles), 0 = all
 #define MTSB_SORT_BLOCK 512
-__global__ void __launch_bounds__(MTSB_SORT_BLOCK) k_sort(SceneView sc, PathBuffers pb, int cur) {
+__global__ void __launch_bounds__(MTSB_SORT_BLOCK) k_sort(SceneView sc, PathBuffers pb, RenderConst rc, int cur, int bounce, uint32_t n_count) {
     __shared__ uint32_t s_cnt[Q_COUNT], s_base[Q_COUNT];
-    const uint32_t n = pb.ctr->n_rays[cur];
+    BounceCtr &bc = pb.ctr->b[bounce % MTSB_CTR_RING];
+    const uint32_t n = bc.n_rays;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        Counters *c = pb.ctr;
+        const uint32_t nc = n_count ? n_count : n;
+        c->closest += nc; c->rays_bounce[min(bounce, MTSB_BOUNCE_STATS - 1)] += nc;
+        if (n) c->launches_closest++;
+        if (bounce > 0) {
+            const uint32_t ns = c->b[(bounce - 1) % MTSB_CTR_RING].n_shadow;
+            c->shadow += ns; c->shadow_bounce[min(bounce - 1, MTSB_BOUNCE_STATS - 1)] += ns;
+            if (ns) c->launches_any++;
+        }
+        uint32_t *z = reinterpret_cast<uint32_t *>(&c->b[(bounce + MTSB_CTR_RING / 2) % MTSB_CTR_RING]);
+        for (int i = 0; i < 16; ++i) z[i] = 0;
+    }
+    unsigned long long path_len = 0;
     for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
         const uint32_t q = base + threadIdx.x;
         if (threadIdx.x < Q_COUNT) s_cnt[threadIdx.x] = 0;
@@ -201,7 +251,8 @@ __global__ void __launch_bounds__(MTSB_SORT_BLOCK) k_sort(SceneView sc, PathBuff
         int which = -1;
         if (q < n) {
             const uint32_t prim = pb.hits[q].prim;
-            which = prim != MTSB_NO_HIT_ID ? queue_of_material(sc.materials, sc.shapes[sc.tri_shape[prim]].material) : (int) Q_MISS;
+            if (prim != MTSB_NO_HIT_ID) which = (int) sc.tri_queue[prim];
+            else path_len += finish_escaped(sc, pb, rc, cur, q);
         }
         // rank inside the block: warp-aggregated shared-memory atomic
         const unsigned peers = __match_any_sync(0xFFFFFFFFu, which);
@@ -211,13 +262,40 @@ __global__ void __launch_bounds__(MTSB_SORT_BLOCK) k_sort(SceneView sc, PathBuff
         wbase = __shfl_sync(0xFFFFFFFFu, wbase, leader);
         const uint32_t rank = wbase + (uint32_t) __popc(peers & ((1u << (threadIdx.x & 31)) - 1u));
         __syncthreads();
-        if (threadIdx.x < Q_COUNT) s_base[threadIdx.x] = s_cnt[threadIdx.x] ? atomicAdd(&pb.ctr->n_q[threadIdx.x], s_cnt[threadIdx.x]) : 0u;
+        if (threadIdx.x < Q_COUNT) s_base[threadIdx.x] = s_cnt[threadIdx.x] ? atomicAdd(&bc.n_q[threadIdx.x], s_cnt[threadIdx.x]) : 0u;
         __syncthreads();
         if (which >= 0) pb.q[which][s_base[which] + rank] = q;
     }
+    for (int o = 16; o; o >>= 1) path_len += __shfl_xor_sync(0xFFFFFFFFu, path_len, o);
+    if ((threadIdx.x & 31) == 0 && path_len) atomicAdd(&pb.ctr->path_len, path_len);
 }
 
-struct RenderConst { int max_depth, rr_depth, strict_normals, hide_emitters; };
+// scene creation: the packed shading record and the queue byte of every triangle (shading.h, render.cuh)
+__global__ void k_pack_tris(SceneView sc, uint32_t n_tris, const uint8_t *shape_queue, U4 *out, uint8_t *tri_queue) {
+    const uint32_t prim = blockIdx.x * blockDim.x + threadIdx.x;
+    if (prim >= n_tris) return;
+    const uint32_t s = sc.tri_shape[prim];
+    const MtsbShape sh = sc.shapes[s];
+    const uint32_t *ix = sc.indices + 3 * (size_t) prim;
+    const uint32_t i0 = ix[0], i1 = ix[1], i2 = ix[2];
+    const bool hn = sh.has_normals && sc.normals, ht = sh.has_texcoords && sc.texcoords;
+    float r[32];
+    for (int k = 0; k < 32; ++k) r[k] = 0.0f;
+    const uint32_t iv[3] = {i0, i1, i2};
+    for (int v = 0; v < 3; ++v) {
+        for (int k = 0; k < 3; ++k) r[4 * v + k] = sc.positions[3 * (size_t) iv[v] + k];
+        if (hn) for (int k = 0; k < 3; ++k) r[12 + 4 * v + k] = sc.normals[3 * (size_t) iv[v] + k];
+    }
+    if (ht) {
+        const float *t0 = sc.texcoords + 2 * (size_t) i0, *t1 = sc.texcoords + 2 * (size_t) i1, *t2 = sc.texcoords + 2 * (size_t) i2;
+        r[15] = t0[0]; r[19] = t0[1]; r[23] = t1[0]; r[24] = t1[1]; r[25] = t2[0]; r[26] = t2[1];
+    }
+    r[3] = __uint_as_float(s);
+    r[7] = __uint_as_float((hn ? 1u : 0u) | (ht ? 2u : 0u));
+    float4 *o = reinterpret_cast<float4 *>(out + (size_t) MTSB_SHADE_TRI_U4 * prim);
+    for (int k = 0; k < 8; ++k) o[k] = make_float4(r[4 * k], r[4 * k + 1], r[4 * k + 2], r[4 * k + 3]);
+    tri_queue[prim] = shape_queue[s];
+}
 
 template <int Q> __device__ __forceinline__ V3 eval_q(const MtsbMaterial *mats, int id, V3 wi, V3 wo) {
     if (Q == Q_GENERIC || Q == Q_TEXTURED) return bsdf_eval(mats, id, wi, wo);
@@ -284,12 +362,14 @@ __device__ __noinline__ void resolve_textured(const SceneView &sc, int mat, cons
 }
 
 template <int Q, bool QMC>
-__global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBuffers pb, PassInfo ps, RenderConst rc, int cur) {
+__global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBuffers pb, PassInfo ps, RenderConst rc, int cur, int bounce) {
     // Outputs (shadow ray + pending contribution, continuation ray) are staged in shared memory and queue space is
     // reserved once per block and queue at the end of the iteration: one global atomic per block instead of one per warp.
     __shared__ float4 s_sray[2 * MTSB_SHADE_BLOCK], s_contrib[MTSB_SHADE_BLOCK], s_nray[2 * MTSB_SHADE_BLOCK];
     __shared__ uint32_t s_wcnt[2][MTSB_SHADE_BLOCK / 32], s_qbase[2];
-    const uint32_t n = pb.ctr->n_q[Q];
+    BounceCtr &bc = pb.ctr->b[bounce % MTSB_CTR_RING];
+    uint32_t *n_next = &pb.ctr->b[(bounce + 1) % MTSB_CTR_RING].n_rays;
+    const uint32_t n = bc.n_q[Q];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned long long shade_events = 0, path_len = 0;
     for (uint32_t i0 = blockIdx.x * blockDim.x; i0 < n; i0 += gridDim.x * blockDim.x) {
@@ -453,7 +533,7 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBu
         if (threadIdx.x < 2) {
             uint32_t tot = 0;
             for (int w = 0; w < MTSB_SHADE_BLOCK / 32; ++w) { const uint32_t c = s_wcnt[threadIdx.x][w]; s_wcnt[threadIdx.x][w] = tot; tot += c; }
-            s_qbase[threadIdx.x] = tot ? atomicAdd(threadIdx.x == 0 ? &pb.ctr->n_shadow : &pb.ctr->n_rays[1 - cur], tot) : 0u;
+            s_qbase[threadIdx.x] = tot ? atomicAdd(threadIdx.x == 0 ? &bc.n_shadow : n_next, tot) : 0u;
         }
         __syncthreads();
         const uint32_t lt = (1u << lane) - 1u;
@@ -476,46 +556,6 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBu
         if (shade_events) atomicAdd(&pb.ctr->shade, shade_events);
         if (path_len) atomicAdd(&pb.ctr->path_len, path_len);
     }
-}
-
-// rays that left the scene: environment term (path.cpp:138-145 first segment; :237-246, 259-266 afterwards)
-__global__ void k_miss(SceneView sc, PathBuffers pb, RenderConst rc, int cur) {
-    const uint32_t n = pb.ctr->n_q[Q_MISS];
-    unsigned long long path_len = 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const uint32_t q = pb.q[Q_MISS][i];
-        const uint32_t slot = pb.ray_slot[cur][q];
-        float4 lb = pb.L_bpdf[slot];
-        const float4 rf = pb.refn_flags[slot];
-        const uint32_t fl = __float_as_uint(rf.w);
-        if (!(fl & PF_VALID)) continue;                                        // dead ray of an edge tile
-        path_len += (unsigned long long) (fl & PF_DEPTH_MASK);
-        if (sc.env_emitter >= 0) {
-            const float4 te = pb.thr_eta[slot];
-            const V3 thr(te.x, te.y, te.z);
-            RayIn ray;
-            if (!(fl & PF_FIRST) || sc.envmap) ray = load_ray(pb.rays[cur], q);     // a constant environment needs no direction
-            else { ray.ox = ray.oy = ray.oz = ray.dx = ray.dy = 0.0f; ray.dz = 1.0f; ray.mint = ray.maxt = 0.0f; }
-            const V3 value = environment_eval(sc, V3(ray.dx, ray.dy, ray.dz));      // constant.cpp:242-244 / envmap.cpp:380-410
-            if (fl & PF_FIRST) {
-                if (!rc.hide_emitters) { lb.x += thr.x * value.x; lb.y += thr.y * value.y; lb.z += thr.z * value.z; }
-            } else {
-                // fillDirectSamplingRecord (constant.cpp:246-260): the ray must start inside the bounding sphere
-                float nearT, farT;
-                const V3 o(ray.ox, ray.oy, ray.oz), d(ray.dx, ray.dy, ray.dz);
-                if (bsphere_intersect(sc.bsphere_c, sc.bsphere_r, o, d, nearT, farT) && !(nearT > 0 || farT < 0)) {
-                    DRec dRec; dRec.ref = o; dRec.refN = V3(rf.x, rf.y, rf.z); dRec.p = o; dRec.n = V3(0.0f); dRec.d = d; dRec.dist = farT;
-                    dRec.measure = MTSB_MEASURE_SOLID_ANGLE; dRec.emitter = sc.env_emitter;
-                    const float w = mi_weight(lb.w, lb.w < 0 ? 0.0f : pdf_emitter_direct(sc, dRec));
-                    lb.x += thr.x * value.x * w; lb.y += thr.y * value.y * w; lb.z += thr.z * value.z * w;
-                }
-            }
-        }
-        lb.w = 0.0f;
-        pb.L_bpdf[slot] = lb;
-    }
-    for (int o = 16; o; o >>= 1) path_len += __shfl_xor_sync(0xFFFFFFFFu, path_len, o);
-    if ((threadIdx.x & 31) == 0 && path_len) atomicAdd(&pb.ctr->path_len, path_len);
 }
 
 // epilogue of the shadow-ray pass: unoccluded -> add the pending emitter contribution
@@ -753,14 +793,15 @@ static void free_buffers(PathBuffers *pb) {
     cudaFree(pb->refn_flags); cudaFree(pb->spos);
     for (int i = 0; i < Q_COUNT; ++i) cudaFree(pb->q[i]);
     cudaFree(pb->ctr); cudaFree(pb->tiles);
-    if (pb->h_ctr) cudaFreeHost(pb->h_ctr);
+    if (pb->h_poll) cudaFreeHost(pb->h_poll);
     delete pb;
 }
 
-// Path buffers are large (about 216 B per slot) and their size does not depend on the scene, so a
+// Path buffers are large (about 212 B per slot) and their size does not depend on the scene, so a
 // destroyed scene parks them in a per-device pool and the next scene's first render picks them up
 // instead of paying cudaMalloc / cudaFree of several GB again.  The pool keeps at most
 // MTSB_MAX_LANES sets per device for the life of the process.
+#define MTSB_SLOT_BYTES 212ull         /* 3 x 32 (rays) + 16 (hits) + 16 (contrib) + 3 x 16 + 8 (state) + 2 x 4 (slots) + 7 x 4 (queues) */
 static std::mutex g_pool_mutex;
 static std::map<int, std::vector<PathBuffers *>> g_pool;
 
@@ -775,6 +816,32 @@ int render_free(Scene *s) {
         s->paths[l] = nullptr;
         if (s->lane_stream[l]) { cudaStreamDestroy(s->lane_stream[l]); s->lane_stream[l] = nullptr; }
     }
+    return MTSB_OK;
+}
+
+// A set of path buffers is handed to the scene only when EVERY allocation succeeded: after an out-of-memory error the
+// scene keeps no half-built set (whose capacity would look sufficient to the next render) and nothing stays allocated.
+static int alloc_buffers(uint32_t capacity, uint32_t n_tiles, PathBuffers **out) {
+    PathBuffers *pb = new PathBuffers();
+    memset(pb, 0, sizeof(*pb));
+    const size_t c = capacity;
+    cudaError_t e = cudaSuccess;
+    auto dm = [&](void **p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, bytes); };
+    for (int i = 0; i < 2; ++i) { dm((void **) &pb->rays[i], c * sizeof(RayIn)); dm((void **) &pb->ray_slot[i], c * 4); }
+    dm((void **) &pb->hits, c * sizeof(HitOut));
+    dm((void **) &pb->srays, c * sizeof(RayIn));
+    dm((void **) &pb->scontrib, c * sizeof(float4));
+    dm((void **) &pb->thr_eta, c * sizeof(float4));
+    dm((void **) &pb->L_bpdf, c * sizeof(float4));
+    dm((void **) &pb->refn_flags, c * sizeof(float4));
+    dm((void **) &pb->spos, c * sizeof(float2));
+    for (int i = 0; i < Q_COUNT; ++i) dm((void **) &pb->q[i], c * 4);
+    dm((void **) &pb->ctr, sizeof(Counters));
+    dm((void **) &pb->tiles, (size_t) std::max(1u, n_tiles) * sizeof(int));
+    if (e == cudaSuccess) e = cudaMallocHost((void **) &pb->h_poll, MTSB_POLL_RING * sizeof(uint32_t));
+    if (e != cudaSuccess) { free_buffers(pb); return cuda_fail(e, "cudaMalloc(path buffers)", __FILE__, __LINE__); }
+    pb->capacity = capacity; pb->tiles_capacity = n_tiles;
+    *out = pb;
     return MTSB_OK;
 }
 
@@ -796,29 +863,32 @@ static int ensure_buffers(Scene *s, int lane, uint32_t capacity, uint32_t n_tile
     if (s->paths[lane]) {
         PathBuffers *pb = s->paths[lane];
         if (pb->tiles_capacity < n_tiles) {
-            cudaFree(pb->tiles); pb->tiles = nullptr;
-            MTSB_CUDA(cudaMalloc((void **) &pb->tiles, (size_t) std::max(1u, n_tiles) * sizeof(int)));
-            pb->tiles_capacity = n_tiles;
+            int *t = nullptr;
+            MTSB_CUDA(cudaMalloc((void **) &t, (size_t) std::max(1u, n_tiles) * sizeof(int)));
+            cudaFree(pb->tiles); pb->tiles = t; pb->tiles_capacity = n_tiles;
         }
         return MTSB_OK;
     }
-    PathBuffers *pb = new PathBuffers();
-    memset(pb, 0, sizeof(*pb));
-    s->paths[lane] = pb;
-    pb->capacity = capacity; pb->tiles_capacity = n_tiles;
-    const size_t c = capacity;
-    for (int i = 0; i < 2; ++i) { MTSB_CUDA(cudaMalloc((void **) &pb->rays[i], c * sizeof(RayIn))); MTSB_CUDA(cudaMalloc((void **) &pb->ray_slot[i], c * 4)); }
-    MTSB_CUDA(cudaMalloc((void **) &pb->hits, c * sizeof(HitOut)));
-    MTSB_CUDA(cudaMalloc((void **) &pb->srays, c * sizeof(RayIn)));
-    MTSB_CUDA(cudaMalloc((void **) &pb->scontrib, c * sizeof(float4)));
-    MTSB_CUDA(cudaMalloc((void **) &pb->thr_eta, c * sizeof(float4)));
-    MTSB_CUDA(cudaMalloc((void **) &pb->L_bpdf, c * sizeof(float4)));
-    MTSB_CUDA(cudaMalloc((void **) &pb->refn_flags, c * sizeof(float4)));
-    MTSB_CUDA(cudaMalloc((void **) &pb->spos, c * sizeof(float2)));
-    for (int i = 0; i < Q_COUNT; ++i) MTSB_CUDA(cudaMalloc((void **) &pb->q[i], c * 4));
-    MTSB_CUDA(cudaMalloc((void **) &pb->ctr, sizeof(Counters)));
-    MTSB_CUDA(cudaMalloc((void **) &pb->tiles, (size_t) std::max(1u, n_tiles) * sizeof(int)));
-    MTSB_CUDA(cudaMallocHost((void **) &pb->h_ctr, sizeof(Counters)));
+    return alloc_buffers(capacity, n_tiles, &s->paths[lane]);
+}
+
+// scene creation (api.cu): packed shading records + the queue byte of every triangle
+int pack_shading_records(Scene *s, uint64_t n_tris) {
+    SceneView &v = s->v;
+    v.shade_tris = nullptr; v.tri_queue = nullptr;
+    if (n_tris == 0) return MTSB_OK;
+    std::vector<uint8_t> sq(s->h_shape_material.size());
+    for (size_t i = 0; i < sq.size(); ++i) sq[i] = (uint8_t) queue_of_material(s->h_materials.data(), s->h_shape_material[i]);
+    const uint8_t *d_sq = nullptr;
+    int rc = dev_upload(s, &d_sq, sq.data(), sq.size());
+    if (rc) return rc;
+    U4 *recs = nullptr; uint8_t *tq = nullptr;
+    if ((rc = dev_alloc(s, &recs, (size_t) MTSB_SHADE_TRI_U4 * n_tris))) return rc;
+    if ((rc = dev_alloc(s, &tq, (size_t) n_tris))) return rc;
+    k_pack_tris<<<grid_for(n_tris, 256), 256, 0, s->stream>>>(v, (uint32_t) n_tris, d_sq, recs, tq);
+    s->launches++;
+    MTSB_CUDA(cudaGetLastError());
+    v.shade_tris = recs; v.tri_queue = tq;
     return MTSB_OK;
 }
 
@@ -848,96 +918,119 @@ static int shade_grid(size_t n_upper, int sm_count) {
     return (int) std::max<size_t>(1, std::min(need, cap));
 }
 
-// One pass = a block of tiles x a block of samples, small enough for the path buffers of a lane.
+// One pass = a block of tiles x a block of samples, small enough for the path buffers.
 struct Pass { PassInfo ps; uint32_t n_slots, n_valid; };
 
-// A lane is an independent wavefront pipeline (own stream, own path buffers).  Passes are handed to
-// lanes as they become free, so the thin late bounces of one pass -- launches with few rays that
-// cannot fill 148 SMs -- and the host round trip that reads the queue sizes overlap with the wide
-// early bounces of another pass.  The film is shared: k_splat adds with atomics.
-struct Lane {
+// The wavefront pipeline of one render call: a stream, its path buffers and the poll ring through which the host
+// learns (late, and without ever waiting for it) how many rays a bounce had.
+struct Pipeline {
+    Scene *s = nullptr;
     cudaStream_t st = nullptr;
     PathBuffers *pb = nullptr;
     StageTimer *timer = nullptr;
-    cudaEvent_t ev = nullptr;      // queue sizes of the bounce in flight are on the host
-    bool busy = false;
-    Pass pass{};
-    uint32_t n_cur = 0;
-    int cur = 0;
-    bool first = false;            // the bounce in flight is the primary one
-    uint32_t queue_mask = 0;       // shading queues this scene can feed
+    std::vector<cudaEvent_t> ev;       // MTSB_POLL_RING events: "count of bounce i is on the host"
+    uint32_t queue_mask = 0;           // shading queues this scene can feed
+    int sm_count = 148;
+    bool qmc = false;
 };
 
-static int lane_bounce(Scene *s, Lane &L, const RenderConst &rcst, int sm_count) {
-    PathBuffers &pb = *L.pb;
-    const SceneView &v = s->v;
-    L.timer->begin(ST_CLOSEST, L.n_cur);
-    int rc = launch_trace_kernel<false>(s, pb.rays[L.cur], &pb.ctr->n_rays[L.cur], L.n_cur, StoreHit{pb.hits}, L.st);
-    L.timer->end();
+template <int Q> static void launch_shade(Pipeline &P, const Pass &p, const RenderConst &rcst, int g, int cur, int bounce) {
+    if (!(P.queue_mask & (1u << Q))) return;
+    if (P.qmc) k_shade<Q, true><<<g, MTSB_SHADE_BLOCK, 0, P.st>>>(P.s->v, *P.pb, p.ps, rcst, cur, bounce);
+    else k_shade<Q, false><<<g, MTSB_SHADE_BLOCK, 0, P.st>>>(P.s->v, *P.pb, p.ps, rcst, cur, bounce);
+    ++P.s->launches;
+}
+
+// Enqueues one bounce: closest hits -> sort (+ escaped rays) -> shading queues -> shadow rays.  n_upper bounds the
+// number of rays of the bounce from above (it only sizes the grids; the kernels read the exact count on the device).
+static int enqueue_bounce(Pipeline &P, const Pass &p, const RenderConst &rcst, int bounce, uint32_t n_upper) {
+    Scene *s = P.s; PathBuffers &pb = *P.pb; const SceneView &v = s->v;
+    const int cur = bounce & 1;
+    BounceCtr *bc = &pb.ctr->b[bounce % MTSB_CTR_RING];
+    P.timer->begin(ST_CLOSEST, n_upper);
+    int rc = launch_trace_kernel<false>(s, pb.rays[cur], &bc->n_rays, n_upper, StoreHit{pb.hits}, P.st);
+    P.timer->end();
     if (rc) return rc;
-    L.timer->begin(ST_SHADE, L.n_cur);
-    const int g = shade_grid(L.n_cur, sm_count);
-    k_bounce_prepare<<<1, 1, 0, L.st>>>(pb, L.cur, L.first ? L.pass.n_valid : 0u);
-    L.first = false;
-    k_sort<<<std::max(1, std::min((int) ((L.n_cur + MTSB_SORT_BLOCK - 1) / MTSB_SORT_BLOCK), sm_count * 4)), MTSB_SORT_BLOCK, 0, L.st>>>(v, pb, L.cur);
+    P.timer->begin(ST_SHADE, n_upper);
+    const int g = shade_grid(n_upper, P.sm_count);
+    k_sort<<<std::max(1, std::min((int) ((n_upper + MTSB_SORT_BLOCK - 1) / MTSB_SORT_BLOCK), P.sm_count * 4)), MTSB_SORT_BLOCK, 0, P.st>>>(
+        v, pb, rcst, cur, bounce, bounce == 0 ? p.n_valid : 0u);
+    ++s->launches;
     // only the queues some material of this scene can feed are launched
-    const uint32_t qm = L.queue_mask;
-    const bool qmc = v.sampler_type != MTSB_SAMPLER_INDEPENDENT;
-    if (qm & (1u << Q_DIFFUSE))    { if (qmc) k_shade<Q_DIFFUSE, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_DIFFUSE, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
-    if (qm & (1u << Q_CONDUCTOR))  { if (qmc) k_shade<Q_CONDUCTOR, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_CONDUCTOR, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
-    if (qm & (1u << Q_DIELECTRIC)) { if (qmc) k_shade<Q_DIELECTRIC, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_DIELECTRIC, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
-    if (qm & (1u << Q_NULL))       { if (qmc) k_shade<Q_NULL, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_NULL, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
-    if (qm & (1u << Q_TEXTURED))   { if (qmc) k_shade<Q_TEXTURED, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_TEXTURED, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
-    if (qm & (1u << Q_GENERIC))    { if (qmc) k_shade<Q_GENERIC, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_GENERIC, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
-    if (qm & (1u << Q_DELTA))      { if (qmc) k_shade<Q_DELTA, true><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); else k_shade<Q_DELTA, false><<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, L.pass.ps, rcst, L.cur); ++s->launches; }
-    k_miss<<<g, MTSB_SHADE_BLOCK, 0, L.st>>>(v, pb, rcst, L.cur);
-    s->launches += 3;
-    L.timer->end();
-    L.timer->begin(ST_ANY, L.n_cur);
-    rc = launch_trace_kernel<true>(s, pb.srays, &pb.ctr->n_shadow, L.n_cur, ShadowResolve{pb.scontrib, pb.L_bpdf}, L.st);
-    L.timer->end();
+    launch_shade<Q_DIFFUSE>(P, p, rcst, g, cur, bounce);
+    launch_shade<Q_CONDUCTOR>(P, p, rcst, g, cur, bounce);
+    launch_shade<Q_DIELECTRIC>(P, p, rcst, g, cur, bounce);
+    launch_shade<Q_NULL>(P, p, rcst, g, cur, bounce);
+    launch_shade<Q_TEXTURED>(P, p, rcst, g, cur, bounce);
+    launch_shade<Q_GENERIC>(P, p, rcst, g, cur, bounce);
+    launch_shade<Q_DELTA>(P, p, rcst, g, cur, bounce);
+    P.timer->end();
+    P.timer->begin(ST_ANY, n_upper);
+    rc = launch_trace_kernel<true>(s, pb.srays, &bc->n_shadow, n_upper, ShadowResolve{pb.scontrib, pb.L_bpdf}, P.st);
+    P.timer->end();
     if (rc) return rc;
-    MTSB_CUDA(cudaMemcpyAsync(pb.h_ctr, pb.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, L.st));
-    MTSB_CUDA(cudaEventRecord(L.ev, L.st));
+    // the size of the next bounce travels to the host behind this bounce; nobody waits for it
+    const int slot = (bounce + 1) % MTSB_POLL_RING;
+    MTSB_CUDA(cudaMemcpyAsync(&pb.h_poll[slot], &pb.ctr->b[(bounce + 1) % MTSB_CTR_RING].n_rays, sizeof(uint32_t), cudaMemcpyDeviceToHost, P.st));
+    MTSB_CUDA(cudaEventRecord(P.ev[(size_t) slot], P.st));
     return MTSB_OK;
 }
 
-static int lane_start(Scene *s, Lane &L, const Pass &p, const RenderConst &rcst, int sm_count) {
-    L.pass = p; L.busy = true; L.cur = 0; L.n_cur = p.n_slots; L.first = true;
-    L.timer->begin(ST_RAYGEN);
-    k_pass_begin<<<1, 1, 0, L.st>>>(*L.pb, p.n_slots);
-    if (s->v.sampler_type != MTSB_SAMPLER_INDEPENDENT) k_raygen<true><<<shade_grid(p.n_slots, sm_count), MTSB_SHADE_BLOCK, 0, L.st>>>(s->v, *L.pb, p.ps, p.n_slots);
-    else k_raygen<false><<<shade_grid(p.n_slots, sm_count), MTSB_SHADE_BLOCK, 0, L.st>>>(s->v, *L.pb, p.ps, p.n_slots);
+// One pass, enqueued without waiting for the device: ray generation, then bounce after bounce until the path length
+// limit -- or until the host has SEEN (in the poll ring) that a bounce ended with no rays left.  The host usually runs
+// ahead of the device, so a few bounces may be enqueued that find their queues empty (a handful of microseconds each).
+static int run_pass(Pipeline &P, const Pass &p, const RenderConst &rcst, size_t splat_smem) {
+    Scene *s = P.s; PathBuffers &pb = *P.pb;
+    P.timer->begin(ST_RAYGEN);
+    k_pass_begin<<<1, 128, 0, P.st>>>(pb, p.n_slots);
+    if (P.qmc) k_raygen<true><<<shade_grid(p.n_slots, P.sm_count), MTSB_SHADE_BLOCK, 0, P.st>>>(s->v, pb, p.ps, p.n_slots);
+    else k_raygen<false><<<shade_grid(p.n_slots, P.sm_count), MTSB_SHADE_BLOCK, 0, P.st>>>(s->v, pb, p.ps, p.n_slots);
     s->launches += 2;
-    L.timer->end();
-    return lane_bounce(s, L, rcst, sm_count);
-}
+    P.timer->end();
 
-static void lane_finish(Scene *s, Lane &L, size_t splat_smem) {
-    L.timer->begin(ST_SPLAT);
-    k_pass_end<<<1, 1, 0, L.st>>>(*L.pb);
+    const int max_bounces = rcst.max_depth > 0 ? rcst.max_depth : 0x7fffffff;     // a path of depth d spawns no ray at depth >= maxDepth (path.cpp:158)
+    uint32_t n_upper = p.n_slots;
+    int confirmed = 0;            // bounces 0 .. confirmed have a known ray count (bounce 0: n_slots)
+    int bounce = 0, last = -1;
+    bool drained = false;
+    std::vector<uint32_t> known(1, p.n_slots);
+    while (bounce < max_bounces && !drained) {
+        if (s->cancel.load()) { set_error("render cancelled"); return MTSB_ERR_CANCELLED; }
+        int rc = enqueue_bounce(P, p, rcst, bounce, n_upper);
+        if (rc) return rc;
+        last = bounce++;
+        // the poll ring holds MTSB_POLL_RING counts: never run further ahead than that
+        while (bounce - confirmed >= MTSB_POLL_RING - 1) {
+            MTSB_CUDA(cudaEventSynchronize(P.ev[(size_t) ((confirmed + 1) % MTSB_POLL_RING)]));
+            known.push_back(pb.h_poll[(confirmed + 1) % MTSB_POLL_RING]); ++confirmed;
+        }
+        while (confirmed < bounce) {
+            const cudaError_t q = cudaEventQuery(P.ev[(size_t) ((confirmed + 1) % MTSB_POLL_RING)]);
+            if (q == cudaErrorNotReady) break;
+            if (q != cudaSuccess) return cuda_fail(q, "wavefront bounce", __FILE__, __LINE__);
+            known.push_back(pb.h_poll[(confirmed + 1) % MTSB_POLL_RING]); ++confirmed;
+        }
+        n_upper = std::min(n_upper, known.back());       // queue sizes never grow from one bounce to the next
+        if (known.back() == 0) drained = true;
+    }
+    P.timer->begin(ST_SPLAT);
+    k_pass_end<<<1, 1, 0, P.st>>>(pb, last);
     {
         // enough CTAs for ~8 per SM: split the samples of a tile over gridDim.y CTAs when the pass has few tiles
-        const uint32_t rounds = (L.pass.ps.spp_pass + MTSB_SPLAT_CHUNK - 1) / MTSB_SPLAT_CHUNK;
-        const uint32_t want = (uint32_t) device_sm_count() * 8u;
-        uint32_t split = (want + L.pass.ps.n_tiles - 1) / L.pass.ps.n_tiles;
+        const uint32_t rounds = (p.ps.spp_pass + MTSB_SPLAT_CHUNK - 1) / MTSB_SPLAT_CHUNK;
+        const uint32_t want = (uint32_t) P.sm_count * 8u;
+        uint32_t split = (want + p.ps.n_tiles - 1) / p.ps.n_tiles;
         split = std::max(1u, std::min(std::min(split, rounds), 64u));
         // filters reaching at most five pixels per axis take the precomputed-weight gather (floor(r + 0.5) <= 2)
         static const bool force_generic = getenv("MTSB_SPLAT_GENERIC") != nullptr;
         if (s->v.filter_radius < 2.5f && s->v.film_border <= 2 && !force_generic)
-            k_splat5<<<dim3(L.pass.ps.n_tiles, split), 256, MTSB_SPLAT5_SMEM, L.st>>>(s->v, *L.pb, L.pass.ps, s->d_film_bad);
+            k_splat5<<<dim3(p.ps.n_tiles, split), 256, MTSB_SPLAT5_SMEM, P.st>>>(s->v, pb, p.ps, s->d_film_bad);
         else
-            k_splat<<<dim3(L.pass.ps.n_tiles, split), 256, splat_smem, L.st>>>(s->v, *L.pb, L.pass.ps, s->d_film_bad);
+            k_splat<<<dim3(p.ps.n_tiles, split), 256, splat_smem, P.st>>>(s->v, pb, p.ps, s->d_film_bad);
     }
     s->launches += 2;
-    L.timer->end();
-    L.busy = false;
-}
-
-static int lane_count() {
-    const char *e = getenv("MTSB_LANES");
-    int n = e ? atoi(e) : 1;
-    return std::max(1, std::min(n, MTSB_MAX_LANES));
+    P.timer->end();
+    return MTSB_OK;
 }
 
 }  // namespace mtsb
@@ -972,38 +1065,41 @@ extern "C" int mtsb_render(mtsb_scene_t scene, const MtsbRenderParams *params, M
         MTSB_CUDA(cudaMemsetAsync(s->d_film_bad, 0, sizeof(unsigned long long), s->stream));
     }
     if (stats) memset(stats, 0, sizeof(*stats));
+    if (stats) stats->n_devices = 1;
     if (tiles.empty()) { MTSB_CUDA(cudaStreamSynchronize(s->stream)); return MTSB_OK; }
 
-    // pass shape: about 16M path slots in flight over all lanes
-    const uint64_t px_per_tile = MTSB_TILE * MTSB_TILE;
-    const uint64_t total_slots = (uint64_t) tiles.size() * px_per_tile * (uint64_t) spp;
-    int n_lanes = lane_count();
-    if (total_slots <= (2ull << 20)) n_lanes = 1;                       // small jobs: one pass, nothing to overlap
-    // path slots in flight over all lanes: as many as fit in a fifth of the free device memory, at most 64M
+    // pass shape: as many path slots as fit in a fifth of the free device memory, at most 64M
     // (a pass pays a fixed price for its thin late bounces, so fewer and larger passes are faster)
+    const uint64_t px_per_tile = MTSB_TILE * MTSB_TILE;
     uint64_t slots_m = 64;
     {
         size_t free_b = 0, total_b = 0;
         if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
             uint64_t have = 0;
-            for (int l = 0; l < MTSB_MAX_LANES; ++l) if (s->paths[l]) have += (uint64_t) s->paths[l]->capacity * 216ull;
-            const uint64_t fit = ((uint64_t) free_b + have) / 5ull / 216ull >> 20;
+            for (int l = 0; l < MTSB_MAX_LANES; ++l) if (s->paths[l]) have += (uint64_t) s->paths[l]->capacity * MTSB_SLOT_BYTES;
+            const uint64_t fit = ((uint64_t) free_b + have) / 5ull / MTSB_SLOT_BYTES >> 20;
             slots_m = std::max<uint64_t>(1, std::min<uint64_t>(slots_m, fit));
         }
         const char *tenv = getenv("MTSB_SLOTS_M");
-        if (tenv && atoi(tenv) > 0) slots_m = (uint64_t) atoi(tenv);
+        if (tenv && atoi(tenv) > 0) slots_m = (uint64_t) std::min(atoi(tenv), 2048);
     }
-    const uint64_t target = (slots_m << 20) / (uint64_t) n_lanes;
-    uint32_t spp_pass = params->spp_per_pass > 0 ? (uint32_t) params->spp_per_pass
-                                                 : (uint32_t) std::max<uint64_t>(1, std::min<uint64_t>((uint64_t) spp, target / (tiles.size() * px_per_tile)));
-    spp_pass = std::min<uint32_t>(spp_pass, (uint32_t) spp);
-    uint32_t tiles_per_pass = (uint32_t) std::max<uint64_t>(1, std::min<uint64_t>(tiles.size(), target / (px_per_tile * spp_pass)));
-    const uint32_t capacity = (uint32_t) (tiles_per_pass * px_per_tile * spp_pass);
+    const uint64_t target = slots_m << 20;
+    // the samples of a pixel are split into equal passes (the tail pass is as wide as the others, so its thin late
+    // bounces are not paid for a sliver of work)
+    uint64_t spp_pass64 = params->spp_per_pass > 0 ? (uint64_t) params->spp_per_pass
+                                                  : std::max<uint64_t>(1, std::min<uint64_t>((uint64_t) spp, target / (tiles.size() * px_per_tile)));
+    spp_pass64 = std::min<uint64_t>(spp_pass64, (uint64_t) spp);
+    if (params->spp_per_pass <= 0) { const uint64_t np = ((uint64_t) spp + spp_pass64 - 1) / spp_pass64; spp_pass64 = ((uint64_t) spp + np - 1) / np; }
+    uint64_t tiles_per_pass = std::max<uint64_t>(1, std::min<uint64_t>(tiles.size(), target / (px_per_tile * spp_pass64)));
+    { const uint64_t np = (tiles.size() + tiles_per_pass - 1) / tiles_per_pass; tiles_per_pass = (tiles.size() + np - 1) / np; }
+    const uint64_t capacity64 = tiles_per_pass * px_per_tile * spp_pass64;
+    if (capacity64 >= (1ull << 32)) { set_error("mtsb_render: a pass of more than 2^32 path slots (spp_per_pass / MTSB_SLOTS_M too large)"); return MTSB_ERR_INVALID; }
+    const uint32_t spp_pass = (uint32_t) spp_pass64, capacity = (uint32_t) capacity64;
     std::vector<Pass> passes;
-    for (uint32_t t0 = 0; t0 < tiles.size(); t0 += tiles_per_pass)
+    for (uint32_t t0 = 0; t0 < tiles.size(); t0 += (uint32_t) tiles_per_pass)
         for (uint32_t s0 = 0; s0 < (uint32_t) spp; s0 += spp_pass) {
             Pass p;
-            p.ps.tile_first = t0; p.ps.n_tiles = std::min<uint32_t>(tiles_per_pass, (uint32_t) tiles.size() - t0);
+            p.ps.tile_first = t0; p.ps.n_tiles = std::min<uint32_t>((uint32_t) tiles_per_pass, (uint32_t) tiles.size() - t0);
             p.ps.spp_pass = std::min<uint32_t>(spp_pass, (uint32_t) spp - s0);
             p.ps.s_first = (uint32_t) params->spp_offset + s0; p.ps.tiles_x = tiles_x; p.ps.seed = params->seed;
             p.n_slots = (uint32_t) (p.ps.n_tiles * px_per_tile * p.ps.spp_pass);
@@ -1015,7 +1111,6 @@ extern "C" int mtsb_render(mtsb_scene_t scene, const MtsbRenderParams *params, M
             p.n_valid = (uint32_t) (px_valid * p.ps.spp_pass);
             passes.push_back(p);
         }
-    n_lanes = std::min<int>(n_lanes, (int) passes.size());
 
     RenderConst rcst; rcst.max_depth = v.integrator.max_depth; rcst.rr_depth = v.integrator.rr_depth;
     rcst.strict_normals = v.integrator.strict_normals; rcst.hide_emitters = v.integrator.hide_emitters;
@@ -1023,72 +1118,40 @@ extern "C" int mtsb_render(mtsb_scene_t scene, const MtsbRenderParams *params, M
     MTSB_CUDA(cudaFuncSetAttribute(k_splat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) splat_smem));
     MTSB_CUDA(cudaFuncSetAttribute(k_splat5, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) MTSB_SPLAT5_SMEM));
 
+    int status = ensure_buffers(s, 0, capacity, (uint32_t) tiles.size());
+    if (status) return status;
+    Pipeline P;
+    P.s = s; P.st = s->lane_stream[0]; P.pb = s->paths[0]; P.sm_count = sm_count;
+    P.qmc = v.sampler_type != MTSB_SAMPLER_INDEPENDENT;
+    for (int32_t m : s->h_shape_material) P.queue_mask |= 1u << queue_of_material(s->h_materials.data(), m);
+    P.timer = new StageTimer(P.st);
+    P.ev.resize(MTSB_POLL_RING);
+    for (auto &e : P.ev) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
     cudaEvent_t ev0, ev1; cudaEventCreate(&ev0); cudaEventCreate(&ev1);
     cudaEventRecord(ev0, s->stream);
-    std::vector<Lane> lanes((size_t) n_lanes);
-    uint32_t queue_mask = 0;
-    for (int32_t m : s->h_shape_material) queue_mask |= 1u << queue_of_material(s->h_materials.data(), m);
-    int status = MTSB_OK;
-    for (int l = 0; l < n_lanes && status == MTSB_OK; ++l) {
-        Lane &L = lanes[(size_t) l];
-        status = ensure_buffers(s, l, capacity, (uint32_t) tiles.size());
-        if (status) break;
-        L.st = s->lane_stream[l]; L.pb = s->paths[l]; L.queue_mask = queue_mask;
-        L.timer = new StageTimer(L.st);
-        cudaEventCreateWithFlags(&L.ev, cudaEventDisableTiming);
-        cudaStreamWaitEvent(L.st, ev0, 0);                               // after the film clear
-        cudaMemcpyAsync(L.pb->tiles, tiles.data(), tiles.size() * sizeof(int), cudaMemcpyHostToDevice, L.st);
-        cudaMemsetAsync(L.pb->ctr, 0, sizeof(Counters), L.st);
-    }
+    cudaStreamWaitEvent(P.st, ev0, 0);                               // after the film clear
+    cudaMemcpyAsync(P.pb->tiles, tiles.data(), tiles.size() * sizeof(int), cudaMemcpyHostToDevice, P.st);
+    cudaMemsetAsync(P.pb->ctr, 0, sizeof(Counters), P.st);
 
-    size_t next_pass = 0;
     uint32_t n_passes = 0;
-    while (status == MTSB_OK) {
-        bool any_busy = false, progressed = false;
-        for (Lane &L : lanes) {
-            if (!L.busy) {
-                if (next_pass < passes.size()) {
-                    status = lane_start(s, L, passes[next_pass++], rcst, sm_count);
-                    ++n_passes; progressed = true; any_busy = true;
-                    if (status) break;
-                }
-                continue;
-            }
-            any_busy = true;
-            cudaError_t q = cudaEventQuery(L.ev);
-            if (q == cudaErrorNotReady) continue;
-            if (q != cudaSuccess) { status = cuda_fail(q, "wavefront bounce", __FILE__, __LINE__); break; }
-            progressed = true;
-            if (s->cancel.load()) { status = MTSB_ERR_CANCELLED; set_error("render cancelled"); break; }
-            L.n_cur = L.pb->h_ctr->n_rays[1 - L.cur];
-            L.cur ^= 1;
-            if (L.n_cur == 0) lane_finish(s, L, splat_smem);
-            else status = lane_bounce(s, L, rcst, sm_count);
-            if (status) break;
-        }
-        if (status != MTSB_OK || !any_busy) break;
-        if (!progressed) {
-            // nothing ready: block on one busy lane instead of spinning
-            for (Lane &L : lanes) if (L.busy) { cudaEventSynchronize(L.ev); break; }
-        }
+    for (const Pass &p : passes) {
+        status = run_pass(P, p, rcst, splat_smem);
+        if (status) break;
+        ++n_passes;
     }
-    for (Lane &L : lanes) if (L.st) {
-        cudaError_t e = cudaStreamSynchronize(L.st);
-        if (e != cudaSuccess && status == MTSB_OK) status = cuda_fail(e, "mtsb_render", __FILE__, __LINE__);
-    }
-    cudaEventRecord(ev1, s->stream);
-    cudaError_t e = cudaStreamSynchronize(s->stream);
+    cudaError_t e = cudaStreamSynchronize(P.st);
+    if (e != cudaSuccess && status == MTSB_OK) status = cuda_fail(e, "mtsb_render", __FILE__, __LINE__);
+    cudaEventRecord(ev1, P.st);
+    cudaStreamWaitEvent(s->stream, ev1, 0);                          // later work on the scene's stream (develop, reduce) sees the film
+    e = cudaStreamSynchronize(P.st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
     if (e != cudaSuccess && status == MTSB_OK) status = cuda_fail(e, "mtsb_render", __FILE__, __LINE__);
     if (status == MTSB_OK) { e = cudaGetLastError(); if (e != cudaSuccess) status = cuda_fail(e, "mtsb_render kernels", __FILE__, __LINE__); }
     if (stats && status == MTSB_OK) {
-        Counters hc; memset(&hc, 0, sizeof(hc));
+        Counters hc;
+        cudaMemcpy(&hc, P.pb->ctr, sizeof(hc), cudaMemcpyDeviceToHost);
         float st[ST_N] = {0, 0, 0, 0, 0};
-        for (Lane &L : lanes) {
-            Counters c;
-            cudaMemcpy(&c, L.pb->ctr, sizeof(c), cudaMemcpyDeviceToHost);
-            hc.closest += c.closest; hc.shadow += c.shadow; hc.shade += c.shade; hc.path_len += c.path_len;
-            L.timer->collect(st, ST_N);
-        }
+        P.timer->collect(st, ST_N);
         unsigned long long bad = 0;
         cudaMemcpy(&bad, s->d_film_bad, sizeof(bad), cudaMemcpyDeviceToHost);
         float total = 0; cudaEventElapsedTime(&total, ev0, ev1);
@@ -1101,11 +1164,13 @@ extern "C" int mtsb_render(mtsb_scene_t scene, const MtsbRenderParams *params, M
         stats->samples = px_in * (uint64_t) spp;
         stats->closest_rays = hc.closest; stats->shadow_rays = hc.shadow; stats->shade_events = hc.shade;
         stats->path_length_sum = hc.path_len; stats->kernel_launches = s->launches - launches0; stats->bad_samples = bad;
-        // stage times are summed over lanes; lanes overlap, so the sum can exceed ms_total
         stats->ms_total = total; stats->ms_raygen = st[ST_RAYGEN]; stats->ms_trace_closest = st[ST_CLOSEST]; stats->ms_shade = st[ST_SHADE];
         stats->ms_trace_any = st[ST_ANY]; stats->ms_splat = st[ST_SPLAT]; stats->n_passes = n_passes;
+        for (int b = 0; b < MTSB_BOUNCE_STATS; ++b) { stats->closest_rays_bounce[b] = hc.rays_bounce[b]; stats->shadow_rays_bounce[b] = hc.shadow_bounce[b]; }
+        stats->closest_launches = (uint32_t) hc.launches_closest; stats->any_launches = (uint32_t) hc.launches_any;
     }
-    for (Lane &L : lanes) { delete L.timer; if (L.ev) cudaEventDestroy(L.ev); }
+    delete P.timer;
+    for (auto &ev : P.ev) cudaEventDestroy(ev);
     cudaEventDestroy(ev0); cudaEventDestroy(ev1);
     return status;
 }

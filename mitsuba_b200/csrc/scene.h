@@ -57,6 +57,7 @@ template <class T> int dev_upload(Scene *s, const T **p, const T *host, size_t c
 
 int build_bvh(Scene *s, const float *d_positions, const uint32_t *d_indices, uint64_t n_tris);
 int render_free(Scene *s);
+int pack_shading_records(Scene *s, uint64_t n_tris);   // render.cu: per-triangle shading records + queue bytes
 
 inline unsigned grid_for(size_t n, unsigned block) { return (unsigned) ((n + block - 1) / block); }
 

@@ -15,6 +15,8 @@ struct SceneView {
     float box_lo[3], box_hi[3];             // enlarged scene box (gkdtree.h:1215-1220)
     // geometry, indexed by global primitive id / global vertex id
     const float *positions, *normals, *texcoords; const uint32_t *indices; const uint32_t *tri_shape;
+    // packed per-triangle shading records (8 x 16 B each, shading.h) and the shading queue every triangle feeds (1 B each)
+    const U4 *shade_tris; const uint8_t *tri_queue;
     const MtsbShape *shapes; const MtsbMaterial *materials; const MtsbEmitter *emitters;
     uint32_t n_shapes, n_materials, n_emitters;
     // emitter sampling tables (DiscreteDistribution, include/mitsuba/core/pmf.h)

@@ -36,27 +36,36 @@ struct Its {
     V3 dpdu, dpdv;          // position partials (skdtree.h:373-380): uv tangents where the mesh has texture coordinates
 };
 
+// Per-triangle shading record, 128 B = one L2 line (built once at scene creation by k_pack_tris, render.cu): everything
+// fillIntersectionRecord reads for a hit sits behind ONE index, instead of the chain prim -> tri_shape -> shape ->
+// indices -> three vertices -> three normals of the flat arrays.
+//   r0 = p0.xyz, shape   r1 = p1.xyz, flags (1: vertex normals, 2: texture coordinates)   r2 = p2.xyz, -
+//   r3 = n0.xyz, uv0.x   r4 = n1.xyz, uv0.y   r5 = n2.xyz, uv1.x   r6 = uv1.y, uv2.x, uv2.y, -   (r3.. only where flagged)
+#define MTSB_SHADE_TRI_U4 8
 MTSB_HD void fill_intersection(const SceneView &sc, V3 ray_d, uint32_t prim, float hu, float hv, Its &its) {
-    const uint32_t s = sc.tri_shape[prim];
-    const MtsbShape &sh = sc.shapes[s];
-    const uint32_t *ix = sc.indices + 3 * (size_t) prim;
-    const uint32_t i0 = ix[0], i1 = ix[1], i2 = ix[2];
+    const U4 *rec = sc.shade_tris + (size_t) MTSB_SHADE_TRI_U4 * prim;
+    const U4 r0 = ld16(rec), r1 = ld16(rec + 1), r2 = ld16(rec + 2);
+    const uint32_t s = r0.w, flags = r1.w;
     const V3 b(1 - hu - hv, hu, hv);
-    const V3 p0 = ld3(sc.positions + 3 * (size_t) i0), p1 = ld3(sc.positions + 3 * (size_t) i1), p2 = ld3(sc.positions + 3 * (size_t) i2);
+    const V3 p0(u2f(r0.x), u2f(r0.y), u2f(r0.z)), p1(u2f(r1.x), u2f(r1.y), u2f(r1.z)), p2(u2f(r2.x), u2f(r2.y), u2f(r2.z));
     its.p = p0 * b.x + p1 * b.y + p2 * b.z;
     V3 side1 = p1 - p0, side2 = p2 - p0;
     V3 faceNormal = cross(side1, side2);
     float len = length(faceNormal);
     if (!isZero(faceNormal)) faceNormal = faceNormal / len;
+    U4 r3, r4, r5;
+    r3.x = r3.y = r3.z = r3.w = 0; r4 = r3; r5 = r3;
+    if (flags & 3u) { r3 = ld16(rec + 3); r4 = ld16(rec + 4); r5 = ld16(rec + 5); }
     V3 shN;
-    if (sh.has_normals) {
-        const V3 n0 = ld3(sc.normals + 3 * (size_t) i0), n1 = ld3(sc.normals + 3 * (size_t) i1), n2 = ld3(sc.normals + 3 * (size_t) i2);
+    if (flags & 1u) {
+        const V3 n0(u2f(r3.x), u2f(r3.y), u2f(r3.z)), n1(u2f(r4.x), u2f(r4.y), u2f(r4.z)), n2(u2f(r5.x), u2f(r5.y), u2f(r5.z));
         shN = normalize(n0 * b.x + n1 * b.y + n2 * b.z);
         if (dot(faceNormal, shN) < 0) faceNormal = -faceNormal;
     } else shN = faceNormal;
     its.geoN = faceNormal;
-    if (sh.has_texcoords && sc.texcoords) {
-        const float *t0 = sc.texcoords + 2 * (size_t) i0, *t1 = sc.texcoords + 2 * (size_t) i1, *t2 = sc.texcoords + 2 * (size_t) i2;
+    if (flags & 2u) {
+        const U4 r6 = ld16(rec + 6);
+        const float t0[2] = {u2f(r3.w), u2f(r4.w)}, t1[2] = {u2f(r5.w), u2f(r6.x)}, t2[2] = {u2f(r6.y), u2f(r6.z)};
         its.uv.x = t0[0] * b.x + t1[0] * b.y + t2[0] * b.z; its.uv.y = t0[1] * b.x + t1[1] * b.y + t2[1] * b.z;
         // TriMesh::computeUVTangents (trimesh.cpp:683-735): this fork's TriMesh::configure always builds the tangents of a
         // mesh that has texture coordinates (trimesh.cpp:383-385), and fillIntersectionRecord then takes dpdu / dpdv from them
@@ -131,6 +140,14 @@ MTSB_HD V3 environment_eval(const SceneView &sc, V3 d) {
     const MtsbEmitter &e = sc.emitters[sc.env_emitter];
     if (e.type == MTSB_EMITTER_ENVMAP) { const EnvmapView &ev = *sc.envmap; return envmap_eval(ev, d); }
     return ld3(e.radiance);                                                  // constant.cpp:242-244
+}
+
+// The same for a camera ray, which carries differentials: EnvironmentMap::evalEnvironment filters the lookup through
+// MIPMap::eval (envmap.cpp:393-407); rxd / ryd are the directions of the ray's x / y offset rays.
+MTSB_HD V3 environment_eval_filtered(const SceneView &sc, V3 d, V3 rxd, V3 ryd) {
+    const MtsbEmitter &e = sc.emitters[sc.env_emitter];
+    if (e.type == MTSB_EMITTER_ENVMAP) { const EnvmapView &ev = *sc.envmap; return envmap_eval_filtered(ev, d, rxd, ryd); }
+    return ld3(e.radiance);
 }
 
 MTSB_HD V3 emitter_sample_direct(const SceneView &sc, int ei, DRec &dRec, P2 u) {

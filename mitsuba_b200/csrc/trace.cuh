@@ -21,7 +21,9 @@ namespace mtsb {
 struct SmemStack {
     uint2 *sm;                       // this thread's column: sm[i * MTSB_TRACE_BLOCK]
     uint2 *loc;                      // overflow array (kept outside the struct so the scalar state stays in registers)
+    const uint8_t *perm_tab;         // shared-memory table [8][256]: perm_byte(mask, octant)
     int sp;
+    __device__ __forceinline__ uint32_t perm(uint32_t m, uint32_t o) const { return perm_tab[o * 256u + m]; }
     __device__ __forceinline__ void reset() { sp = 0; }
     __device__ __forceinline__ bool empty() const { return sp == 0; }
     __device__ __forceinline__ void push(uint32_t x, uint32_t y) {
@@ -50,12 +52,16 @@ struct TraceArgs {
 template <bool ANY, class Epilogue>
 __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_MIN_CTAS) k_trace(TraceArgs a, Epilogue ep) {
     __shared__ uint2 s_stack[MTSB_SM_STACK * MTSB_TRACE_BLOCK];
+    __shared__ uint8_t s_perm[8 * 256];
+    for (uint32_t i = threadIdx.x; i < 8u * 256u; i += MTSB_TRACE_BLOCK) s_perm[i] = (uint8_t) perm_byte(i & 255u, i >> 8);
+    __syncthreads();
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t n = a.d_count ? min(*a.d_count, a.n_max) : a.n_max;
     uint2 overflow[MTSB_LOCAL_STACK];
     Traversal<SmemStack> tr;
     tr.stack.sm = s_stack + threadIdx.x;
     tr.stack.loc = overflow;
+    tr.stack.perm_tab = s_perm;
     tr.stack.sp = 0;
     tr.bias = a.prmt_bias;
     bool active = false;
@@ -102,10 +108,10 @@ __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_MIN_CTAS) k_trace
             if (active && tr.wants_node()) tr.visit_node(a.nodes);
             __syncwarp();
             bool done = false;
-            if (active && tr.tg != 0) done = tr.template test_triangle<ANY>(a.tris);
+            if (active && tr.tw != 0) done = tr.template test_triangle<ANY>(a.tris);
             __syncwarp();
             if (active && (done || tr.finished())) {
-                ep(ray_idx, ray, tr.hit);
+                ep(ray_idx, ray, tr.result(a.tris));
                 active = false;
             }
             live = __ballot_sync(0xFFFFFFFFu, active);

@@ -92,6 +92,26 @@ int mtsbh_render(mtsbh_scene_t s, int spp, float *rgb, MtsbStats *stats) {
     return rc;
 }
 
+int mtsbh_render_multi(mtsbh_scene_t s, int spp, int n_devices, float *rgb, MtsbStats *stats) {
+    if (!s || !rgb) { g_error = "mtsbh_render_multi: NULL argument"; return MTSB_ERR_INVALID; }
+    if (n_devices <= 0) n_devices = mtsb_device_count();
+    if (n_devices <= 0) { g_error = "no CUDA device present (this library has no CPU fallback)"; return MTSB_ERR_NO_DEVICE; }
+    if (n_devices == 1) return mtsbh_render(s, spp, rgb, stats);
+    mtsb_multi_t multi = nullptr;
+    int rc = mtsb_multi_create(&s->flat.desc, n_devices, nullptr, &multi);
+    if (rc) { g_error = mtsb_last_error(); return rc; }
+    MtsbRenderParams rp;
+    std::memset(&rp, 0, sizeof(rp));
+    rp.spp = spp;
+    rp.seed = (uint64_t) s->flat.seed;
+    MtsbStats local;
+    rc = mtsb_multi_render(multi, &rp, stats ? stats : &local);
+    if (!rc) rc = mtsb_film_develop(mtsb_multi_scene(multi, 0), rgb);
+    if (rc) g_error = mtsb_last_error();
+    mtsb_multi_destroy(multi);
+    return rc;
+}
+
 int mtsbh_write_pfm(const char *path, const float *rgb, int width, int height) {
     if (!path || !rgb || width <= 0 || height <= 0) { g_error = "mtsbh_write_pfm: bad argument"; return MTSB_ERR_INVALID; }
     FILE *f = fopen(path, "wb");

@@ -1,6 +1,6 @@
 // mtsb200 -- command line front end, the subset of the reference's `mitsuba` binary that drives the
 // path hot path (src/mitsuba/mitsuba.cpp:80-140 usage, 176-260 option parsing, 330-372 job loop):
-//     mtsb200 [-D name=value]... [-o out.pfm] [-s spp] [-q] scene.xml [scene2.xml ...]
+//     mtsb200 [-D name=value]... [-o out.pfm] [-n spp] [-g gpus] [-q] scene.xml [scene2.xml ...]
 // Options of the reference that configure its CPU scheduler or network (-p, -c, -s servers, -j, -r, -b,
 // -x, -z) have no meaning here; -p is accepted and ignored so that existing command lines keep working.
 #include <cstdio>
@@ -18,6 +18,8 @@ static void usage() {
            "   -D key=val  Define a constant, which can be referenced as \"$key\" in the scene\n"
            "   -o fname    Write the output image (PFM) to the file denoted by \"fname\"\n"
            "   -n spp      Override the sampler's sampleCount\n"
+           "   -g count    Render every frame on this many GPUs of the node (0 = all; default 1): the blocks of the\n"
+           "               frame are distributed over the GPUs and merged with one NCCL reduce\n"
            "   -p count    Ignored (CPU core count of the reference)\n"
            "   -q          Quiet mode - do not print any log messages to stdout\n");
 }
@@ -26,7 +28,7 @@ int main(int argc, char **argv) {
     std::vector<std::string> defs, scenes;
     std::string out;
     bool quiet = false;
-    int spp = 0;
+    int spp = 0, gpus = 1;
     for (int i = 1; i < argc; ++i) {
         std::string a = argv[i];
         auto need = [&](const char *opt) -> const char * {
@@ -39,6 +41,7 @@ int main(int argc, char **argv) {
         else if (a.size() > 2 && a.compare(0, 2, "-D") == 0) defs.push_back(a.substr(2));
         else if (a == "-o") out = need("-o");
         else if (a == "-n") spp = atoi(need("-n"));
+        else if (a == "-g") gpus = atoi(need("-g"));
         else if (a == "-p") need("-p");
         else if (!a.empty() && a[0] == '-') { fprintf(stderr, "Unknown option %s\n", a.c_str()); usage(); return -1; }
         else scenes.push_back(a);
@@ -57,7 +60,7 @@ int main(int argc, char **argv) {
         const int w = d->sensor.crop_width, h = d->sensor.crop_height;
         std::vector<float> rgb((size_t) w * h * 3);
         MtsbStats st;
-        if (mtsbh_render(scene, spp, rgb.data(), &st)) { fprintf(stderr, "%s\n", mtsbh_last_error()); mtsbh_scene_free(scene); return -1; }
+        if (gpus == 1 ? mtsbh_render(scene, spp, rgb.data(), &st) : mtsbh_render_multi(scene, spp, gpus, rgb.data(), &st)) { fprintf(stderr, "%s\n", mtsbh_last_error()); mtsbh_scene_free(scene); return -1; }
         // mitsuba.cpp:352-360: the default destination is the scene file name with the film's extension
         std::string dest = out;
         if (dest.empty()) {

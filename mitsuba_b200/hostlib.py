@@ -16,7 +16,7 @@ CLI_PATH = os.path.join(_HERE, "mtsb200")
 
 SYMBOLS = [
     "mtsbh_last_error", "mtsbh_load_file", "mtsbh_load_string", "mtsbh_scene_free", "mtsbh_scene_desc", "mtsbh_scene_seed",
-    "mtsbh_warning_count", "mtsbh_warning", "mtsbh_render", "mtsbh_write_pfm",
+    "mtsbh_warning_count", "mtsbh_warning", "mtsbh_render", "mtsbh_render_multi", "mtsbh_write_pfm",
 ]
 
 _lib = None
@@ -40,6 +40,7 @@ def lib():
         L.mtsbh_warning.argtypes = [C.c_void_p, C.c_int]
         L.mtsbh_warning.restype = C.c_char_p
         L.mtsbh_render.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.POINTER(abi.Stats)]
+        L.mtsbh_render_multi.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.POINTER(abi.Stats)]
         L.mtsbh_write_pfm.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
         _lib = L
     return _lib
@@ -120,12 +121,16 @@ class HostScene:
         d = self.desc
         return [d.emitters[i] for i in range(d.n_emitters)]
 
-    def render(self, spp=0):
-        """RenderJob: device scene + mtsb_render + develop.  Returns (rgb[h,w,3], Stats)."""
+    def render(self, spp=0, gpus=1):
+        """RenderJob: device scene + mtsb_render + develop.  Returns (rgb[h,w,3], Stats).
+        gpus != 1: the frame's blocks are distributed over that many GPUs of the node (0 = all)."""
         s = self.desc.sensor
         rgb = np.zeros((s.crop_height, s.crop_width, 3), np.float32)
         st = abi.Stats()
-        rc = lib().mtsbh_render(self.h, int(spp), rgb.ctypes.data_as(C.c_void_p), C.byref(st))
+        if gpus == 1:
+            rc = lib().mtsbh_render(self.h, int(spp), rgb.ctypes.data_as(C.c_void_p), C.byref(st))
+        else:
+            rc = lib().mtsbh_render_multi(self.h, int(spp), int(gpus), rgb.ctypes.data_as(C.c_void_p), C.byref(st))
         if rc:
             raise MtsbError(rc, lib().mtsbh_last_error().decode(errors="replace"))
         return rgb, st

@@ -23,7 +23,8 @@ SYMBOLS = [
     "mtsb_scene_destroy", "mtsb_trace", "mtsb_trace_device", "mtsb_bsdf_query", "mtsb_emitter_sample",
     "mtsb_fill_intersection", "mtsb_sensor_rays", "mtsb_film_clear", "mtsb_film_put", "mtsb_film_size",
     "mtsb_film_download", "mtsb_film_device_ptr", "mtsb_film_develop", "mtsb_render", "mtsb_cancel",
-    "mtsb_gen_rays_device",
+    "mtsb_gen_rays_device", "mtsb_multi_create", "mtsb_multi_render", "mtsb_multi_cancel", "mtsb_multi_scene",
+    "mtsb_multi_device_count", "mtsb_multi_destroy",
 ]
 
 
@@ -70,6 +71,14 @@ def lib():
         L.mtsb_render.argtypes = [C.c_void_p, C.POINTER(abi.RenderParams), C.POINTER(abi.Stats)]
         L.mtsb_cancel.argtypes = [C.c_void_p]
         L.mtsb_gen_rays_device.argtypes = [C.c_void_p, C.c_int, C.c_size_t, C.c_uint64, C.c_void_p]
+        L.mtsb_multi_create.argtypes = [C.POINTER(abi.SceneDesc), C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_void_p)]
+        L.mtsb_multi_render.argtypes = [C.c_void_p, C.POINTER(abi.RenderParams), C.POINTER(abi.Stats)]
+        L.mtsb_multi_cancel.argtypes = [C.c_void_p]
+        L.mtsb_multi_scene.argtypes = [C.c_void_p, C.c_int]
+        L.mtsb_multi_scene.restype = C.c_void_p
+        L.mtsb_multi_device_count.argtypes = [C.c_void_p]
+        L.mtsb_multi_destroy.argtypes = [C.c_void_p]
+        L.mtsb_multi_destroy.restype = None
         _lib = L
     return _lib
 
@@ -202,3 +211,61 @@ class Scene:
 
     def cancel(self):
         _check(lib().mtsb_cancel(self.h))
+
+
+class _SceneView(Scene):
+    """Scene methods on a handle that somebody else owns (a replica inside a MultiScene)."""
+
+    def __init__(self, handle, owner):
+        self.h, self._owner = handle, owner
+
+    def close(self):
+        self.h = None
+
+
+class MultiScene:
+    """One scene replicated over several GPUs of this node inside the library (mtsb_multi_t): one frame's tiles are
+    interleaved over the devices and the films are merged by one NCCL reduce onto the first device."""
+
+    def __init__(self, builder_or_desc, n_devices, device_ids=None):
+        L = lib()
+        self._desc, self._keep = builder_or_desc.desc() if hasattr(builder_or_desc, "desc") else builder_or_desc
+        ids = (C.c_int * n_devices)(*device_ids) if device_ids is not None else None
+        h = C.c_void_p()
+        _check(L.mtsb_multi_create(C.byref(self._desc), int(n_devices), ids, C.byref(h)))
+        self.h = h
+
+    def device_count(self):
+        return lib().mtsb_multi_device_count(self.h)
+
+    def scene(self, i=0):
+        """A non-owning Scene view of the replica on the i-th device (i = 0 holds the merged film)."""
+        hh = lib().mtsb_multi_scene(self.h, int(i))
+        if not hh:
+            raise MtsbError(abi.ERR_INVALID, "no such device")
+        return _SceneView(C.c_void_p(hh), self)
+
+    def render(self, spp=0, seed=1, spp_offset=0, spp_per_pass=0, keep_film=False):
+        p = abi.RenderParams()
+        p.spp, p.spp_offset, p.seed, p.spp_per_pass = int(spp), int(spp_offset), int(seed), int(spp_per_pass)
+        p.flags = abi.RENDER_KEEP_FILM if keep_film else 0
+        st = abi.Stats()
+        _check(lib().mtsb_multi_render(self.h, C.byref(p), C.byref(st)))
+        return st
+
+    def film_develop(self):
+        return self.scene(0).film_develop()
+
+    def cancel(self):
+        _check(lib().mtsb_multi_cancel(self.h))
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().mtsb_multi_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

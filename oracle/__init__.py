@@ -24,6 +24,55 @@ def build(ref=True):
     subprocess.check_call(["make", "-C", _HERE, "all"] + (["ref"] if ref else []), stdout=subprocess.DEVNULL)
 
 
+def _host_cpu():
+    """(model name, has AVX-512F, has AVX2+FMA) of the machine this process runs on."""
+    model, flags = "unknown", set()
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name") and model == "unknown":
+                model = line.split(":", 1)[1].strip()
+            elif line.startswith("flags"):
+                flags = set(line.split(":", 1)[1].split())
+                break
+    except OSError:
+        pass
+    return model, "avx512f" in flags and "avx512vl" in flags and "avx512bw" in flags and "avx512dq" in flags, "avx2" in flags and "fma" in flags
+
+
+_fast_flags = None
+
+
+def use_timed_build():
+    """Switch this process to the TIMED builds (bench.py's CPU legs only; parity always uses the strict build):
+    liboracle_fast.so compiled on this machine with the reference's release flags at -march=native, and the
+    prebuilt _ref/libmtsref_fast_{v3,v4}.so this host can run.  Must be called before the first lib() / ref().
+    Returns a description of the flags for the bench line."""
+    global _LIB, _REF, _fast_flags
+    if _fast_flags is not None:
+        return _fast_flags
+    if _lib is not None or _ref is not None:
+        raise RuntimeError("oracle.use_timed_build() must run before the strict libraries are loaded")
+    model, v4, v3 = _host_cpu()
+    stamp = os.path.join(_HERE, "liboracle_fast.host")
+    fast = os.path.join(_HERE, "liboracle_fast.so")
+    same_host = os.path.exists(stamp) and os.path.exists(fast) and open(stamp).read() == model + ("/v4" if v4 else "/v3" if v3 else "/v2")
+    subprocess.check_call(["make", "-C", _HERE] + ([] if same_host else ["-B"]) + ["fast"], stdout=subprocess.DEVNULL)
+    open(stamp, "w").write(model + ("/v4" if v4 else "/v3" if v3 else "/v2"))
+    _LIB = fast
+    out = {"oracle": open(os.path.join(_HERE, "liboracle_fast.flags")).read().strip(), "host_cpu": model}
+    for lvl, ok in (("v4", v4), ("v3", v3)):
+        cand = os.path.join(_HERE, "_ref", "libmtsref_fast_%s.so" % lvl)
+        if ok and os.path.exists(cand):
+            _REF = cand
+            out["reference_kdtree"] = open(cand[:-3] + ".flags").read().strip()
+            break
+    else:
+        if os.path.exists(_REF):
+            out["reference_kdtree"] = "-O2 -ffp-contract=off (strict build: no release build for this host)"
+    _fast_flags = out
+    return out
+
+
 class OrcStats(C.Structure):
     _fields_ = [("samples", C.c_uint64), ("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
                 ("shade_events", C.c_uint64), ("path_length_sum", C.c_uint64), ("bad_samples", C.c_uint64),

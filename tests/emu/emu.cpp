@@ -115,7 +115,7 @@ extern "C" uint64_t emu_trace(void *h, const RayIn *rays, size_t n, int mode, Hi
             tr.begin(rays[i], mint, maxt);
             if (mode == 1) { while (!tr.step<true>(nodes, tris)) {} }
             else { while (!tr.step<false>(nodes, tris)) {} }
-            out = tr.hit; steps += tr.steps; g_tri_tests += tr.tri_tests; g_sparse_steps += tr.sparse_steps;
+            out = tr.result(tris); steps += tr.steps; g_tri_tests += tr.tri_tests; g_sparse_steps += tr.sparse_steps;
         }
         hits[i] = out;
     }
@@ -333,7 +333,7 @@ extern "C" void emu_trace_profile(void *h, const RayIn *rays, size_t n, int mode
                     ++len;
                 }
                 bool done = false;
-                if (tr.tg != 0) done = mode == 1 ? tr.test_triangle<true>(tris) : tr.test_triangle<false>(tris);
+                if (tr.tw != 0) done = mode == 1 ? tr.test_triangle<true>(tris) : tr.test_triangle<false>(tris);
                 if (done || tr.finished()) break;
             }
         }
