@@ -235,6 +235,9 @@ def run_b200_arm(args):
     def step(seed):
         flush.zero_()                                   # L2 flush between timed iterations
         torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()                              # every rank starts the frame together (outside the timed spans)
+            torch.cuda.synchronize()
         st = scene.render(spp=total_spp, seed=seed, tile_index=rank, tile_count=world)
         ms = st.ms_total
         if world > 1:

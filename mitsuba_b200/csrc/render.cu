@@ -1133,12 +1133,19 @@ extern "C" int mtsb_render(mtsb_scene_t scene, const MtsbRenderParams *params, M
     cudaMemcpyAsync(P.pb->tiles, tiles.data(), tiles.size() * sizeof(int), cudaMemcpyHostToDevice, P.st);
     cudaMemsetAsync(P.pb->ctr, 0, sizeof(Counters), P.st);
 
+    // The host never runs more than two passes ahead of the device: enough queued work to keep the GPU busy across the
+    // pass boundary, little enough that mtsb_cancel (checked before every bounce is enqueued) takes effect within two passes.
     uint32_t n_passes = 0;
+    cudaEvent_t pass_done[2] = {nullptr, nullptr};
+    for (auto &e2 : pass_done) cudaEventCreateWithFlags(&e2, cudaEventDisableTiming);
     for (const Pass &p : passes) {
+        if (n_passes >= 2) cudaEventSynchronize(pass_done[n_passes & 1]);
         status = run_pass(P, p, rcst, splat_smem);
         if (status) break;
+        cudaEventRecord(pass_done[n_passes & 1], P.st);
         ++n_passes;
     }
+    for (auto &e2 : pass_done) cudaEventDestroy(e2);
     cudaError_t e = cudaStreamSynchronize(P.st);
     if (e != cudaSuccess && status == MTSB_OK) status = cuda_fail(e, "mtsb_render", __FILE__, __LINE__);
     cudaEventRecord(ev1, P.st);

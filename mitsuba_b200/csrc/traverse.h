@@ -287,6 +287,14 @@ template <class Stack> struct Traversal {
             const uint32_t w = leaves24 | counts;
             if (tw == 0) { tw = w; tbase = n1.y; } else { tw2 = w; tbase2 = n1.y; }
         }
+#if MTSB_DEVICE_CODE && defined(MTSB_PREFETCH_NODE)
+        if (ng_y > 0x00FFFFFFu) {          // the child this lane visits next: start its fetch behind the triangle phase
+            const uint32_t slot2 = ((uint32_t) bfind(ng_y) - 24u) ^ octinv;
+            const U4 *nx2 = nodes + 5 * (size_t) (ng_x + (uint32_t) popc(ng_y & ~(0xFFFFFFFFu << slot2) & 0xFFu));
+            asm volatile("prefetch.global.L1 [%0];" :: "l"(nx2));
+            asm volatile("prefetch.global.L1 [%0];" :: "l"(nx2 + 4));
+        }
+#endif
     }
 
     // (b) test one pending triangle; returns true when an any-hit query is satisfied

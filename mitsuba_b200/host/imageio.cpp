@@ -144,7 +144,7 @@ void readRGBE(std::istream &is, Image &img) {
 // linearised as FormatConverter does (fmtconv.cpp:151-157, 1092-1101: value/max, then the sRGB curve or pow in Float).
 inline uint32_t be32(const unsigned char *p) { return ((uint32_t) p[0] << 24) | ((uint32_t) p[1] << 16) | ((uint32_t) p[2] << 8) | p[3]; }
 
-void readPNG(std::istream &is, Image &img) {
+void readPNG(std::istream &is, Image &img, float gammaOverride) {
     std::vector<unsigned char> file((std::istreambuf_iterator<char>(is)), std::istreambuf_iterator<char>());
     static const unsigned char sig[8] = {0x89, 'P', 'N', 'G', 0x0D, 0x0A, 0x1A, 0x0A};
     if (file.size() < 8 || std::memcmp(file.data(), sig, 8) != 0) error("readPNG(): invalid signature!");
@@ -169,6 +169,7 @@ void readPNG(std::istream &is, Image &img) {
     // an sRGB chunk wins over gAMA (png_get_sRGB is asked first)
     for (size_t pos = 8; pos + 12 <= file.size(); pos += 12 + (size_t) be32(&file[pos]))
         if (std::memcmp(&file[pos + 4], "sRGB", 4) == 0) gamma = -1.0f;
+    if (gammaOverride != 0) gamma = gammaOverride;            // Bitmap::setGamma (textures/bitmap.cpp:251-252): -1 = sRGB, else the exponent
     if (img.width <= 0 || img.height <= 0) error("readPNG(): invalid image size!");
     if (interlace != 0) error("readPNG(): interlaced PNG files are not supported by the B200 host");
     const int channels = ctype == 0 ? 1 : ctype == 2 ? 3 : ctype == 3 ? 1 : ctype == 4 ? 2 : ctype == 6 ? 4 : 0;
@@ -235,17 +236,28 @@ void readPNG(std::istream &is, Image &img) {
 
 }  // namespace
 
-Image readImage(const std::string &path, const char *what) {
+// FormatConverter::undoGamma (fmtconv.cpp:1091-1100): what a `gamma` override does to an image whose file format is linear
+static float undoGamma(float value, float gamma) {
+    if (gamma == -1.0f) return value <= 0.04045f ? value * (float) (1.0 / 12.92) : std::pow((float) ((value + 0.055f) * (float) (1.0 / 1.055)), 2.4f);
+    return std::pow(value, gamma);
+}
+
+// gammaOverride: the `gamma` property of the bitmap texture / envmap (0 = keep the file's own gamma, -1 = sRGB, otherwise
+// the exponent that linearises the stored values; textures/bitmap.cpp:218,251-252, envmap.cpp:127-128)
+Image readImage(const std::string &path, const char *what, float gammaOverride) {
     std::ifstream is(path, std::ios::binary);
     if (!is) error(std::string(what) + " file \"" + path + "\" could not be found!");          // envmap.cpp:121-122, bitmap.cpp:196-197
     char magic[2] = {0, 0};
     is.read(magic, 2);
     is.seekg(0);
     Image img;
+    const bool linearFormat = (magic[0] == 'P' && (magic[1] == 'F' || magic[1] == 'f')) || (magic[0] == '#' && magic[1] == '?');
     if (magic[0] == 'P' && (magic[1] == 'F' || magic[1] == 'f')) readPFM(is, img);
     else if (magic[0] == '#' && magic[1] == '?') readRGBE(is, img);
-    else if ((unsigned char) magic[0] == 0x89 && magic[1] == 'P') readPNG(is, img);
+    else if ((unsigned char) magic[0] == 0x89 && magic[1] == 'P') readPNG(is, img, gammaOverride);
     else error("\"" + path + "\": unsupported image format -- the B200 host reads PFM, Radiance RGBE and PNG; OpenEXR and JPEG need libraries that are unavailable on this box");
+    if (linearFormat && gammaOverride != 0 && gammaOverride != 1.0f)      // PFM / RGBE carry gamma 1; an override re-interprets the values
+        for (float &v : img.rgb) v = undoGamma(v, gammaOverride);
     return img;
 }
 

@@ -51,7 +51,7 @@ struct Image {              // linear RGB, row 0 on top
     bool luminance = false; // the file held one channel (replicated into r, g, b)
 };
 // imageio.cpp: PFM, Radiance RGBE, PNG (8/16 bit, sRGB -> linear as Bitmap::convert does).  `what` names the consumer in error texts.
-Image readImage(const std::string &path, const char *what = "Environment map");
+Image readImage(const std::string &path, const char *what = "Environment map", float gammaOverride = 0.0f);
 
 // src/textures/{bitmap,checkerboard,gridtexture,scale}.cpp + Texture2D (src/librender/texture.cpp:81-96)
 class Texture : public ConfigurableObject {

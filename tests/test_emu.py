@@ -122,3 +122,30 @@ def test_sample_floats_are_in_unit_interval_and_uniform(emu):
         emu.emu_sample_block(1004, (i << 24) | 3, 1, 0, vp(vals[i]))
     assert vals.min() >= 0.0 and vals.max() < 1.0
     assert abs(vals.mean() - 0.5) < 0.01 and abs(np.corrcoef(vals[:, 0], vals[:, 1])[0, 1]) < 0.05
+
+
+def test_full_size_1m_scene_vs_reference_kdtree_records(emu, oracle_mod):
+    """BASELINE configs[1] geometry at full size (1 048 580 triangles): the emulated BVH build + traversal against the
+    committed records of the reference kd-tree (tests/golden/hits_big_1m.npz) on the 65 536-ray subsamples of the
+    coherent and the incoherent set.  (The CUDA path runs the same comparison, and all 4 M rays, in
+    tests/test_gpu_trace_big.py.)"""
+    import hashlib
+    from tests.golden.make_golden_big import sensor_rays_oracle
+    b = scenes.scene_1m()
+    g = util.load_golden("hits_big_1m.npz")
+    assert util.scene_digest(b).encode() == g["digest"].tobytes(), "the scene generator does not reproduce the golden scene on this host"
+    h, keep = build(emu, b)
+    nn, t6, e6 = C.c_uint32(), np.zeros(6, np.float32), np.zeros(6, np.float32)
+    emu.emu_info(h, C.byref(nn), vp(t6), vp(e6))
+    assert np.array_equal(t6, g["tight"])
+    sets = util.big_ray_sets(b, sensor_rays_oracle(b), t6[:3], t6[3:])
+    for sname, rays in sets.items():
+        assert hashlib.sha256(rays.tobytes()).hexdigest().encode() == g["sha_" + sname].tobytes(), sname
+        sub = rays[util.golden_subset(len(rays))]
+        hits, _ = trace(emu, h, sub, abi.TRACE_CLOSEST)
+        rep = util.hit_parity_report(hits, g["closest_" + sname])
+        assert rep["hard_mismatches"] == 0 and rep["excluded_fraction"] <= 2e-3 and rep["bit_exact_fraction"] >= 0.995, (sname, rep)
+        occl, _ = trace(emu, h, sub, abi.TRACE_ANY)
+        g_any = np.unpackbits(g["any_" + sname])[:len(sub)].astype(bool)
+        assert ((occl["prim"] != abi.NO_HIT) != g_any).sum() <= max(3, 2e-3 * len(sub))
+    emu.emu_destroy(h)

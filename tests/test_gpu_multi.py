@@ -64,7 +64,7 @@ def test_cancel_from_second_thread(gpu_lib):
     assert "err" in result and result["err"].code == abi.ERR_CANCELLED, result
     again = sc.render(spp=2, seed=1, spp_per_pass=1)
     assert again.samples == ref.samples and again.closest_rays == ref.closest_rays
-    np.testing.assert_array_equal(sc.film_develop(), img_ref)
+    np.testing.assert_allclose(sc.film_develop(), img_ref, rtol=1e-5, atol=1e-6)      # film atomics: fp32 addition order
     sc.close()
 
 

@@ -6,8 +6,10 @@ Two kinds of check:
    ray / shade / path-length counters must be identical up to rounding-induced decision flips;
  * independent-stream parity -- against the oracle with its sequential generator (the reference's
    model): mean luminance inside the 3-sigma Monte Carlo interval, relMSE against a high-spp oracle
-   image no worse than 3x the CPU oracle's own at equal spp (the squared-error estimator is heavy
-   tailed; the same-stream test is the sharp one).  Tolerances per SURVEY.md 8(d)."""
+   image no worse than 1.5x the CPU oracle's own at equal spp.  SURVEY.md 8(d) states 1.25x; these images are
+   ~5-9 k pixels at 8-32 spp, where the squared-error estimate itself carries ~10 % sampling error, so the
+   1.25x bar is applied where it is meaningful -- BASELINE configs[0] at full size against a 4096-spp image,
+   tests/test_gpu_render_full.py -- and the same-stream test remains the sharp one here."""
 import numpy as np
 import pytest
 
@@ -43,7 +45,7 @@ def check_render(gpu_lib, oracle_mod, b, spp, ref_spp, label):
     assert abs(lum_gpu - lum_ref) <= 3 * sigma + 1e-3 * lum_ref, (label, lum_gpu, lum_ref, sigma)
     # relMSE at equal spp no worse than the CPU oracle's own (plus slack for a different random stream)
     e_gpu, e_cpu = rel_mse(gpu, ref), rel_mse(cpu, ref)
-    assert e_gpu <= 3.0 * e_cpu + 1e-4, (label, e_gpu, e_cpu)
+    assert e_gpu <= 1.5 * e_cpu + 1e-4, (label, e_gpu, e_cpu)
     # same amount of work per sample: ray counts and path length (reference statistics counters)
     for f, tol in (("closest_rays", 0.02), ("shade_events", 0.02), ("path_length_sum", 0.02)):
         a, c = getattr(st, f) / st.samples, getattr(cpu_stats, f) / cpu_stats.samples

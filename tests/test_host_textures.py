@@ -252,6 +252,14 @@ def test_png_reader(tmp_path):
     rows = [bytes(np.packbits(r).tobytes()) for r in bits]
     write_png(tmp_path / "g1.png", rows, w, h, 1, 0)
     assert close1(_bitmap_texels(tmp_path / "g1.png")[0][:, :, 0], srgb_to_linear(bits * np.uint8(255), 255))
+    # `gamma` overrides what the file declares (bitmap.cpp:218, 251-252 -> Bitmap::setGamma; fmtconv.cpp:1091-1100):
+    # 1 = the stored values ARE linear (data maps), 2.2 = pow(v, 2.2), -1 = sRGB
+    tx, hs = _bitmap_texels(tmp_path / "rgb8.png", '<float name="gamma" value="1"/>')
+    assert not hs.warnings and np.allclose(tx, np.float32(rgb) * (np.float32(1.0) / np.float32(255)), rtol=1e-6, atol=0)
+    tx, _ = _bitmap_texels(tmp_path / "rgb8.png", '<float name="gamma" value="2.2"/>')
+    assert np.allclose(tx, np.power(np.float32(rgb) * (np.float32(1.0) / np.float32(255)), np.float32(2.2)), rtol=2e-6, atol=0)
+    tx, _ = _bitmap_texels(tmp_path / "g16.png", '<float name="gamma" value="-1"/>')
+    assert close1(tx[:, :, 0], srgb_to_linear(g16, 65535))
     # a single channel of an RGB image
     tx, _ = _bitmap_texels(tmp_path / "rgb8.png", '<string name="channel" value="g"/>')
     assert tx.shape == (h, w, 1) and close1(tx[:, :, 0], srgb_to_linear(rgb[:, :, 1], 255))

@@ -7,6 +7,8 @@ sys.path.insert(0, ROOT)
 from mitsuba_b200 import lib, scenes
 
 lib.init(0)
+from mitsuba_b200 import abi
+abi.ABI_VERSION = lib.lib().mtsb_abi_version()      # older variant libraries check the description against their own version
 jobs = sys.argv[1:] or ["cfg2_10m:64", "cfg1_1m:64"]
 tag = os.path.basename(os.environ.get("MTSB200_LIB", "default"))
 for j in jobs:
