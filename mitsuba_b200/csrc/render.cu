@@ -561,7 +561,7 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBu
 // epilogue of the shadow-ray pass: unoccluded -> add the pending emitter contribution
 struct ShadowResolve {
     const float4 *contrib; float4 *L_bpdf;
-    __device__ __forceinline__ void operator()(uint32_t i, const RayIn &, const HitOut &h) const {
+    __device__ __forceinline__ void operator()(uint32_t i, const HitOut &h) const {
         if (h.prim != MTSB_NO_HIT_ID) return;
         const float4 c = contrib[i];
         const uint32_t slot = __float_as_uint(c.w);

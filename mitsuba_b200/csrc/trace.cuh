@@ -49,13 +49,41 @@ struct TraceArgs {
     uint32_t prmt_bias;          // 0x47000000, passed as data so it stays a register operand of PRMT (the selector is then the immediate)
 };
 
+// ---- warp-cooperative triangle phase ---------------------------------------------------------------------------------
+// In a lock-step loop every lane owns one ray.  Node visits keep ~25 of 32 lanes busy, but "each lane tests one of ITS
+// pending triangles" ran with under 9 lanes on average while costing a quarter of all issued instructions (ncu source
+// counters of the round-1 kernel, profiles/r02_trace_regions.md).  So triangles are no longer tested by the lane that owns
+// the ray: every lane hands the triangles of its next hit leaf to a per-warp queue in shared memory, and when 32 tests
+// are queued (or nothing else can make progress) the warp runs ONE triangle phase in which lane j tests queue entry j
+// -- any ray's triangle -- against that ray's origin / direction / interval, which every lane keeps in shared memory.
+// Hits go back to the owning lane through a 64-bit shared-memory minimum over (t, record), so a ray that is hit by
+// several triangles of one phase keeps the nearest, exactly as the sequential order would.  The arithmetic per
+// triangle is unchanged (tri_test with the owner's current [mint, maxt]).
+#define MTSB_TQ_CAP 128            /* queue entries per warp: < 32 are left after the triangle phases, <= 96 are added per iteration */
+#ifndef MTSB_TQ_FLUSH
+#define MTSB_TQ_FLUSH 24           /* run a triangle phase when this many tests are queued (<= 32; 24 measured best)                                */
+#endif
+#define MTSB_TQ_OWNER_SHIFT 27     /* entry = owner lane << 27 | triangle record index (2^27 records)                              */
+
+struct WarpShared {
+    uint32_t tq[MTSB_TQ_CAP];
+    float4 ro[32], rd[32];         // the lanes' rays: (origin, mint), (direction, maxt); maxt follows the accepted hits
+    unsigned long long best[32];   // per owner: min over (ordered t << 32 | record) of the hits of one triangle phase
+};
+
+__device__ __forceinline__ uint32_t order_float(float f) { const uint32_t u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+__device__ __forceinline__ float unorder_float(uint32_t u) { return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u); }
+
 template <bool ANY, class Epilogue>
 __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_MIN_CTAS) k_trace(TraceArgs a, Epilogue ep) {
     __shared__ uint2 s_stack[MTSB_SM_STACK * MTSB_TRACE_BLOCK];
     __shared__ uint8_t s_perm[8 * 256];
+    __shared__ WarpShared s_warp[MTSB_TRACE_BLOCK / 32];
     for (uint32_t i = threadIdx.x; i < 8u * 256u; i += MTSB_TRACE_BLOCK) s_perm[i] = (uint8_t) perm_byte(i & 255u, i >> 8);
-    __syncthreads();
     const uint32_t lane = threadIdx.x & 31;
+    WarpShared &ws = s_warp[threadIdx.x >> 5];
+    ws.best[lane] = ~0ull;
+    __syncthreads();
     const uint32_t n = a.d_count ? min(*a.d_count, a.n_max) : a.n_max;
     uint2 overflow[MTSB_LOCAL_STACK];
     Traversal<SmemStack> tr;
@@ -64,10 +92,13 @@ __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_MIN_CTAS) k_trace
     tr.stack.perm_tab = s_perm;
     tr.stack.sp = 0;
     tr.bias = a.prmt_bias;
+    tr.tw = 0; tr.tw2 = 0; tr.ng_y = 0;
     bool active = false;
     bool exhausted = false;
     uint32_t ray_idx = 0;
-    RayIn ray;
+    uint32_t qhead = 0, qtail = 0;        // warp-uniform, monotonic: entries [qhead, qtail) of the ring are pending
+    uint32_t my_last = 0;                 // queue position behind this lane's last entry: all its tests are done when qhead has passed it
+    const uint32_t lt = (1u << lane) - 1u;
     while (true) {
         // ---- refill idle lanes ----
         const unsigned idle = __ballot_sync(0xFFFFFFFFu, !active);
@@ -78,20 +109,24 @@ __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_MIN_CTAS) k_trace
             base = __shfl_sync(0xFFFFFFFFu, base, leader);
             if (base >= n) exhausted = true;          // uniform across the warp
             if (!active) {
-                const uint32_t idx = base + (uint32_t) __popc(idle & ((1u << lane) - 1u));
+                const uint32_t idx = base + (uint32_t) __popc(idle & lt);
                 if (idx < n) {
                     const float4 r0 = __ldg(reinterpret_cast<const float4 *>(a.rays) + 2 * (size_t) idx);
                     const float4 r1 = __ldg(reinterpret_cast<const float4 *>(a.rays) + 2 * (size_t) idx + 1);
+                    RayIn ray;
                     ray.ox = r0.x; ray.oy = r0.y; ray.oz = r0.z; ray.mint = r0.w;
                     ray.dx = r1.x; ray.dy = r1.y; ray.dz = r1.z; ray.maxt = r1.w;
                     ray_idx = idx;
                     float mint, maxt;
                     if (a.n_nodes != 0 && ray_interval(ray, a.box_lo, a.box_hi, ANY, mint, maxt)) {
                         tr.begin(ray, mint, maxt);
+                        ws.ro[lane] = make_float4(ray.ox, ray.oy, ray.oz, mint);
+                        ws.rd[lane] = make_float4(ray.dx, ray.dy, ray.dz, maxt);
+                        my_last = qhead;
                         active = true;
                     } else {
                         HitOut miss; miss.prim = MTSB_NO_HIT_ID; miss.u = 0; miss.v = 0; miss.t = MTSB_INF;
-                        ep(idx, ray, miss);
+                        ep(idx, miss);
                     }
                 }
             }
@@ -101,17 +136,60 @@ __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_MIN_CTAS) k_trace
             continue;
         }
         // ---- lock-step traversal until the warp has drained below the refill threshold ----
-        // Each iteration: (a) lanes without pending triangles visit one node, (b) lanes with
-        // pending triangles test one, (c) pop / finish.  The three regions are warp-converged.
         unsigned live;
         do {
+            // (a) node phase: lanes with node work and a free batch slot visit one node
             if (active && tr.wants_node()) tr.visit_node(a.nodes);
             __syncwarp();
-            bool done = false;
-            if (active && tr.tw != 0) done = tr.template test_triangle<ANY>(a.tris);
-            __syncwarp();
-            if (active && (done || tr.finished())) {
-                ep(ray_idx, ray, tr.result(a.tris));
+            // (b) every lane with a pending batch hands the triangles of ONE hit leaf (1..3) to the warp's queue
+            uint32_t rec0 = 0, cnt = 0;
+            if (active && tr.tw != 0) tr.next_leaf(rec0, cnt);
+            const unsigned b1 = __ballot_sync(0xFFFFFFFFu, cnt & 1u), b2 = __ballot_sync(0xFFFFFFFFu, cnt & 2u);
+            if (cnt) {
+                const uint32_t pos = qtail + (uint32_t) __popc(b1 & lt) + 2u * (uint32_t) __popc(b2 & lt);
+                const uint32_t e = (lane << MTSB_TQ_OWNER_SHIFT) | rec0;
+                ws.tq[pos & (MTSB_TQ_CAP - 1)] = e;
+                if (cnt > 1) ws.tq[(pos + 1) & (MTSB_TQ_CAP - 1)] = e + 1;
+                if (cnt > 2) ws.tq[(pos + 2) & (MTSB_TQ_CAP - 1)] = e + 2;
+                my_last = pos + cnt;
+            }
+            qtail += (uint32_t) __popc(b1) + 2u * (uint32_t) __popc(b2);
+            // (c) triangle phase: when a full warp of tests is queued, or when nothing else can make progress
+            const bool other_work = __any_sync(0xFFFFFFFFu, active && (tr.tw != 0 || tr.wants_node()));
+            while (qtail - qhead >= (uint32_t) MTSB_TQ_FLUSH || (qtail != qhead && !other_work)) {
+                __syncwarp();
+                const uint32_t nq = min(32u, qtail - qhead);
+                if (lane < nq) {
+                    const uint32_t e = ws.tq[(qhead + lane) & (MTSB_TQ_CAP - 1)];
+                    const uint32_t owner = e >> MTSB_TQ_OWNER_SHIFT, rec = e & ((1u << MTSB_TQ_OWNER_SHIFT) - 1u);
+                    const float4 ro = ws.ro[owner], rd = ws.rd[owner];
+                    const U4 *tp = a.tris + 3 * (size_t) rec;
+                    const U4 q0 = ld16(tp), q1 = ld16(tp + 1), q2 = ld16(tp + 2);
+                    float u, v, t;
+                    if (tri_test(q0, q1, q2, ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, ro.w, rd.w, u, v, t))
+                        atomicMin(&ws.best[owner], ((unsigned long long) order_float(t) << 32) | rec);
+                }
+                qhead += nq;
+                __syncwarp();
+                const unsigned long long b = ws.best[lane];
+                if (b != ~0ull) {                       // this lane's ray was hit in the phase: the nearest hit is the new interval end
+                    ws.best[lane] = ~0ull;
+                    tr.hit_rec = (uint32_t) b;
+                    if (ANY) { tr.ng_y = 0; tr.stack.reset(); tr.tw = 0; tr.tw2 = 0; }      // satisfied: only its queued tests remain to drain
+                    else { tr.tmax = unorder_float((uint32_t) (b >> 32)); ws.rd[lane].w = tr.tmax; }
+                }
+            }
+            // (d) a ray is finished when it has no nodes, no leaves to hand out and no test left in the queue
+            if (active && tr.tw == 0 && !tr.has_nodes() && (int32_t) (qhead - my_last) >= 0) {
+                HitOut h; h.prim = MTSB_NO_HIT_ID; h.u = 0; h.v = 0; h.t = MTSB_INF;
+                if (tr.hit_rec != MTSB_NO_HIT_ID) {
+                    const float4 ro = ws.ro[lane], rd = ws.rd[lane];
+                    const U4 *tp = a.tris + 3 * (size_t) tr.hit_rec;
+                    const U4 q0 = ld16(tp), q1 = ld16(tp + 1), q2 = ld16(tp + 2);
+                    tri_eval(q0, q1, q2, ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, h.u, h.v, h.t);
+                    h.prim = q2.z;
+                }
+                ep(ray_idx, h);
                 active = false;
             }
             live = __ballot_sync(0xFFFFFFFFu, active);
@@ -121,7 +199,7 @@ __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_MIN_CTAS) k_trace
 
 struct StoreHit {
     HitOut *hits;
-    __device__ __forceinline__ void operator()(uint32_t i, const RayIn &, const HitOut &h) const {
+    __device__ __forceinline__ void operator()(uint32_t i, const HitOut &h) const {
         reinterpret_cast<uint4 *>(hits)[i] = make_uint4(h.prim, __float_as_uint(h.u), __float_as_uint(h.v), __float_as_uint(h.t));
     }
 };

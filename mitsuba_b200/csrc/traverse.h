@@ -177,7 +177,7 @@ template <class Stack> struct Traversal {
         ng_x = 0; ng_y = 0x80000000u;
         hit_rec = MTSB_NO_HIT_ID;
         stack.reset();
-        tw = 0; tbase = 0; tcur = 0; tw2 = 0; tbase2 = 0;
+        tw = 0; tbase = 0; tcur = 0; tleft = 0; tw2 = 0; tbase2 = 0;
 #if !MTSB_DEVICE_CODE
         steps = 0; sparse_steps = 0; last_batch = 0;
 #endif
@@ -191,15 +191,16 @@ template <class Stack> struct Traversal {
     // (expensive) node phase; tools/warp_sim.py has the model behind this choice.
     //
     // A leaf batch is the set of hit leaf children of ONE node: word = hit leaves (8 bits, traversal order) << 24 |
-    // triangles left in the leaf being tested << 16 | the node's 2-bit triangle counts, plus the node's
-    // tri_base.  Leaves are expanded lazily, one at a time, when their first triangle is due: the node visit
+    // the node's 2-bit triangle counts, plus the node's tri_base.  Leaves are expanded lazily, one at a time, when their first triangle is due: the node visit
     // itself spends no instructions on per-child triangle masks.
-    uint32_t tw, tbase, tcur;     // batch being tested; tcur = next triangle record of the leaf being tested
+    uint32_t tw, tbase;           // batch whose leaves are handed out next
+    uint32_t tcur, tleft;         // sequential form only: next triangle record / triangles left of the leaf being tested
     uint32_t tw2, tbase2;         // deferred batch (empty when tw2 == 0)
 
     MTSB_HD bool has_nodes() const { return ng_y > 0x00FFFFFFu || !stack.empty(); }
     MTSB_HD bool wants_node() const { return tw2 == 0 && has_nodes(); }
-    MTSB_HD bool finished() const { return tw == 0 && !has_nodes(); }
+    MTSB_HD bool has_triangles() const { return tw != 0 || tleft != 0; }
+    MTSB_HD bool finished() const { return tw == 0 && tleft == 0 && !has_nodes(); }
 
     // (a) take the nearest pending child of the current group and intersect its 8 children
     MTSB_HD void visit_node(const U4 *nodes) {
@@ -235,7 +236,7 @@ template <class Stack> struct Traversal {
         const float gx = fabsf(sdx) * 0.00390625f, gy = fabsf(sdy) * 0.00390625f, gz = fabsf(sdz) * 0.00390625f;
         const float anx = bx - gx, any_ = by - gy, anz = bz - gz, afx = bx + gx, afy = by + gy, afz = bz + gz;
         // near / far planes by ray direction sign
-        const bool nx = dx < 0.0f, ny = dy < 0.0f, nz = dz < 0.0f;
+        const bool nx = !(octinv & 1u), ny = !(octinv & 2u), nz = !(octinv & 4u);      // d < 0 (begin(): octinv bit = d >= 0)
         const uint32_t lox0 = n2.x, lox1 = n2.y, loy0 = n2.z, loy1 = n2.w, loz0 = n3.x, loz1 = n3.y;
         const uint32_t hix0 = n3.z, hix1 = n3.w, hiy0 = n4.x, hiy1 = n4.y, hiz0 = n4.z, hiz1 = n4.w;
         const uint32_t nearx[2] = {nx ? hix0 : lox0, nx ? hix1 : lox1}, farx[2] = {nx ? lox0 : hix0, nx ? lox1 : hix1};
@@ -287,36 +288,31 @@ template <class Stack> struct Traversal {
             const uint32_t w = leaves24 | counts;
             if (tw == 0) { tw = w; tbase = n1.y; } else { tw2 = w; tbase2 = n1.y; }
         }
-#if MTSB_DEVICE_CODE && defined(MTSB_PREFETCH_NODE)
-        if (ng_y > 0x00FFFFFFu) {          // the child this lane visits next: start its fetch behind the triangle phase
-            const uint32_t slot2 = ((uint32_t) bfind(ng_y) - 24u) ^ octinv;
-            const U4 *nx2 = nodes + 5 * (size_t) (ng_x + (uint32_t) popc(ng_y & ~(0xFFFFFFFFu << slot2) & 0xFFu));
-            asm volatile("prefetch.global.L1 [%0];" :: "l"(nx2));
-            asm volatile("prefetch.global.L1 [%0];" :: "l"(nx2 + 4));
-        }
-#endif
     }
 
-    // (b) test one pending triangle; returns true when an any-hit query is satisfied
+    // (b) next hit leaf of the pending batch (nearest first): its first triangle record and its triangle count (1..3);
+    // promotes the deferred batch when the current one has no leaves left
+    MTSB_HD void next_leaf(uint32_t &rec0, uint32_t &cnt) {
+        const int b = bfind(tw);                                   // 24 + position in traversal order
+        tw &= ~(1u << b);
+        const uint32_t s2 = (((uint32_t) b - 24u) ^ octinv) * 2u;
+        const uint32_t c = tw & 0xffffu;
+        const uint32_t below = c & ~(0xFFFFFFFFu << s2);
+        rec0 = tbase + (uint32_t) popc(below & 0x5555u) + 2u * (uint32_t) popc(below & 0xAAAAu);
+        cnt = (c >> s2) & 3u;
+        if ((tw & 0xFF000000u) == 0) { tw = tw2; tbase = tbase2; tw2 = 0; }
+    }
+
+    // (b') sequential form (emulation build, trace_one): test ONE pending triangle; returns true when an any-hit query
+    // is satisfied.  The leaf being tested is kept in (tcur, tleft) because next_leaf() may already have promoted the batch.
     template <bool ANY> MTSB_HD bool test_triangle(const U4 *tris) {
-        if ((tw & 0x00030000u) == 0) {
-            // next hit leaf of the batch (nearest first): its slot, triangle count and offset inside the node's run
-            const int b = bfind(tw);                                   // 24 + position in traversal order
-            tw &= ~(1u << b);
-            const uint32_t s2 = (((uint32_t) b - 24u) ^ octinv) * 2u;
-            const uint32_t c = tw & 0xffffu;
-            const uint32_t below = c & ~(0xFFFFFFFFu << s2);
-            tcur = tbase + (uint32_t) popc(below & 0x5555u) + 2u * (uint32_t) popc(below & 0xAAAAu);
-            tw |= ((c >> s2) & 3u) << 16;
-        }
+        if (tleft == 0) next_leaf(tcur, tleft);
 #if !MTSB_DEVICE_CODE
         ++tri_tests;
 #endif
         const uint32_t rec = tcur;
         const U4 *tp = tris + 3 * (size_t) rec;
-        ++tcur;
-        tw -= 1u << 16;
-        if ((tw & 0xFF030000u) == 0) { tw = tw2; tbase = tbase2; tw2 = 0; }      // batch done: promote the deferred one
+        ++tcur; --tleft;
         const U4 q0 = ld16(tp), q1 = ld16(tp + 1), q2 = ld16(tp + 2);
         float u, v, t;
         if (tri_test(q0, q1, q2, ox, oy, oz, dx, dy, dz, tmin, tmax, u, v, t)) {
@@ -342,7 +338,7 @@ template <class Stack> struct Traversal {
     // one lock-step iteration for a single ray
     template <bool ANY> MTSB_HD bool step(const U4 *nodes, const U4 *tris) {
         if (wants_node()) visit_node(nodes);
-        if (tw != 0 && test_triangle<ANY>(tris)) return true;
+        if (has_triangles() && test_triangle<ANY>(tris)) return true;
         return finished();
     }
 };

@@ -333,7 +333,7 @@ extern "C" void emu_trace_profile(void *h, const RayIn *rays, size_t n, int mode
                     ++len;
                 }
                 bool done = false;
-                if (tr.tw != 0) done = mode == 1 ? tr.test_triangle<true>(tris) : tr.test_triangle<false>(tris);
+                if (tr.has_triangles()) done = mode == 1 ? tr.test_triangle<true>(tris) : tr.test_triangle<false>(tris);
                 if (done || tr.finished()) break;
             }
         }

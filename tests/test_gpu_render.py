@@ -43,9 +43,16 @@ def check_render(gpu_lib, oracle_mod, b, spp, ref_spp, label):
     lum_gpu = float((gpu @ LUM).mean())
     lum_ref = float((ref @ LUM).mean())
     assert abs(lum_gpu - lum_ref) <= 3 * sigma + 1e-3 * lum_ref, (label, lum_gpu, lum_ref, sigma)
-    # relMSE at equal spp no worse than the CPU oracle's own (plus slack for a different random stream)
-    e_gpu, e_cpu = rel_mse(gpu, ref), rel_mse(cpu, ref)
-    assert e_gpu <= 1.5 * e_cpu + 1e-4, (label, e_gpu, e_cpu)
+    # relMSE at equal spp no worse than the CPU oracle's own.  The squared-error estimate of a ~5 k-pixel image is
+    # dominated by a few firefly pixels (glass under an environment), so both sides take the MEDIAN over five seeds.
+    e_gpu_all, e_cpu_all = [rel_mse(gpu, ref)], [rel_mse(cpu, ref)]
+    for k in range(1, 5):
+        sc.render(spp=spp, seed=7 + 100 * k)
+        e_gpu_all.append(rel_mse(sc.film_develop().astype(np.float64), ref))
+        orc.render(spp=spp, seed=5 + 100 * k)
+        e_cpu_all.append(rel_mse(orc.film_develop().astype(np.float64), ref))
+    e_gpu, e_cpu = float(np.median(e_gpu_all)), float(np.median(e_cpu_all))
+    assert e_gpu <= 1.5 * e_cpu + 1e-4, (label, e_gpu_all, e_cpu_all)
     # same amount of work per sample: ray counts and path length (reference statistics counters)
     for f, tol in (("closest_rays", 0.02), ("shade_events", 0.02), ("path_length_sum", 0.02)):
         a, c = getattr(st, f) / st.samples, getattr(cpu_stats, f) / cpu_stats.samples
