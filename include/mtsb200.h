@@ -339,6 +339,20 @@ mtsb_scene_t mtsb_multi_scene(mtsb_multi_t m, int i);   /* scene on the i-th dev
 int  mtsb_multi_device_count(mtsb_multi_t m);
 void mtsb_multi_destroy(mtsb_multi_t m);
 
+/* ---- allocation-free ray query --------------------------------------------------------------------------------
+ * mtsb_trace_static has NO counterpart in the reference; it was added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same
+ * inputs, outputs and results as mtsb_trace (host buffers; mode = MTSB_TRACE_CLOSEST / MTSB_TRACE_ANY), same kernel, but
+ * every byte of scratch (ray staging, hit staging, the persistent kernel's work counter) lives in one file-scope device
+ * array of fixed size, so the call allocates nothing: no cudaMalloc, no cudaFree, no allocating library routine.
+ * Limit: n <= MTSB_STATIC_TRACE_MAX_RAYS per call (larger n: MTSB_ERR_INVALID, nothing is traced); the array is
+ * 12 MiB + 256 B and every GPU that loads the library holds it until the process exits.  All calls share the array, which
+ * keeps the last call's contents (the work counter is cleared before every launch): calls that overlap on one GPU
+ * race -- serialise them.  The call returns after the hits are in `hits`.                                            */
+#define MTSB_STATIC_TRACE_MAX_RAYS 262144
+int  mtsb_trace_static(mtsb_scene_t scene, const MtsbRay *rays, size_t n, int mode, MtsbHit *hits);
+int  mtsb_trace_static_max_rays(void);
+
 /* Synthetic workload generators used by bench.py / tests (device-side ray sets of cfg 4). */
 int  mtsb_gen_rays_device(mtsb_scene_t scene, int kind /*0 camera-coherent, 1 bsphere chords*/,
                           size_t n, uint64_t seed, void *d_rays);

@@ -24,7 +24,7 @@ SYMBOLS = [
     "mtsb_fill_intersection", "mtsb_sensor_rays", "mtsb_film_clear", "mtsb_film_put", "mtsb_film_size",
     "mtsb_film_download", "mtsb_film_device_ptr", "mtsb_film_develop", "mtsb_render", "mtsb_cancel",
     "mtsb_gen_rays_device", "mtsb_multi_create", "mtsb_multi_render", "mtsb_multi_cancel", "mtsb_multi_scene",
-    "mtsb_multi_device_count", "mtsb_multi_destroy",
+    "mtsb_multi_device_count", "mtsb_multi_destroy", "mtsb_trace_static", "mtsb_trace_static_max_rays",
 ]
 
 
@@ -71,6 +71,7 @@ def lib():
         L.mtsb_render.argtypes = [C.c_void_p, C.POINTER(abi.RenderParams), C.POINTER(abi.Stats)]
         L.mtsb_cancel.argtypes = [C.c_void_p]
         L.mtsb_gen_rays_device.argtypes = [C.c_void_p, C.c_int, C.c_size_t, C.c_uint64, C.c_void_p]
+        L.mtsb_trace_static.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]
         L.mtsb_multi_create.argtypes = [C.POINTER(abi.SceneDesc), C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_void_p)]
         L.mtsb_multi_render.argtypes = [C.c_void_p, C.POINTER(abi.RenderParams), C.POINTER(abi.Stats)]
         L.mtsb_multi_cancel.argtypes = [C.c_void_p]
@@ -132,6 +133,13 @@ class Scene:
         rays = np.ascontiguousarray(rays, dtype=abi.RAY_DTYPE)
         hits = np.zeros(rays.shape[0], dtype=abi.HIT_DTYPE)
         _check(lib().mtsb_trace(self.h, _vp(rays), rays.shape[0], mode, _vp(hits)))
+        return hits
+
+    def trace_static(self, rays, mode=abi.TRACE_CLOSEST):
+        """mtsb_trace_static: the same query with all scratch in a fixed device array (no allocation; n <= 262144)."""
+        rays = np.ascontiguousarray(rays, dtype=abi.RAY_DTYPE)
+        hits = np.zeros(rays.shape[0], dtype=abi.HIT_DTYPE)
+        _check(lib().mtsb_trace_static(self.h, _vp(rays), rays.shape[0], mode, _vp(hits)))
         return hits
 
     def trace_device(self, d_rays_ptr, n, d_hits_ptr, mode=abi.TRACE_CLOSEST, stream=None, timed=True):

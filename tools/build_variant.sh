@@ -7,7 +7,7 @@ name=$1; flags=$2
 mkdir -p _exp/build_$name
 NV="/usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC,-Wall,-Wno-unused-function --expt-relaxed-constexpr $flags"
 pids=()
-for f in api bvh_build trace query render multi; do
+for f in api bvh_build trace query render multi noalloc; do
   $NV -c mitsuba_b200/csrc/$f.cu -o _exp/build_$name/$f.o & pids+=($!)
 done
 for p in "${pids[@]}"; do wait $p; done
