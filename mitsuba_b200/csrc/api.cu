@@ -183,10 +183,20 @@ static int validate(const MtsbSceneDesc *d) {
         if (sh.has_normals && !d->normals) { set_error("shape has_normals but normals == NULL"); return MTSB_ERR_INVALID; }
     }
     if (tri_sum != d->n_tris) { set_error("shape triangle counts do not add up to n_tris"); return MTSB_ERR_INVALID; }
+    for (uint32_t i = 0; i < d->n_shapes; ++i) {
+        const MtsbShape &sh = d->shapes[i];
+        if (sh.emitter < 0) continue;
+        if (d->emitters[sh.emitter].type != MTSB_EMITTER_AREA || d->emitters[sh.emitter].shape != (int32_t) i) { set_error("shape refers to an emitter that is not its area emitter"); return MTSB_ERR_INVALID; }
+        // the area cdf of an emitter shape is built on the host from these indices: check them here (all other indices are checked on the device)
+        for (uint64_t j = 0; j < 3ull * sh.n_tris; ++j) {
+            const uint32_t ix = d->indices[3ull * sh.first_tri + j];
+            if (ix < sh.first_vertex || ix >= sh.first_vertex + sh.n_vertices) { set_error("triangle index outside its shape's vertex range"); return MTSB_ERR_INVALID; }
+        }
+    }
     for (uint32_t i = 0; i < d->n_materials; ++i) {
         const MtsbMaterial &m = d->materials[i];
         if (m.type > MTSB_BSDF_PLASTIC || m.distribution > MTSB_DISTR_GGX || m.back >= (int32_t) d->n_materials) { set_error("bad material record"); return MTSB_ERR_INVALID; }
-        if (m.tex_reflectance > d->n_textures || m.tex_transmittance > d->n_textures) { set_error("material refers to a missing texture"); return MTSB_ERR_INVALID; }
+        if (m.tex_reflectance > d->n_textures || m.tex_transmittance > d->n_textures || m.tex_alpha > d->n_textures) { set_error("material refers to a missing texture"); return MTSB_ERR_INVALID; }
     }
     if (d->n_textures && !d->textures) { set_error("scene description: NULL texture array"); return MTSB_ERR_INVALID; }
     for (uint32_t i = 0; i < d->n_textures; ++i) {
@@ -207,6 +217,7 @@ static int validate(const MtsbSceneDesc *d) {
             if (em->width > 0xFFFF || em->height > 0xFFFF) { set_error("Environment maps images must be smaller than 65536 pixels in width and height"); return MTSB_ERR_INVALID; }
         }
         if (e.type == MTSB_EMITTER_AREA && (e.shape < 0 || e.shape >= (int32_t) d->n_shapes)) { set_error("area emitter without a shape"); return MTSB_ERR_INVALID; }
+        if (e.type == MTSB_EMITTER_AREA && d->shapes[e.shape].emitter != (int32_t) i) { set_error("area emitter and its shape do not refer to each other"); return MTSB_ERR_INVALID; }
         if ((e.type == MTSB_EMITTER_CONSTANT || e.type == MTSB_EMITTER_ENVMAP) && ++n_env > 1) { set_error("only one environment emitter is allowed (scene.cpp:575-579)"); return MTSB_ERR_INVALID; }
     }
     const MtsbSensor &se = d->sensor;
@@ -216,6 +227,17 @@ static int validate(const MtsbSceneDesc *d) {
     if (d->sampler.type > MTSB_SAMPLER_SOBOL) { set_error("bad sampler type"); return MTSB_ERR_INVALID; }
     if (!(se.fov_x_deg > 0 && se.fov_x_deg < 180) || !(se.near_clip > 0) || !(se.far_clip > se.near_clip)) { set_error("bad sensor parameters"); return MTSB_ERR_INVALID; }
     return MTSB_OK;
+}
+
+// every triangle index must lie inside the vertex range of the triangle's shape (the kernels index positions / normals /
+// texcoords with them); checked on the device right after the upload: one pass at HBM speed instead of a host loop
+__global__ void k_check_indices(const uint32_t *indices, const uint32_t *tri_shape, const MtsbShape *shapes, uint64_t n_tris, uint32_t *bad) {
+    const uint64_t prim = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (prim >= n_tris) return;
+    const MtsbShape sh = shapes[tri_shape[prim]];
+    bool ok = true;
+    for (int k = 0; k < 3; ++k) { const uint32_t ix = indices[3 * prim + k]; ok &= ix >= sh.first_vertex && ix < sh.first_vertex + sh.n_vertices; }
+    if (!ok) atomicOr(bad, 1u);
 }
 
 static float rfilter_eval(const MtsbSensor &se, float x) {
@@ -344,6 +366,30 @@ extern "C" int mtsb_scene_create(const MtsbSceneDesc *d, mtsb_scene_t *out) {
         ev.normalization = (float) (1.0f / ((double) rowSum * (2 * 3.14159265358979323846 / W) * (3.14159265358979323846 / H)));
         ev.pixel_size_x = (float) (2 * 3.14159265358979323846 / W); ev.pixel_size_y = (float) (3.14159265358979323846 / H);
         for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) { ev.to_world[3 * r + c] = em.to_world[4 * r + c]; ev.to_local[3 * r + c] = em.to_local[4 * r + c]; }
+        {   // the MIP pyramid of the map for filtered lookups (envmap.cpp:140-178: Lanczos-2 downsampling, repeat in u, clamp
+            // in v, EWA with maxAnisotropy 10) -- the same builder and lookup code as the bitmap texture
+            MtsbTexture mt;
+            std::memset(&mt, 0, sizeof(mt));
+            mt.type = MTSB_TEX_BITMAP; mt.filter = MTSB_TEXFILTER_EWA; mt.wrap_u = MTSB_WRAP_REPEAT; mt.wrap_v = MTSB_WRAP_CLAMP;
+            mt.uv_scale[0] = mt.uv_scale[1] = 1.0f; mt.scale[0] = mt.scale[1] = mt.scale[2] = 1.0f;
+            mt.max_anisotropy = 10.0f; mt.width = W; mt.height = H; mt.channels = 3; mt.texels = em.rgb;
+            TextureView tv;
+            std::memset(&tv, 0, sizeof(tv));
+            tv.type = mt.type; tv.filter = mt.filter; tv.wrap_u = mt.wrap_u; tv.wrap_v = mt.wrap_v;
+            for (int k = 0; k < 2; ++k) tv.uv_scale[k] = 1.0f;
+            for (int k = 0; k < 3; ++k) tv.scale[k] = 1.0f;
+            tv.max_anisotropy = mt.max_anisotropy;
+            std::vector<HalfTexel> pyr;
+            build_texture_levels(mt, tv, pyr);
+            float lut[MTSB_MIPMAP_LUT_SIZE];
+            for (int i = 0; i < MTSB_MIPMAP_LUT_SIZE; ++i) {
+                const float r2 = (float) i / (float) (MTSB_MIPMAP_LUT_SIZE - 1);
+                lut[i] = (float) std::exp((double) (-2.0f * r2)) - (float) std::exp((double) -2.0f);     // mipmap.h:296-302
+            }
+            if ((rc = dev_upload(s, &tv.weight_lut, lut, (size_t) MTSB_MIPMAP_LUT_SIZE))) return fail(rc);
+            if ((rc = dev_upload(s, &tv.texels, pyr.data(), pyr.size()))) return fail(rc);
+            if ((rc = dev_upload(s, &ev.mip, &tv, 1))) return fail(rc);
+        }
         if ((rc = dev_upload(s, &ev.texels, tex.data(), tex.size()))) return fail(rc);
         if ((rc = dev_upload(s, &ev.cdf_rows, cdf_rows.data(), cdf_rows.size()))) return fail(rc);
         if ((rc = dev_upload(s, &ev.cdf_cols, cdf_cols.data(), cdf_cols.size()))) return fail(rc);
@@ -408,6 +454,17 @@ extern "C" int mtsb_scene_create(const MtsbSceneDesc *d, mtsb_scene_t *out) {
         }
         v.sampler_type = sv.type;
         if ((rc = dev_upload(s, &v.sampler, &sv, 1))) return fail(rc);
+    }
+    if (d->n_tris) {
+        uint32_t *d_bad = nullptr, h_bad = 0;
+        if ((rc = dev_alloc(s, &d_bad, 1))) return fail(rc);
+        if (cudaMemsetAsync(d_bad, 0, sizeof(uint32_t), s->stream) != cudaSuccess) return fail(MTSB_ERR_CUDA);
+        k_check_indices<<<grid_for(d->n_tris, 256), 256, 0, s->stream>>>(v.indices, v.tri_shape, v.shapes, d->n_tris, d_bad);
+        s->launches++;
+        if (cudaMemcpyAsync(&h_bad, d_bad, sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream) != cudaSuccess || cudaStreamSynchronize(s->stream) != cudaSuccess) {
+            set_error("index check failed"); cudaGetLastError(); return fail(MTSB_ERR_CUDA);
+        }
+        if (h_bad) { set_error("triangle index outside its shape's vertex range"); return fail(MTSB_ERR_INVALID); }
     }
     if ((rc = build_bvh(s, v.positions, v.indices, d->n_tris))) return fail(rc);
     if ((rc = pack_shading_records(s, d->n_tris))) return fail(rc);

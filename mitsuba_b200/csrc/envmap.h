@@ -4,11 +4,10 @@
 //   internalPdfDirection       :603-633
 //   sampleDirect / pdfDirect   :516-556
 // The texels are kept in half precision, as the reference keeps them (envmap.cpp:101-103).
-// Filtered lookups: the reference sends rays that carry differentials (primary rays) through MIPMap::eval (EWA); that
-// call returns evalBilinear(0, uv) whenever the pixel footprint is smaller than a texel (mipmap.h:694-710,
-// majorRadius < 1), which is the regime of every map whose texels are larger than an image pixel.  Ray differentials
-// are not produced on this path, so the level-0 bilinear lookup is used throughout; minified maps
-// are therefore unfiltered where the reference would blur them.
+// Filtered lookups: the reference sends rays that carry differentials (the camera rays; path.cpp drops them after the
+// first hit) through MIPMap::eval -- EWA on the Lanczos pyramid with maxAnisotropy 10, repeat in u, clamp in v
+// (envmap.cpp:140-178, 393-407).  envmap_eval_filtered (texture.h, next to the pyramid code it shares with the bitmap
+// texture) does the same for the first segment of a path; every other lookup is the level-0 bilinear one.
 #pragma once
 #include "hd.h"
 #include "../../include/mtsb200.h"
@@ -24,8 +23,11 @@ struct __align__(8) HalfTexel { uint32_t x, y; };      // half4: (r | g << 16, b
 struct alignas(8) HalfTexel { uint32_t x, y; };
 #endif
 
+struct TextureView;                 // texture.h
+
 struct EnvmapView {
     int width, height;
+    const TextureView *mip;         // the map's MIP pyramid (EWA, repeat / clamp), for lookups of rays with differentials
     const HalfTexel *texels;           // half4 per texel: (r, g, b, unused)
     const float *cdf_rows;          // height + 1
     const float *cdf_cols;          // (width + 1) * height
@@ -85,9 +87,6 @@ MTSB_HD V3 envmap_eval(const EnvmapView &ev, V3 d) {
                    + envmap_texel(ev, xPos + 1, yPos) * dx1 * dy2 + envmap_texel(ev, xPos + 1, yPos + 1) * dx1 * dy1;   // mipmap.h:592-595
     return value * ev.scale;
 }
-
-// PLACEHOLDER until the MIP pyramid of the map is built (texture.h): unfiltered
-MTSB_HD V3 envmap_eval_filtered(const EnvmapView &ev, V3 d, V3 rxd, V3 ryd) { (void) rxd; (void) ryd; return envmap_eval(ev, d); }
 
 // EnvironmentMap::sampleReuse (envmap.cpp:655-661): std::lower_bound on a float CDF
 MTSB_HD uint32_t envmap_sample_reuse(const float *cdf, uint32_t size, float &sample) {

@@ -40,6 +40,10 @@ namespace mtsb {
 
 #define MTSB_TILE 32
 #define MTSB_SHADE_BLOCK 128
+#ifndef MTSB_SHADE_MIN_BLOCKS
+#define MTSB_SHADE_MIN_BLOCKS 8      /* resident CTAs per SM the shading kernels' register allocation is held to (64 registers: the stage waits on
+                                        dependent gathers, so resident warps pay more than the spills cost; 1 / 5 / 6 / 8 measured: 41.1 / 42.9 / 39.5 / 38.3 ms) */
+#endif
 
 __device__ __forceinline__ uint32_t queue_push(uint32_t *counter) {
     cg::coalesced_group g = cg::coalesced_threads();
@@ -342,6 +346,7 @@ __device__ __noinline__ void resolve_textured(const SceneView &sc, int mat, cons
         for (int i = 0; i < n; ++i) {
             if (lm[i].tex_reflectance) bitmap |= sc.textures[lm[i].tex_reflectance - 1].type == MTSB_TEX_BITMAP;
             if (lm[i].tex_transmittance) bitmap |= sc.textures[lm[i].tex_transmittance - 1].type == MTSB_TEX_BITMAP;
+            if (lm[i].tex_alpha) bitmap |= sc.textures[lm[i].tex_alpha - 1].type == MTSB_TEX_BITMAP;
         }
         if (bitmap) {
             V3 rxd, ryd;
@@ -358,11 +363,18 @@ __device__ __noinline__ void resolve_textured(const SceneView &sc, int mat, cons
             const V3 c = texture_eval(sc.textures[lm[i].tex_transmittance - 1], its.uv, pt);
             lm[i].transmittance[0] = c.x; lm[i].transmittance[1] = c.y; lm[i].transmittance[2] = c.z;
         }
+        if (lm[i].tex_alpha) {
+            // roughconductor.cpp:379-384 / roughdielectric.cpp:300-305: MicrofacetDistribution(type, m_alphaU->eval(its).average(),
+            // m_alphaV->eval(its).average()), whose constructor clamps both to >= 1e-4 (microfacet.h:135-136)
+            const V3 c = texture_eval(sc.textures[lm[i].tex_alpha - 1], its.uv, pt);
+            const float a = fmaxf((c.x + c.y + c.z) * (1.0f / 3.0f), 1e-4f);
+            lm[i].alpha_u = a; lm[i].alpha_v = a;
+        }
     }
 }
 
 template <int Q, bool QMC>
-__global__ void __launch_bounds__(MTSB_SHADE_BLOCK) k_shade(SceneView sc, PathBuffers pb, PassInfo ps, RenderConst rc, int cur, int bounce) {
+__global__ void __launch_bounds__(MTSB_SHADE_BLOCK, MTSB_SHADE_MIN_BLOCKS) k_shade(SceneView sc, PathBuffers pb, PassInfo ps, RenderConst rc, int cur, int bounce) {
     // Outputs (shadow ray + pending contribution, continuation ray) are staged in shared memory and queue space is
     // reserved once per block and queue at the end of the iteration: one global atomic per block instead of one per warp.
     __shared__ float4 s_sray[2 * MTSB_SHADE_BLOCK], s_contrib[MTSB_SHADE_BLOCK], s_nray[2 * MTSB_SHADE_BLOCK];
@@ -1154,6 +1166,7 @@ extern "C" int mtsb_render(mtsb_scene_t scene, const MtsbRenderParams *params, M
     if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
     if (e != cudaSuccess && status == MTSB_OK) status = cuda_fail(e, "mtsb_render", __FILE__, __LINE__);
     if (status == MTSB_OK) { e = cudaGetLastError(); if (e != cudaSuccess) status = cuda_fail(e, "mtsb_render kernels", __FILE__, __LINE__); }
+    if (status == MTSB_OK) status = check_stack_overflow("mtsb_render");
     if (stats && status == MTSB_OK) {
         Counters hc;
         cudaMemcpy(&hc, P.pb->ctr, sizeof(hc), cudaMemcpyDeviceToHost);

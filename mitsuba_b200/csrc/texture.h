@@ -155,6 +155,19 @@ MTSB_HD V3 tex_eval_filtered(const TextureView &tv, P2 uv, float d0x, float d0y,
     return tex_eval_ewa(tv, ilevel, uv, A, B, C) * (1.0f - a) + tex_eval_ewa(tv, ilevel + 1, uv, A, B, C) * a;
 }
 
+// EnvironmentMap::evalEnvironment for a ray that carries differentials (envmap.cpp:380-410): d = ray direction,
+// rxd / ryd = directions of its x / y offset rays (all in world space)
+MTSB_HD V3 envmap_eval_filtered(const EnvmapView &ev, V3 d, V3 rxd, V3 ryd) {
+    const V3 v = envmap_xform(ev.to_local, d);
+    P2 uv; uv.x = atan2f(v.x, -v.z) * MTSB_INV_TWOPI; uv.y = envmap_safe_acos(v.y) * MTSB_INV_PI;
+    const V3 dvdx = envmap_xform(ev.to_local, rxd) - v, dvdy = envmap_xform(ev.to_local, ryd) - v;
+    const float t1 = MTSB_INV_TWOPI / (v.x * v.x + v.z * v.z);
+    const float t2 = -MTSB_INV_PI / fmaxf(sqrtf(fmaxf(0.0f, 1.0f - v.y * v.y)), MTSB_EPSILON);
+    const float dudx_x = t1 * (dvdx.z * v.x - dvdx.x * v.z), dudx_y = t2 * dvdx.y;
+    const float dudy_x = t1 * (dvdy.z * v.x - dvdy.x * v.z), dudy_y = t2 * dvdy.y;
+    return tex_eval_filtered(*ev.mip, uv, dudx_x, dudx_y, dudy_x, dudy_y) * ev.scale;
+}
+
 MTSB_HD V3 tex_procedural(const TextureView &tv, P2 uv) {
     if (tv.type == MTSB_TEX_CHECKERBOARD) {                                                // checkerboard.cpp:61-69
         const int x = 2 * tex_modulo((int) (uv.x * 2), 2) - 1, y = 2 * tex_modulo((int) (uv.y * 2), 2) - 1;

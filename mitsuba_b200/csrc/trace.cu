@@ -9,6 +9,11 @@
 #include "trace.cuh"
 #include "sensor.h"
 #include "rng.h"
+#include <map>
+#include <mutex>
+#include <thread>
+#include <cstring>
+#include <algorithm>
 
 namespace mtsb {
 
@@ -69,24 +74,109 @@ extern "C" int mtsb_trace_device(mtsb_scene_t scene, const void *d_rays, size_t 
     return rc;
 }
 
+// ---- mtsb_trace: host buffers in, host buffers out ---------------------------------------------------------------
+// The batch moves through the GPU in chunks of MTSB_TRACE_CHUNK rays on three streams -- copy in | trace | copy out -- so that
+// the PCIe transfers of neighbouring chunks overlap the kernel (one cudaMemcpyAsync per chunk and direction).  Pageable
+// caller memory is staged through two pinned buffers per direction, filled / drained by a few host threads (a single
+// memcpy thread moves ~10 GB/s, less than one PCIe direction); buffers the caller has pinned itself (cudaHostAlloc /
+// cudaHostRegister) are used in place.  The staging memory is allocated once per device and kept.
+#define MTSB_TRACE_CHUNK (1u << 20)
+#define MTSB_TRACE_COPY_THREADS 4
+
+namespace {
+struct TracePipe {
+    bool ready = false;
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    MtsbRay *pin_rays[2] = {nullptr, nullptr}; MtsbHit *pin_hits[2] = {nullptr, nullptr};
+    cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_k[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
+};
+std::mutex g_pipe_mutex;
+std::map<int, TracePipe> g_pipes;
+
+int pipe_init(TracePipe &p) {
+    if (p.ready) return MTSB_OK;
+    MTSB_CUDA(cudaStreamCreateWithFlags(&p.s_in, cudaStreamNonBlocking));
+    MTSB_CUDA(cudaStreamCreateWithFlags(&p.s_out, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+        MTSB_CUDA(cudaHostAlloc((void **) &p.pin_rays[i], (size_t) MTSB_TRACE_CHUNK * sizeof(MtsbRay), cudaHostAllocDefault));
+        MTSB_CUDA(cudaHostAlloc((void **) &p.pin_hits[i], (size_t) MTSB_TRACE_CHUNK * sizeof(MtsbHit), cudaHostAllocDefault));
+        MTSB_CUDA(cudaEventCreateWithFlags(&p.ev_in[i], cudaEventDisableTiming));
+        MTSB_CUDA(cudaEventCreateWithFlags(&p.ev_k[i], cudaEventDisableTiming));
+        MTSB_CUDA(cudaEventCreateWithFlags(&p.ev_out[i], cudaEventDisableTiming));
+    }
+    p.ready = true;
+    return MTSB_OK;
+}
+
+bool is_pinned(const void *ptr) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, ptr) != cudaSuccess) { cudaGetLastError(); return false; }
+    return at.type == cudaMemoryTypeHost;
+}
+
+void parallel_copy(void *dst, const void *src, size_t bytes) {
+    if (bytes < (4u << 20)) { std::memcpy(dst, src, bytes); return; }
+    std::thread th[MTSB_TRACE_COPY_THREADS - 1];
+    const size_t part = (bytes / MTSB_TRACE_COPY_THREADS + 63) & ~(size_t) 63;
+    for (int t = 1; t < MTSB_TRACE_COPY_THREADS; ++t) {
+        const size_t off = (size_t) t * part;
+        if (off >= bytes) break;
+        th[t - 1] = std::thread([=] { std::memcpy((char *) dst + off, (const char *) src + off, std::min(part, bytes - off)); });
+    }
+    std::memcpy(dst, src, std::min(part, bytes));
+    for (auto &t : th) if (t.joinable()) t.join();
+}
+}  // namespace
+
 extern "C" int mtsb_trace(mtsb_scene_t scene, const MtsbRay *rays, size_t n, int mode, MtsbHit *hits) {
     Scene *s = reinterpret_cast<Scene *>(scene);
-    if (!s || (n && (!rays || !hits))) { set_error("mtsb_trace: bad argument"); return MTSB_ERR_INVALID; }
+    if (!s || (n && (!rays || !hits)) || (mode != MTSB_TRACE_CLOSEST && mode != MTSB_TRACE_ANY)) { set_error("mtsb_trace: bad argument"); return MTSB_ERR_INVALID; }
     if (n == 0) return MTSB_OK;
     MTSB_CUDA(cudaSetDevice(s->device));
-    void *d_rays = nullptr, *d_hits = nullptr;
-    MTSB_CUDA(dmalloc(&d_rays, n * sizeof(MtsbRay)));
-    cudaError_t e = dmalloc(&d_hits, n * sizeof(MtsbHit));
-    if (e != cudaSuccess) { dfree(d_rays); return cuda_fail(e, "cudaMalloc", __FILE__, __LINE__); }
-    int rc = MTSB_OK;
-    e = cudaMemcpyAsync(d_rays, rays, n * sizeof(MtsbRay), cudaMemcpyHostToDevice, s->stream);
-    if (e == cudaSuccess) rc = mtsb_trace_device(scene, d_rays, n, mode, d_hits, s->stream, nullptr);
-    if (e == cudaSuccess && rc == MTSB_OK) e = cudaMemcpyAsync(hits, d_hits, n * sizeof(MtsbHit), cudaMemcpyDeviceToHost, s->stream);
-    if (e == cudaSuccess && rc == MTSB_OK) e = cudaStreamSynchronize(s->stream);
-    if (e != cudaSuccess || rc != MTSB_OK) cudaStreamSynchronize(s->stream);       // nothing in flight when the blocks go back to the cache
-    dfree(d_rays); dfree(d_hits);
+    std::lock_guard<std::mutex> g(g_pipe_mutex);             // one host-buffer query per process at a time: the staging buffers are shared
+    TracePipe &p = g_pipes[s->device];
+    int rc = pipe_init(p);
+    if (rc) return rc;
+    const size_t chunk = std::min<size_t>(n, MTSB_TRACE_CHUNK);
+    void *d_rays[2] = {nullptr, nullptr}, *d_hits[2] = {nullptr, nullptr};
+    cudaError_t e = cudaSuccess;
+    for (int i = 0; i < 2 && e == cudaSuccess; ++i) { e = dmalloc(&d_rays[i], chunk * sizeof(MtsbRay)); if (e == cudaSuccess) e = dmalloc(&d_hits[i], chunk * sizeof(MtsbHit)); }
+    const bool pin_in = is_pinned(rays), pin_out = is_pinned(hits);
+    const size_t n_chunks = (n + chunk - 1) / chunk;
+    auto drain = [&](size_t c) {                             // hits of chunk c: pinned staging -> caller memory
+        const int sl = (int) (c & 1);
+        const size_t first = c * chunk, cnt = std::min(chunk, n - first);
+        cudaError_t er = cudaEventSynchronize(p.ev_out[sl]);
+        if (er == cudaSuccess && !pin_out) parallel_copy(hits + first, p.pin_hits[sl], cnt * sizeof(MtsbHit));
+        return er;
+    };
+    for (size_t c = 0; c < n_chunks && e == cudaSuccess && rc == MTSB_OK; ++c) {
+        const int sl = (int) (c & 1);
+        const size_t first = c * chunk, cnt = std::min(chunk, n - first);
+        if (c >= 2) e = drain(c - 2);                        // slot `sl` is free again once its previous hits have left
+        if (e != cudaSuccess) break;
+        const MtsbRay *src = rays + first;
+        if (!pin_in) { parallel_copy(p.pin_rays[sl], src, cnt * sizeof(MtsbRay)); src = p.pin_rays[sl]; }
+        e = cudaMemcpyAsync(d_rays[sl], src, cnt * sizeof(MtsbRay), cudaMemcpyHostToDevice, p.s_in);
+        if (e == cudaSuccess) e = cudaEventRecord(p.ev_in[sl], p.s_in);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(s->stream, p.ev_in[sl], 0);
+        if (e != cudaSuccess) break;
+        rc = launch_trace(s, (const RayIn *) d_rays[sl], nullptr, (uint32_t) cnt, mode, (HitOut *) d_hits[sl], s->stream);
+        if (rc != MTSB_OK) break;
+        e = cudaEventRecord(p.ev_k[sl], s->stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(p.s_out, p.ev_k[sl], 0);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(pin_out ? (void *) (hits + first) : (void *) p.pin_hits[sl], d_hits[sl], cnt * sizeof(MtsbHit), cudaMemcpyDeviceToHost, p.s_out);
+        if (e == cudaSuccess) e = cudaEventRecord(p.ev_out[sl], p.s_out);
+    }
+    if (e == cudaSuccess && rc == MTSB_OK) {
+        if (n_chunks >= 2) e = drain(n_chunks - 2);
+        if (e == cudaSuccess) e = drain(n_chunks - 1);
+    }
+    cudaStreamSynchronize(p.s_in); cudaStreamSynchronize(s->stream); cudaStreamSynchronize(p.s_out);     // nothing in flight when the blocks go back to the cache
+    for (int i = 0; i < 2; ++i) { dfree(d_rays[i]); dfree(d_hits[i]); }
+    if (rc != MTSB_OK) return rc;
     if (e != cudaSuccess) return cuda_fail(e, "mtsb_trace", __FILE__, __LINE__);
-    return rc;
+    return check_stack_overflow("mtsb_trace");
 }
 
 extern "C" int mtsb_gen_rays_device(mtsb_scene_t scene, int kind, size_t n, uint64_t seed, void *d_rays) {

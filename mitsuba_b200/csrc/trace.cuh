@@ -17,6 +17,11 @@ namespace mtsb {
 #define MTSB_LOCAL_STACK 56    /* overflow entries per thread in local memory      */
 #define MTSB_REFILL 26         /* refill a warp when fewer lanes than this are busy */
 
+// Pushes that found the stack full (MTSB_SM_STACK + MTSB_LOCAL_STACK = 64 entries; one entry per level of the wide tree at
+// most, so only a pathologically deep tree gets here).  A dropped entry would silently lose a subtree, so the entry points
+// read this counter after their launches and fail with MTSB_ERR_CUDA.  One copy per translation unit (no -rdc).
+static __device__ unsigned int g_stack_overflow;
+
 // Shared-memory short stack with local-memory overflow.
 struct SmemStack {
     uint2 *sm;                       // this thread's column: sm[i * MTSB_TRACE_BLOCK]
@@ -29,6 +34,7 @@ struct SmemStack {
     __device__ __forceinline__ void push(uint32_t x, uint32_t y) {
         if (sp < MTSB_SM_STACK) sm[sp * MTSB_TRACE_BLOCK] = make_uint2(x, y);
         else if (sp < MTSB_SM_STACK + MTSB_LOCAL_STACK) loc[sp - MTSB_SM_STACK] = make_uint2(x, y);
+        else atomicAdd(&g_stack_overflow, 1u);
         ++sp;
     }
     __device__ __forceinline__ void pop(uint32_t &x, uint32_t &y) {
@@ -56,19 +62,22 @@ struct TraceArgs {
 // the ray: every lane hands the triangles of its next hit leaf to a per-warp queue in shared memory, and when 32 tests
 // are queued (or nothing else can make progress) the warp runs ONE triangle phase in which lane j tests queue entry j
 // -- any ray's triangle -- against that ray's origin / direction / interval, which every lane keeps in shared memory.
-// Hits go back to the owning lane through a 64-bit shared-memory minimum over (t, record), so a ray that is hit by
-// several triangles of one phase keeps the nearest, exactly as the sequential order would.  The arithmetic per
+// Hits go back to the owning lane through a 64-bit shared-memory minimum over (t, record, tester lane), so a ray that is
+// hit by several triangles of one phase keeps the nearest, exactly as the sequential order would; the tester leaves the
+// hit record (u, v, t, prim) in shared memory, where the owner picks it up.  The arithmetic per
 // triangle is unchanged (tri_test with the owner's current [mint, maxt]).
 #define MTSB_TQ_CAP 128            /* queue entries per warp: < 32 are left after the triangle phases, <= 96 are added per iteration */
 #ifndef MTSB_TQ_FLUSH
 #define MTSB_TQ_FLUSH 24           /* run a triangle phase when this many tests are queued (<= 32; 24 measured best)                                */
 #endif
-#define MTSB_TQ_OWNER_SHIFT 27     /* entry = owner lane << 27 | triangle record index (2^27 records)                              */
+#define MTSB_TQ_OWNER_SHIFT 27     /* entry = owner lane << 27 | triangle record index (2^27 records = 134 M triangles)           */
 
 struct WarpShared {
     uint32_t tq[MTSB_TQ_CAP];
     float4 ro[32], rd[32];         // the lanes' rays: (origin, mint), (direction, maxt); maxt follows the accepted hits
-    unsigned long long best[32];   // per owner: min over (ordered t << 32 | record) of the hits of one triangle phase
+    unsigned long long best[32];   // per owner: min over (ordered t << 32 | record << 5 | tester lane) of the hits of one triangle phase
+    float4 cand[32];               // per tester lane: (u, v, t, prim) of the hit it found in the current phase
+    float4 hit[32];                // per owner: record of the accepted hit (copied from the winning tester's cand)
 };
 
 __device__ __forceinline__ uint32_t order_float(float f) { const uint32_t u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
@@ -143,7 +152,9 @@ __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_MIN_CTAS) k_trace
             __syncwarp();
             // (b) every lane with a pending batch hands the triangles of ONE hit leaf (1..3) to the warp's queue
             uint32_t rec0 = 0, cnt = 0;
-            if (active && tr.tw != 0) tr.next_leaf(rec0, cnt);
+            const bool have_leaf = active && tr.tw != 0;
+            if (__any_sync(0xFFFFFFFFu, have_leaf)) {
+            if (have_leaf) tr.next_leaf(rec0, cnt);
             const unsigned b1 = __ballot_sync(0xFFFFFFFFu, cnt & 1u), b2 = __ballot_sync(0xFFFFFFFFu, cnt & 2u);
             if (cnt) {
                 const uint32_t pos = qtail + (uint32_t) __popc(b1 & lt) + 2u * (uint32_t) __popc(b2 & lt);
@@ -154,6 +165,7 @@ __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_MIN_CTAS) k_trace
                 my_last = pos + cnt;
             }
             qtail += (uint32_t) __popc(b1) + 2u * (uint32_t) __popc(b2);
+            }
             // (c) triangle phase: when a full warp of tests is queued, or when nothing else can make progress
             const bool other_work = __any_sync(0xFFFFFFFFu, active && (tr.tw != 0 || tr.wants_node()));
             while (qtail - qhead >= (uint32_t) MTSB_TQ_FLUSH || (qtail != qhead && !other_work)) {
@@ -166,29 +178,27 @@ __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_MIN_CTAS) k_trace
                     const U4 *tp = a.tris + 3 * (size_t) rec;
                     const U4 q0 = ld16(tp), q1 = ld16(tp + 1), q2 = ld16(tp + 2);
                     float u, v, t;
-                    if (tri_test(q0, q1, q2, ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, ro.w, rd.w, u, v, t))
-                        atomicMin(&ws.best[owner], ((unsigned long long) order_float(t) << 32) | rec);
+                    if (tri_test(q0, q1, q2, ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, ro.w, rd.w, u, v, t)) {
+                        ws.cand[lane] = make_float4(u, v, t, __uint_as_float(q2.z));
+                        atomicMin(&ws.best[owner], ((unsigned long long) order_float(t) << 32) | ((unsigned long long) rec << 5) | lane);
+                    }
                 }
                 qhead += nq;
                 __syncwarp();
                 const unsigned long long b = ws.best[lane];
                 if (b != ~0ull) {                       // this lane's ray was hit in the phase: the nearest hit is the new interval end
                     ws.best[lane] = ~0ull;
-                    tr.hit_rec = (uint32_t) b;
+                    const float4 c = ws.cand[(uint32_t) b & 31u];                          // the winning tester's record (bit-identical to tri_eval's)
+                    ws.hit[lane] = c;
+                    tr.hit_rec = 0;                                                         // "has a hit"
                     if (ANY) { tr.ng_y = 0; tr.stack.reset(); tr.tw = 0; tr.tw2 = 0; }      // satisfied: only its queued tests remain to drain
-                    else { tr.tmax = unorder_float((uint32_t) (b >> 32)); ws.rd[lane].w = tr.tmax; }
+                    else { tr.tmax = c.z; ws.rd[lane].w = c.z; }
                 }
             }
             // (d) a ray is finished when it has no nodes, no leaves to hand out and no test left in the queue
             if (active && tr.tw == 0 && !tr.has_nodes() && (int32_t) (qhead - my_last) >= 0) {
                 HitOut h; h.prim = MTSB_NO_HIT_ID; h.u = 0; h.v = 0; h.t = MTSB_INF;
-                if (tr.hit_rec != MTSB_NO_HIT_ID) {
-                    const float4 ro = ws.ro[lane], rd = ws.rd[lane];
-                    const U4 *tp = a.tris + 3 * (size_t) tr.hit_rec;
-                    const U4 q0 = ld16(tp), q1 = ld16(tp + 1), q2 = ld16(tp + 2);
-                    tri_eval(q0, q1, q2, ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, h.u, h.v, h.t);
-                    h.prim = q2.z;
-                }
+                if (tr.hit_rec != MTSB_NO_HIT_ID) { const float4 c = ws.hit[lane]; h.u = c.x; h.v = c.y; h.t = c.z; h.prim = __float_as_uint(c.w); }
                 ep(ray_idx, h);
                 active = false;
             }
@@ -226,6 +236,19 @@ int launch_trace_kernel(Scene *s, const RayIn *d_rays, const uint32_t *d_count, 
     k_trace<ANY, Epilogue><<<grid, MTSB_TRACE_BLOCK, 0, st>>>(a, ep);
     s->launches++;
     MTSB_CUDA(cudaGetLastError());
+    return MTSB_OK;
+}
+
+// reads and clears this translation unit's overflow counter (call after the stream that ran k_trace has been synchronised)
+static inline int check_stack_overflow(const char *who) {
+    unsigned int n = 0;
+    MTSB_CUDA(cudaMemcpyFromSymbol(&n, g_stack_overflow, sizeof(n)));
+    if (n) {
+        const unsigned int zero = 0;
+        cudaMemcpyToSymbol(g_stack_overflow, &zero, sizeof(zero));
+        set_error(std::string(who) + ": traversal stack overflow (the BVH is deeper than 64 levels); results would be incomplete");
+        return MTSB_ERR_CUDA;
+    }
     return MTSB_OK;
 }
 

@@ -93,8 +93,8 @@ private:
     MtsbMaterial record(std::vector<MtsbTexture> &tex) const;
     MtsbMaterial m_rec;
     // textures given as children: slot 0 replaces MtsbMaterial::reflectance, slot 1 ::transmittance
-    std::shared_ptr<Texture> m_tex[2];
-    Vec3 m_texScale[2] = {Vec3{1, 1, 1}, Vec3{1, 1, 1}};      // ensureEnergyConservation's factor
+    std::shared_ptr<Texture> m_tex[3];                         // reflectance-like, transmittance-like, roughness `alpha`
+    Vec3 m_texScale[3] = {Vec3{1, 1, 1}, Vec3{1, 1, 1}, Vec3{1, 1, 1}};      // ensureEnergyConservation's factor (slots 0, 1)
     bool m_twosided = false;
     std::vector<std::shared_ptr<Bsdf>> m_nested;
 };

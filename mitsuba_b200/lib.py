@@ -135,6 +135,10 @@ class Scene:
         _check(lib().mtsb_trace(self.h, _vp(rays), rays.shape[0], mode, _vp(hits)))
         return hits
 
+    def trace_into(self, rays_ptr, n, hits_ptr, mode=abi.TRACE_CLOSEST):
+        """mtsb_trace on caller-owned host buffers given by address (e.g. pinned memory): no allocation in the binding."""
+        _check(lib().mtsb_trace(self.h, C.c_void_p(rays_ptr), int(n), mode, C.c_void_p(hits_ptr)))
+
     def trace_static(self, rays, mode=abi.TRACE_CLOSEST):
         """mtsb_trace_static: the same query with all scratch in a fixed device array (no allocation; n <= 262144)."""
         rays = np.ascontiguousarray(rays, dtype=abi.RAY_DTYPE)

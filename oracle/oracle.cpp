@@ -113,8 +113,11 @@ V3 Li(const Scene &sc, const MtsbRay &primary, Rng &rng, Counters &cnt, float &a
 
     while (depth <= maxDepth || maxDepth < 0) {
         if (!its.valid) {
-            if (emittedRadiance && (!hideEmitters || scattered) && sc.envEmitter >= 0)
-                L += throughput * evalEnvironment(sc, V3(ray.d[0], ray.d[1], ray.d[2]));   // path.cpp:141-143
+            if (emittedRadiance && (!hideEmitters || scattered) && sc.envEmitter >= 0) {
+                const V3 dir(ray.d[0], ray.d[1], ray.d[2]);
+                // the camera ray still carries its differentials here (path.cpp:141-143; they are dropped at :223)
+                L += throughput * ((depth == 1 && !scattered && rxd) ? evalEnvironmentFiltered(sc, dir, *rxd, *ryd) : evalEnvironment(sc, dir));
+            }
             break;
         }
         const MtsbShape &shape = sc.shapes[its.shape];
@@ -254,7 +257,8 @@ int orc_scene_create(const MtsbSceneDesc *d, void **out) {
     {   // BSDF::usesRayDifferentials(): true when one of its textures is a bitmap (bitmap.cpp:547-549; twosided.cpp:98-99)
         auto bitmapTex = [&](const MtsbMaterial &m) {
             return (m.tex_reflectance && sc->textures[m.tex_reflectance - 1].rec.type == MTSB_TEX_BITMAP) ||
-                   (m.tex_transmittance && sc->textures[m.tex_transmittance - 1].rec.type == MTSB_TEX_BITMAP); };
+                   (m.tex_transmittance && sc->textures[m.tex_transmittance - 1].rec.type == MTSB_TEX_BITMAP) ||
+                   (m.tex_alpha && sc->textures[m.tex_alpha - 1].rec.type == MTSB_TEX_BITMAP); };
         sc->shapeNeedsPartials.assign(d->n_shapes, false);
         for (uint32_t s = 0; s < d->n_shapes; ++s) {
             const int m = sc->shapes[s].material;

@@ -125,6 +125,7 @@ struct Envmap {
     std::vector<float> cdfRows, cdfCols, rowWeights;
     float normalization = 0, scale = 1; P2 pixelSize{0, 0};
     float toWorld[16], toLocal[16];
+    MipMap mip;                               // the MIPMap the reference builds over the map (envmap.cpp:140-178): EWA, repeat / clamp, maxAnisotropy 10
     bool present() const { return w > 0; }
     // MIPMap::evalTexel (mipmap.h:503-563), ERepeat in u, EClamp in v
     V3 evalTexel(int x, int y) const {
@@ -148,6 +149,14 @@ struct Envmap {
         std::memcpy(toWorld, em.to_world, sizeof(toWorld)); std::memcpy(toLocal, em.to_local, sizeof(toLocal));
         texels.resize((size_t) 3 * w * h);
         for (size_t i = 0; i < texels.size(); ++i) texels[i] = floatToHalf(em.rgb[i]);
+        {   // the MIP pyramid for filtered lookups (envmap.cpp:140-178)
+            MtsbTexture mt;
+            std::memset(&mt, 0, sizeof(mt));
+            mt.type = MTSB_TEX_BITMAP; mt.filter = MTSB_TEXFILTER_EWA; mt.wrap_u = MTSB_WRAP_REPEAT; mt.wrap_v = MTSB_WRAP_CLAMP;
+            mt.uv_scale[0] = mt.uv_scale[1] = 1.0f; mt.scale[0] = mt.scale[1] = mt.scale[2] = 1.0f;
+            mt.max_anisotropy = 10.0f; mt.width = w; mt.height = h; mt.channels = 3; mt.texels = em.rgb;
+            mip.build(mt);
+        }
         size_t nEntries = (size_t) (w + 1) * (size_t) h;
         cdfCols.assign(nEntries, 0); cdfRows.assign((size_t) h + 1, 0); rowWeights.assign((size_t) h, 0);
         size_t colPos = 0, rowPos = 0;
@@ -225,6 +234,15 @@ struct Envmap {
         V3 v = xf(toLocal, dWorld);
         P2 uv{std::atan2(v.x, -v.z) * kInvTwoPi, std::acos(std::min(1.0f, std::max(-1.0f, v.y))) * kInvPi};
         return evalBilinear(uv) * scale;
+    }
+    // evalEnvironment for a ray with differentials (envmap.cpp:393-407): rxd / ryd = directions of the offset rays
+    V3 evalFiltered(V3 dWorld, V3 rxd, V3 ryd) const {
+        V3 v = xf(toLocal, dWorld);
+        P2 uv{std::atan2(v.x, -v.z) * kInvTwoPi, std::acos(std::min(1.0f, std::max(-1.0f, v.y))) * kInvPi};
+        V3 dvdx = xf(toLocal, rxd) - v, dvdy = xf(toLocal, ryd) - v;
+        float t1 = kInvTwoPi / (v.x * v.x + v.z * v.z), t2 = -kInvPi / std::max(std::sqrt(std::max(0.0f, 1.0f - v.y * v.y)), kEpsilon);
+        P2 dudx{t1 * (dvdx.z * v.x - dvdx.x * v.z), t2 * dvdx.y}, dudy{t1 * (dvdy.z * v.x - dvdy.x * v.z), t2 * dvdy.y};
+        return mip.eval(uv, dudx, dudy) * scale;
     }
     static V3 xf(const float *m, V3 v) {
         return V3(m[0] * v.x + m[1] * v.y + m[2] * v.z, m[4] * v.x + m[5] * v.y + m[6] * v.z, m[8] * v.x + m[9] * v.y + m[10] * v.z);
@@ -438,6 +456,11 @@ inline float emitterPdfDirect(const Scene &sc, int ei, const DRec &dRec) {
     }
 }
 
+// Scene::evalEnvironment for a ray that carries differentials (a camera ray): envmap.cpp:393-407 filters the lookup
+inline V3 evalEnvironmentFiltered(const Scene &sc, V3 d, V3 rxd, V3 ryd) {
+    const MtsbEmitter &e = sc.emitters[sc.envEmitter];
+    return e.type == MTSB_EMITTER_ENVMAP ? sc.envmap.evalFiltered(d, rxd, ryd) : rgb(e.radiance);
+}
 // Scene::evalEnvironment (scene.h:914-917)
 inline V3 evalEnvironment(const Scene &sc, V3 d) {
     const MtsbEmitter &e = sc.emitters[sc.envEmitter];
@@ -509,6 +532,11 @@ inline int resolveMaterials(const Scene &sc, int mat, const Its &its, MtsbMateri
     if ((lm[0].flags & MTSB_MAT_TWOSIDED) && lm[0].back >= 0) { lm[1] = sc.materials[lm[0].back]; lm[0].back = 1; n = 2; }
     for (int i = 0; i < n; ++i) {
         if (lm[i].tex_reflectance) { V3 v = sc.textures[lm[i].tex_reflectance - 1].eval(its.uv, pt); lm[i].reflectance[0] = v.x; lm[i].reflectance[1] = v.y; lm[i].reflectance[2] = v.z; }
+        if (lm[i].tex_alpha) {         // roughconductor.cpp:379-384, roughdielectric.cpp:300-305; clamp of microfacet.h:135-136
+            V3 v = sc.textures[lm[i].tex_alpha - 1].eval(its.uv, pt);
+            float a = std::max((v.x + v.y + v.z) * (1.0f / 3.0f), 1e-4f);
+            lm[i].alpha_u = a; lm[i].alpha_v = a;
+        }
         if (lm[i].tex_transmittance) { V3 v = sc.textures[lm[i].tex_transmittance - 1].eval(its.uv, pt); lm[i].transmittance[0] = v.x; lm[i].transmittance[1] = v.y; lm[i].transmittance[2] = v.z; }
     }
     return 0;

@@ -61,14 +61,14 @@ def check_render(gpu_lib, oracle_mod, b, spp, ref_spp, label):
     return e_gpu, e_cpu
 
 
-def check_same_stream(gpu_lib, oracle_mod, b, spp, label, seed=9):
+def check_same_stream(gpu_lib, oracle_mod, b, spp, label, seed=9, rtol=1e-3):
     """GPU film == oracle film when both draw the same random numbers."""
     sc, orc = gpu_lib.Scene(b), oracle_mod.Oracle(b)
     st = sc.render(spp=spp, seed=seed)
     fg = sc.film_download().astype(np.float64)
     ost = orc.render(spp=spp, seed=seed, counter_rng=True)
     fo = orc.film_download().astype(np.float64)
-    bad = (np.abs(fg - fo) > 1e-3 * np.maximum(np.abs(fo), 1e-3))[..., :3].any(-1)
+    bad = (np.abs(fg - fo) > rtol * np.maximum(np.abs(fo), 1e-3))[..., :3].any(-1)
     assert bad.mean() <= 2e-3, (label, int(bad.sum()), bad.size)
     assert rel_mse(sc.film_develop().astype(np.float64), orc.film_develop().astype(np.float64)) < 1e-5
     assert st.samples == ost.samples
@@ -312,6 +312,34 @@ def test_same_stream_envmap(gpu_lib, oracle_mod):
     check_same_stream(gpu_lib, oracle_mod, b, 4, "mixed + envmap")
 
 
+def test_same_stream_envmap_minified_sky_is_filtered(gpu_lib, oracle_mod):
+    """A sky map much finer than the image (1024 x 512 texels behind 64 x 36 pixels): camera rays that escape carry
+    differentials, so the reference filters the lookup through MIPMap::eval (envmap.cpp:393-407: EWA on the Lanczos
+    pyramid).  The film equals the oracle's under the same random numbers, and differs from an unfiltered lookup."""
+    def scene(res):
+        b = scenes.scene_10m(nu=24, nv=12, n_obj=12, width=64, height=36, spp=4)
+        b.emitters = [e for e in b.emitters if e.type != abi.EMITTER_CONSTANT]
+        sky = scenes.synthetic_sky(res, res // 2, sun=False)
+        yy, xx = np.mgrid[0:res // 2, 0:res]
+        sky = sky * (0.25 + 1.5 * ((xx // 2 + yy // 2) % 2))[..., None].astype(np.float32)      # 2-texel checker: aliases unless filtered
+        b.add_envmap(sky.astype(np.float32), scale=0.8)
+        return b
+    b = scene(1024)
+    # per-pixel tolerance 1 %: the EWA loop indexes its 64-entry weight table with (int) q, and q (a quadratic form of the
+    # texel offset) differs by an ulp between the device (FMA contraction) and the strict-IEEE oracle, so a texel now and
+    # then takes the neighbouring table entry -- visible on this map because neighbouring texels differ by a factor of 7
+    check_same_stream(gpu_lib, oracle_mod, b, 4, "minified envmap", rtol=1e-2)
+    # the filter matters here: unfiltered lookups (4 per pixel into a checker whose texels differ by a factor of 7) would
+    # make neighbouring sky pixels jump by tens of percent; through the pyramid they vary smoothly
+    sc = gpu_lib.Scene(b)
+    sc.render(spp=4, seed=9)
+    row = sc.film_develop().astype(np.float64)[0].sum(axis=1)            # top image row: sky
+    sc.close()
+    row = row[row > 0.05 * row.max()]
+    jump = np.abs(np.diff(row)) / (row[1:] + row[:-1])
+    assert len(row) > 32 and np.median(jump) < 0.15, float(np.median(jump))      # measured 0.067 (the sky carries 10 % texel noise); unfiltered: > 0.3
+
+
 def test_envmap_halton_same_sequence(gpu_lib, oracle_mod):
     b = _sky_scene(width=96, height=54, spp=4)
     b.set_sampler("halton", sample_count=4)
@@ -329,6 +357,24 @@ def test_same_stream_textured_cbox(gpu_lib, oracle_mod):
     MIP levels on camera-ray hits, level-0 bilinear on every later hit), the left wall's is magnified."""
     b = scenes.cbox_textured(width=96, height=72, spp=4, max_depth=6)
     check_same_stream(gpu_lib, oracle_mod, b, 4, "textured cbox")
+
+
+def test_same_stream_textured_roughness(gpu_lib, oracle_mod):
+    """Textured `alpha` (roughconductor.cpp:379-384, roughdielectric.cpp:300-305): the roughness of a rough conductor and of
+    a rough dielectric block comes from a checkerboard / a bitmap evaluated at the hit; films equal the oracle's."""
+    from mitsuba_b200.scenedesc import roughconductor, roughdielectric
+    b = scenes.cbox_textured(width=72, height=54, spp=4)
+    rough = scenes.pattern_image(32, 32, seed=9)[:, :, 0] * np.float32(0.5) + np.float32(0.02)
+    mc = roughconductor(*scenes.METALS["Cu"], alpha=0.1, distribution="ggx")
+    mc.tex_alpha = b.add_checkerboard(0.05, 0.45, uscale=3, vscale=3)
+    md = roughdielectric(1.5, 1.0, alpha=0.1, distribution="beckmann")
+    md.tex_alpha = b.add_bitmap(rough, "bilinear", "repeat", uscale=2, vscale=2)
+    ic, idl = b.add_material(mc), b.add_material(md)
+    uv4 = np.float32([[0, 0], [1, 0], [1, 1], [0, 1]])
+    for (x0, z0, m) in ((80.0, 60.0, ic), (330.0, 90.0, idl)):
+        pts = np.float32([(x0, 200, z0), (x0 + 150, 200, z0), (x0 + 150, 260, z0 + 150), (x0, 260, z0 + 150)])
+        b.add_mesh(pts, np.array([[0, 1, 2], [0, 2, 3]], np.uint32), m, texcoords=uv4)
+    check_same_stream(gpu_lib, oracle_mod, b, 4, "textured roughness")
 
 
 def test_textured_cbox_halton_same_sequence_and_passes(gpu_lib, oracle_mod):

@@ -186,3 +186,37 @@ def test_full_size_10m_properties_and_brute_force(gpu_lib):
         agree = (bp[both] == gp[both]).float().mean().item()
         assert agree > 0.97, agree            # different primitive only at shared edges (equal t within rounding)
     sc.close()
+
+
+def test_many_triangles_sharing_one_centroid(gpu_lib, oracle_mod):
+    """100 000 triangles with the SAME centroid: identical Morton keys (the radix tree falls back to the index
+    tie-break), maximal overlap, long leaf chains.  Hits must equal the oracle's and the traversal stack must not
+    overflow (an overflow is reported as an error, never as a silently missing subtree)."""
+    from mitsuba_b200.scenedesc import SceneBuilder, diffuse
+    rng = np.random.default_rng(21)
+    n = 100000
+    tri = rng.normal(size=(n, 3, 3)) * rng.uniform(0.05, 1.0, (n, 1, 1))
+    tri -= tri.mean(axis=1, keepdims=True)                     # every centroid at the origin
+    b = SceneBuilder()
+    b.add_mesh(tri.reshape(-1, 3).astype(np.float32), np.arange(n * 3, dtype=np.uint32).reshape(-1, 3), b.add_material(diffuse(0.5)))
+    sc = gpu_lib.Scene(b)
+    rays = scenes.chord_rays([0, 0, 0], 3.0, 3000, seed=4)
+    got = sc.trace(rays)
+    ref = oracle_mod.Oracle(b).trace(rays)
+    st = util.compare_hits(got, ref, label="one centroid", max_degenerate_frac=5e-3)
+    assert st["hit_frac"] > 0.5
+    sc.close()
+
+
+def test_invalid_indices_are_rejected(gpu_lib):
+    """A description whose triangle indices leave the shape's vertex range is refused (MTSB_ERR_INVALID), not traced."""
+    from mitsuba_b200.scenedesc import SceneBuilder, diffuse
+    b = SceneBuilder()
+    m = b.add_material(diffuse(0.5))
+    b.add_quad((-1, 0, -1), (-1, 0, 1), (1, 0, 1), (1, 0, -1), m)
+    b.add_quad((-1, 1, -1), (-1, 1, 1), (1, 1, 1), (1, 1, -1), m)
+    b._idx[1] = b._idx[1].copy()
+    b._idx[1][0, 0] = 0                                        # second shape points into the first shape's vertices
+    with pytest.raises(gpu_lib.MtsbError) as e:
+        gpu_lib.Scene(b)
+    assert e.value.code == abi.ERR_INVALID

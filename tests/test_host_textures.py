@@ -209,7 +209,7 @@ def test_bitmap_property_errors(tmp_path):
                  '<string name="%s" value="%s"/></texture></bsdf></shape>' % (tmp_path / "a.pfm", prop, val))
         assert msg in str(e.value)
     with pytest.raises(MtsbError) as e:
-        load('<shape type="rectangle"><bsdf type="roughconductor"><texture type="checkerboard" name="alpha"/></bsdf></shape>')
+        load('<shape type="rectangle"><bsdf type="roughconductor"><texture type="checkerboard" name="alphaV"/></bsdf></shape>')
     assert "not part of the B200 path" in str(e.value)
 
 
@@ -306,3 +306,17 @@ def test_oracle_renders_the_loaded_scene_like_the_builder_scene(tmp_path):
     f2 = o2.film_download()
     assert np.isfinite(f1).all() and f1[..., :3].max() > 0.05
     assert np.array_equal(f1, f2)
+
+
+def test_textured_roughness_goes_to_the_alpha_slot():
+    """<texture name="alpha"> on a rough BSDF (roughconductor.cpp:241-247): the third texture slot of the record; a constant
+    under a `scale` stays a constant roughness; separately textured alphaU / alphaV are refused."""
+    hs = load('<shape type="rectangle"><bsdf type="roughconductor"><string name="distribution" value="ggx"/>'
+              '<texture type="checkerboard" name="alpha"><spectrum name="color0" value="0.05"/><spectrum name="color1" value="0.4"/></texture>'
+              '</bsdf></shape>')
+    m = hs.materials()[0]
+    assert m.tex_alpha == 1 and m.tex_reflectance == 0 and hs.desc.n_textures == 1
+    t = hs.desc.textures[0]
+    assert t.type == abi.TEX_CHECKERBOARD and abs(t.color0[0] - 0.05) < 1e-7 and abs(t.color1[0] - 0.4) < 1e-7
+    with pytest.raises(MtsbError):
+        load('<shape type="rectangle"><bsdf type="roughdielectric"><texture type="checkerboard" name="alphaU"/></bsdf></shape>')
