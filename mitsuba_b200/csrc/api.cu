@@ -11,6 +11,8 @@
 #include <mutex>
 #include <cmath>
 #include <cstring>
+#include <thread>
+#include <algorithm>
 
 namespace mtsb {
 
@@ -120,6 +122,53 @@ void dcache_release() {
     std::lock_guard<std::mutex> g(c.m);
     for (auto &b : c.free_blocks) cudaFree(b.second);
     c.free_blocks.clear(); c.cached_bytes = 0;
+}
+
+// ---- staged uploads --------------------------------------------------------------------------------------------------
+// cudaMemcpy from pageable memory moves ~5 GB/s (the driver stages it through one bounce buffer on one thread).  Scene
+// arrays of a 10 M-triangle scene are ~300 MB, and mtsb_scene_create is inside the end-to-end step, so large arrays are
+// staged here: two pinned 32 MiB buffers per device, filled by a few host threads while the previous chunk is on the bus.
+namespace {
+struct Stager { bool ready = false; cudaStream_t st = nullptr; void *pin[2] = {nullptr, nullptr}; cudaEvent_t ev[2] = {nullptr, nullptr}; };
+std::mutex g_stager_mutex;
+std::map<int, Stager> g_stagers;
+const size_t kStageChunk = (size_t) 32 << 20;
+void stage_copy(void *dst, const void *src, size_t bytes) {
+    const int nt = 4;
+    if (bytes < ((size_t) 4 << 20)) { std::memcpy(dst, src, bytes); return; }
+    std::thread th[nt - 1];
+    const size_t part = (bytes / nt + 63) & ~(size_t) 63;
+    for (int t = 1; t < nt; ++t) {
+        const size_t off = (size_t) t * part;
+        if (off >= bytes) break;
+        th[t - 1] = std::thread([=] { std::memcpy((char *) dst + off, (const char *) src + off, std::min(part, bytes - off)); });
+    }
+    std::memcpy(dst, src, std::min(part, bytes));
+    for (auto &t : th) if (t.joinable()) t.join();
+}
+}  // namespace
+
+int staged_h2d(void *dst, const void *src, size_t bytes) {
+    if (bytes < ((size_t) 1 << 20)) { MTSB_CUDA(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice)); return MTSB_OK; }
+    int dev = 0; MTSB_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> g(g_stager_mutex);
+    Stager &sg = g_stagers[dev];
+    if (!sg.ready) {
+        MTSB_CUDA(cudaStreamCreateWithFlags(&sg.st, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) { MTSB_CUDA(cudaHostAlloc(&sg.pin[i], kStageChunk, cudaHostAllocDefault)); MTSB_CUDA(cudaEventCreateWithFlags(&sg.ev[i], cudaEventDisableTiming)); }
+        sg.ready = true;
+    }
+    size_t c = 0;
+    for (size_t off = 0; off < bytes; off += kStageChunk, ++c) {
+        const int sl = (int) (c & 1);
+        const size_t cnt = std::min(kStageChunk, bytes - off);
+        if (c >= 2) MTSB_CUDA(cudaEventSynchronize(sg.ev[sl]));
+        stage_copy(sg.pin[sl], (const char *) src + off, cnt);
+        MTSB_CUDA(cudaMemcpyAsync((char *) dst + off, sg.pin[sl], cnt, cudaMemcpyHostToDevice, sg.st));
+        MTSB_CUDA(cudaEventRecord(sg.ev[sl], sg.st));
+    }
+    MTSB_CUDA(cudaStreamSynchronize(sg.st));
+    return MTSB_OK;
 }
 
 int trace_grid(Scene *s, const void *kernel) {
@@ -240,6 +289,15 @@ __global__ void k_check_indices(const uint32_t *indices, const uint32_t *tri_sha
     if (!ok) atomicOr(bad, 1u);
 }
 
+__global__ void k_fill_tri_shape(const MtsbShape *shapes, uint32_t n_shapes, uint64_t n_tris, uint32_t *tri_shape) {
+    const uint64_t prim = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (prim >= n_tris) return;
+    uint32_t lo = 0, hi = n_shapes;                 // last shape with first_tri <= prim (empty shapes share a first_tri: take the one that owns it)
+    while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if ((uint64_t) shapes[mid].first_tri <= prim) lo = mid; else hi = mid; }
+    while (lo > 0 && shapes[lo].n_tris == 0) --lo;
+    tri_shape[prim] = lo;
+}
+
 static float rfilter_eval(const MtsbSensor &se, float x) {
     if (se.rfilter == MTSB_RFILTER_GAUSSIAN) {      // gaussian.cpp:50-55
         float alpha = -1.0f / (2.0f * se.rfilter_stddev * se.rfilter_stddev);
@@ -273,11 +331,16 @@ extern "C" int mtsb_scene_create(const MtsbSceneDesc *d, mtsb_scene_t *out) {
     s->h_shape_material.resize(d->n_shapes);
     for (uint32_t i = 0; i < d->n_shapes; ++i) s->h_shape_material[i] = d->shapes[i].material;
     if ((rc = dev_upload(s, &v.emitters, d->emitters, (size_t) d->n_emitters))) return fail(rc);
-    {   // primitive -> shape map (ShapeKDTree::findShape, skdtree.h:205-210, as a table)
-        std::vector<uint32_t> ts((size_t) d->n_tris);
-        for (uint32_t i = 0; i < d->n_shapes; ++i)
-            for (uint32_t j = 0; j < d->shapes[i].n_tris; ++j) ts[(size_t) d->shapes[i].first_tri + j] = i;
-        if ((rc = dev_upload(s, &v.tri_shape, ts.data(), ts.size()))) return fail(rc);
+    {   // primitive -> shape map (ShapeKDTree::findShape, skdtree.h:205-210, as a table), filled on the device: shapes tile
+        // the triangle array in order (validate()), so a primitive's shape is found by bisection over first_tri
+        uint32_t *ts = nullptr;
+        if ((rc = dev_alloc(s, &ts, (size_t) d->n_tris))) return fail(rc);
+        if (d->n_tris) {
+            k_fill_tri_shape<<<grid_for(d->n_tris, 256), 256, 0, s->stream>>>(v.shapes, d->n_shapes, d->n_tris, ts);
+            s->launches++;
+            if (cudaGetLastError() != cudaSuccess) return fail(MTSB_ERR_CUDA);
+        }
+        v.tri_shape = ts;
     }
     {   // emitter selection pmf (scene.cpp:375-381) and per-mesh area pmfs (trimesh.cpp:388-403)
         std::vector<float> cdf(1, 0.0f);

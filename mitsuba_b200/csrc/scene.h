@@ -46,11 +46,15 @@ template <class T> int dev_alloc(Scene *s, T **p, size_t count) {
     *p = static_cast<T *>(q);
     return MTSB_OK;
 }
+// host -> device copy of a caller-owned (usually pageable) array; large arrays go through pinned staging buffers filled by
+// several host threads, one cudaMemcpyAsync per chunk (api.cu).  Returns after the data has left the host array.
+int staged_h2d(void *dst, const void *src, size_t bytes);
+
 template <class T> int dev_upload(Scene *s, const T **p, const T *host, size_t count) {
     T *q = nullptr;
     int rc = dev_alloc(s, &q, count);
     if (rc) return rc;
-    if (count) MTSB_CUDA(cudaMemcpy(q, host, count * sizeof(T), cudaMemcpyHostToDevice));
+    if (count && (rc = staged_h2d(q, host, count * sizeof(T)))) return rc;
     *p = q;
     return MTSB_OK;
 }
