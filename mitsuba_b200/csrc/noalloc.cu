@@ -42,7 +42,7 @@ static int static_scratch(int device, unsigned char **out) {
 template <bool ANY>
 static int launch_static(Scene *s, const RayIn *d_rays, uint32_t n, HitOut *d_hits, uint32_t *d_counter) {
     TraceArgs a;
-    a.nodes = s->v.nodes; a.tris = s->v.tris; a.n_nodes = s->v.n_nodes;
+    a.nodes = s->v.nodes; a.tris = s->v.tris; a.n_nodes = s->v.n_nodes; a.n_tri_records = (uint32_t) s->info.n_tris;
     for (int k = 0; k < 3; ++k) { a.box_lo[k] = s->v.box_lo[k]; a.box_hi[k] = s->v.box_hi[k]; }
     a.rays = d_rays; a.d_count = nullptr; a.n_max = n;
     a.refill = MTSB_REFILL; a.prmt_bias = 0x47000000u;

@@ -39,6 +39,8 @@ namespace cg = cooperative_groups;
 namespace mtsb {
 
 #define MTSB_TILE 32
+// checked build: a film write must land inside the bordered film
+#define MTSB_CHECK_FILM(sc, X, Y) MTSB_CHECK((X) >= 0 && (Y) >= 0 && (X) < (sc).film_w + 2 * (sc).film_border && (Y) < (sc).film_h + 2 * (sc).film_border, CHK_FILM)
 #define MTSB_SHADE_BLOCK 128
 #ifndef MTSB_SHADE_MIN_BLOCKS
 #define MTSB_SHADE_MIN_BLOCKS 8      /* resident CTAs per SM the shading kernels' register allocation is held to (64 registers: the stage waits on
@@ -268,6 +270,7 @@ __global__ void __launch_bounds__(MTSB_SORT_BLOCK) k_sort(SceneView sc, PathBuff
         __syncthreads();
         if (threadIdx.x < Q_COUNT) s_base[threadIdx.x] = s_cnt[threadIdx.x] ? atomicAdd(&bc.n_q[threadIdx.x], s_cnt[threadIdx.x]) : 0u;
         __syncthreads();
+        MTSB_CHECK(which < 0 || s_base[which] + rank < pb.capacity, CHK_QUEUE);
         if (which >= 0) pb.q[which][s_base[which] + rank] = q;
     }
     for (int o = 16; o; o >>= 1) path_len += __shfl_xor_sync(0xFFFFFFFFu, path_len, o);
@@ -390,7 +393,9 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK, MTSB_SHADE_MIN_BLOCKS) k_sha
         uint32_t spawn_slot = 0xFFFFFFFFu;
         if (i < n) {
         const uint32_t q = pb.q[Q][i];
+        MTSB_CHECK(q < pb.capacity, CHK_QUEUE);
         const uint32_t slot = pb.ray_slot[cur][q];
+        MTSB_CHECK(slot < pb.capacity, CHK_SLOT);
         const RayIn ray = load_ray(pb.rays[cur], q);
         const uint4 hraw = reinterpret_cast<const uint4 *>(pb.hits)[q];
         const uint32_t prim = hraw.x; const float hu = __uint_as_float(hraw.y), hv = __uint_as_float(hraw.z), ht = __uint_as_float(hraw.w);
@@ -551,12 +556,14 @@ __global__ void __launch_bounds__(MTSB_SHADE_BLOCK, MTSB_SHADE_MIN_BLOCKS) k_sha
         const uint32_t lt = (1u << lane) - 1u;
         if (have_shadow) {
             const uint32_t sq = s_qbase[0] + s_wcnt[0][warp] + (uint32_t) __popc(b_s & lt);
+            MTSB_CHECK(sq < pb.capacity, CHK_QUEUE);
             reinterpret_cast<float4 *>(pb.srays)[2 * (size_t) sq] = s_sray[2 * threadIdx.x];
             reinterpret_cast<float4 *>(pb.srays)[2 * (size_t) sq + 1] = s_sray[2 * threadIdx.x + 1];
             pb.scontrib[sq] = s_contrib[threadIdx.x];
         }
         if (spawn_slot != 0xFFFFFFFFu) {
             const uint32_t nq = s_qbase[1] + s_wcnt[1][warp] + (uint32_t) __popc(b_r & lt);
+            MTSB_CHECK(nq < pb.capacity, CHK_QUEUE);
             reinterpret_cast<float4 *>(pb.rays[1 - cur])[2 * (size_t) nq] = s_nray[2 * threadIdx.x];
             reinterpret_cast<float4 *>(pb.rays[1 - cur])[2 * (size_t) nq + 1] = s_nray[2 * threadIdx.x + 1];
             pb.ray_slot[1 - cur][nq] = spawn_slot;
@@ -639,7 +646,9 @@ __global__ void __launch_bounds__(256) k_splat(SceneView sc, PathBuffers pb, Pas
                             for (int X = x0; X <= x1; ++X) {
                                 const float w = s_filter[min((int) fabsf(((float) X - pos.x) * f_scale), 31)] *
                                                 s_filter[min((int) fabsf(((float) Y - pos.y) * f_scale), 31)];
-                                float *dest = sc.film + ((size_t) (oy + Y) * fsx + (ox + X)) * 5;
+                                MTSB_CHECK_FILM(sc, ox + X, oy + Y);
+                                MTSB_CHECK_FILM(sc, ox + X, oy + Y);
+            float *dest = sc.film + ((size_t) (oy + Y) * fsx + (ox + X)) * 5;
                                 atomicAdd(dest, w * val.x); atomicAdd(dest + 1, w * val.y); atomicAdd(dest + 2, w * val.z);
                                 atomicAdd(dest + 3, w * val.w); atomicAdd(dest + 4, w);
                             }
@@ -672,6 +681,7 @@ __global__ void __launch_bounds__(256) k_splat(SceneView sc, PathBuffers pb, Pas
                                         s_filter[min((int) fabsf((Yf - pos.y) * f_scale), 31)];
                         acc[0] += w * val.x; acc[1] += w * val.y; acc[2] += w * val.z; acc[3] += w * val.w; acc[4] += w;
                     }
+            MTSB_CHECK_FILM(sc, ox + X, oy + Y);
             float *dest = sc.film + ((size_t) (oy + Y) * fsx + (ox + X)) * 5;
 #pragma unroll
             for (int k = 0; k < 5; ++k) if (acc[k] != 0.0f) atomicAdd(dest + k, acc[k]);
@@ -736,7 +746,9 @@ __global__ void __launch_bounds__(256) k_splat5(SceneView sc, PathBuffers pb, Pa
                             for (int X = x0; X <= x1; ++X) {
                                 const float w = s_filter[min((int) fabsf(((float) X - posx) * f_scale), 31)] *
                                                 s_filter[min((int) fabsf(((float) Y - posy) * f_scale), 31)];
-                                float *dest = sc.film + ((size_t) (oy + Y) * fsx + (ox + X)) * 5;
+                                MTSB_CHECK_FILM(sc, ox + X, oy + Y);
+                                MTSB_CHECK_FILM(sc, ox + X, oy + Y);
+            float *dest = sc.film + ((size_t) (oy + Y) * fsx + (ox + X)) * 5;
                                 atomicAdd(dest, w * val.x); atomicAdd(dest + 1, w * val.y); atomicAdd(dest + 2, w * val.z);
                                 atomicAdd(dest + 3, w * val.w); atomicAdd(dest + 4, w);
                             }
@@ -789,6 +801,7 @@ __global__ void __launch_bounds__(256) k_splat5(SceneView sc, PathBuffers pb, Pa
         const int p = (int) threadIdx.x + q * 256;
         if (p >= sx * sy) break;
         const int X = p % sx, Y = p / sx;
+        MTSB_CHECK_FILM(sc, ox + X, oy + Y);
         float *dest = sc.film + ((size_t) (oy + Y) * fsx + (ox + X)) * 5;
 #pragma unroll
         for (int k = 0; k < 5; ++k) if (acc[q][k] != 0.0f) atomicAdd(dest + k, acc[q][k]);

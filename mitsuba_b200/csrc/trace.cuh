@@ -22,6 +22,20 @@ namespace mtsb {
 // read this counter after their launches and fail with MTSB_ERR_CUDA.  One copy per translation unit (no -rdc).
 static __device__ unsigned int g_stack_overflow;
 
+// ---- checked build (-DMTSB_CHECKED) ------------------------------------------------------------------------------------
+// compute-sanitizer is closed on the pool this library is developed on, so the bounds a memcheck run would watch are
+// checked by the kernels themselves in a checked build: every queue write against the capacity of the path buffers, every
+// node / triangle-record fetch against the array sizes, the warp queue against its ring, film writes against the film.
+// A failed check bumps a counter (it does not stop the kernel); mtsb_render / mtsb_trace return MTSB_ERR_CUDA when any is
+// non-zero.  The shipped build compiles the checks away.  tools/checked_run.sh runs the test cases under the checked build.
+enum { CHK_QUEUE = 0, CHK_NODE, CHK_TRI, CHK_WARPQ, CHK_FILM, CHK_SLOT, CHK_N };
+#ifdef MTSB_CHECKED
+static __device__ unsigned int g_check_fail[CHK_N];
+#define MTSB_CHECK(cond, code) do { if (!(cond)) atomicAdd(&g_check_fail[code], 1u); } while (0)
+#else
+#define MTSB_CHECK(cond, code) do { } while (0)
+#endif
+
 // Shared-memory short stack with local-memory overflow.
 struct SmemStack {
     uint2 *sm;                       // this thread's column: sm[i * MTSB_TRACE_BLOCK]
@@ -46,6 +60,7 @@ struct SmemStack {
 
 struct TraceArgs {
     const U4 *nodes, *tris; uint32_t n_nodes;
+    uint32_t n_tri_records;      // checked build: number of 48-B triangle records
     float box_lo[3], box_hi[3];
     const RayIn *rays;
     const uint32_t *d_count;     // number of rays if non-null (device), else n_max
@@ -148,6 +163,14 @@ __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_MIN_CTAS) k_trace
         unsigned live;
         do {
             // (a) node phase: lanes with node work and a free batch slot visit one node
+#ifdef MTSB_CHECKED
+            if (active && tr.wants_node()) {     // the node the visit is about to fetch
+                uint32_t gx = tr.ng_x, gy = tr.ng_y;
+                if (gy <= 0x00FFFFFFu && tr.stack.sp > 0) { const int sp = tr.stack.sp - 1; const uint2 v = sp < MTSB_SM_STACK ? tr.stack.sm[sp * MTSB_TRACE_BLOCK] : tr.stack.loc[min(sp, MTSB_SM_STACK + MTSB_LOCAL_STACK - 1) - MTSB_SM_STACK]; gx = v.x; gy = v.y; }
+                const uint32_t slot = ((uint32_t) bfind(gy) - 24u) ^ tr.octinv;
+                MTSB_CHECK(gx + (uint32_t) __popc(gy & ~(0xFFFFFFFFu << slot) & 0xFFu) < a.n_nodes, CHK_NODE);
+            }
+#endif
             if (active && tr.wants_node()) tr.visit_node(a.nodes);
             __syncwarp();
             // (b) every lane with a pending batch hands the triangles of ONE hit leaf (1..3) to the warp's queue
@@ -165,6 +188,7 @@ __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_MIN_CTAS) k_trace
                 my_last = pos + cnt;
             }
             qtail += (uint32_t) __popc(b1) + 2u * (uint32_t) __popc(b2);
+            MTSB_CHECK(qtail - qhead <= (uint32_t) MTSB_TQ_CAP, CHK_WARPQ);
             }
             // (c) triangle phase: when a full warp of tests is queued, or when nothing else can make progress
             const bool other_work = __any_sync(0xFFFFFFFFu, active && (tr.tw != 0 || tr.wants_node()));
@@ -175,6 +199,7 @@ __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_MIN_CTAS) k_trace
                     const uint32_t e = ws.tq[(qhead + lane) & (MTSB_TQ_CAP - 1)];
                     const uint32_t owner = e >> MTSB_TQ_OWNER_SHIFT, rec = e & ((1u << MTSB_TQ_OWNER_SHIFT) - 1u);
                     const float4 ro = ws.ro[owner], rd = ws.rd[owner];
+                    MTSB_CHECK(rec < a.n_tri_records, CHK_TRI);
                     const U4 *tp = a.tris + 3 * (size_t) rec;
                     const U4 q0 = ld16(tp), q1 = ld16(tp + 1), q2 = ld16(tp + 2);
                     float u, v, t;
@@ -222,7 +247,7 @@ template <bool ANY, class Epilogue>
 int launch_trace_kernel(Scene *s, const RayIn *d_rays, const uint32_t *d_count, uint32_t n_max, Epilogue ep, cudaStream_t st) {
     if (n_max == 0) return MTSB_OK;
     TraceArgs a;
-    a.nodes = s->v.nodes; a.tris = s->v.tris; a.n_nodes = s->v.n_nodes;
+    a.nodes = s->v.nodes; a.tris = s->v.tris; a.n_nodes = s->v.n_nodes; a.n_tri_records = (uint32_t) s->info.n_tris;
     for (int k = 0; k < 3; ++k) { a.box_lo[k] = s->v.box_lo[k]; a.box_hi[k] = s->v.box_hi[k]; }
     a.rays = d_rays; a.d_count = d_count; a.n_max = n_max;
     { static int r = 0; if (!r) { const char *e = getenv("MTSB_REFILL"); r = e ? atoi(e) : MTSB_REFILL; } a.refill = r; }
@@ -249,6 +274,21 @@ static inline int check_stack_overflow(const char *who) {
         set_error(std::string(who) + ": traversal stack overflow (the BVH is deeper than 64 levels); results would be incomplete");
         return MTSB_ERR_CUDA;
     }
+#ifdef MTSB_CHECKED
+    unsigned int f[CHK_N];
+    MTSB_CUDA(cudaMemcpyFromSymbol(f, g_check_fail, sizeof(f)));
+    unsigned int tot = 0;
+    for (int i = 0; i < CHK_N; ++i) tot += f[i];
+    if (tot) {
+        char buf[256];
+        snprintf(buf, sizeof(buf), "%s: checked build: %u out-of-range queue writes, %u node fetches, %u triangle fetches, %u warp-queue overruns, %u film writes, %u slot indices",
+                 who, f[CHK_QUEUE], f[CHK_NODE], f[CHK_TRI], f[CHK_WARPQ], f[CHK_FILM], f[CHK_SLOT]);
+        const unsigned int zero[CHK_N] = {0};
+        cudaMemcpyToSymbol(g_check_fail, zero, sizeof(zero));
+        set_error(buf);
+        return MTSB_ERR_CUDA;
+    }
+#endif
     return MTSB_OK;
 }
 
