@@ -345,6 +345,8 @@ def run_b200_arm(args):
             "wall_s_timed_region": wall_s,
             "stage_ms_last_step": {"raygen": s0.ms_raygen, "trace_closest": s0.ms_trace_closest, "shade": s0.ms_shade,
                                    "trace_any": s0.ms_trace_any, "splat": s0.ms_splat, "total": s0.ms_total, "passes": s0.n_passes},
+            # rays in flight per bounce of the last step (this rank's tiles): closest-hit rays of bounce b (b = 0: camera rays), shadow rays made at bounce b
+            "rays_in_flight_per_bounce": {"closest": [int(x) for x in s0.closest_rays_bounce if x], "shadow": [int(x) for x in s0.shadow_rays_bounce if x]},
             "roofline": {"bound": "hbm", "kernel": "k_trace<closest>", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "traffic_note": traffic_note,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
