@@ -4,9 +4,9 @@ TAG=${1:-s}; WL=${2:-cfg2_10m}
 mkdir -p gpurun_out
 for N in 8 4 2 1; do
   if [ $N == 1 ]; then
-    timeout 900 python bench.py --gpus 1 --steps 3 --warmup 3 --workload $WL --no-cpu-baseline > gpurun_out/scale_${WL}_n${N}_$TAG.json 2> gpurun_out/scale_${WL}_n${N}_$TAG.err
+    timeout 900 python bench.py --gpus 1 --steps ${STEPS:-3} --warmup ${WARM:-3} --workload $WL --no-cpu-baseline > gpurun_out/scale_${WL}_n${N}_$TAG.json 2> gpurun_out/scale_${WL}_n${N}_$TAG.err
   else
-    timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $((29500+N)) bench.py --gpus $N --steps 3 --warmup 3 --workload $WL --no-cpu-baseline > gpurun_out/scale_${WL}_n${N}_$TAG.json 2> gpurun_out/scale_${WL}_n${N}_$TAG.err
+    timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $((29500+N)) bench.py --gpus $N --steps ${STEPS:-3} --warmup ${WARM:-3} --workload $WL --no-cpu-baseline > gpurun_out/scale_${WL}_n${N}_$TAG.json 2> gpurun_out/scale_${WL}_n${N}_$TAG.err
   fi
   python - <<PY
 import json
