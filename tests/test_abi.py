@@ -83,3 +83,31 @@ def test_host_render_refuses_without_gpu():
     with pytest.raises(lib.MtsbError) as ei:
         hs.render()
     assert ei.value.code == abi.ERR_NO_DEVICE
+
+
+def test_ctypes_mirror_matches_the_compiled_header(tmp_path):
+    """Every record that crosses the C ABI has the same size (and the statistics record the same field offsets) in the
+    ctypes mirror (mitsuba_b200/abi.py) as in include/mtsb200.h compiled by the C compiler."""
+    import subprocess
+    names = ["MtsbMaterial", "MtsbTexture", "MtsbShape", "MtsbEmitter", "MtsbEnvmap", "MtsbSensor", "MtsbIntegrator", "MtsbSampler",
+             "MtsbSceneDesc", "MtsbRay", "MtsbHit", "MtsbBsdfQuery", "MtsbBsdfResult", "MtsbDirectQuery", "MtsbDirectResult",
+             "MtsbRenderParams", "MtsbStats", "MtsbSceneInfo"]
+    src = '#include <stdio.h>\n#include <stddef.h>\n#include "mtsb200.h"\nint main(void) {\n'
+    src += "".join('  printf("%s %%zu\\n", sizeof(%s));\n' % (n, n) for n in names)
+    for f in ("n_passes", "closest_launches", "ms_reduce", "closest_rays_bounce", "shadow_rays_bounce"):
+        src += '  printf("MtsbStats.%s %%zu\\n", offsetof(MtsbStats, %s));\n' % (f, f)
+    src += '  printf("MtsbMaterial.tex_alpha %zu\\n", offsetof(MtsbMaterial, tex_alpha));\n  return 0;\n}\n'
+    (tmp_path / "sz.c").write_text(src)
+    subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), "-o", str(tmp_path / "sz"), str(tmp_path / "sz.c")])
+    got = dict(l.split() for l in subprocess.check_output([str(tmp_path / "sz")], text=True).splitlines())
+    mirror = {"MtsbMaterial": abi.Material, "MtsbTexture": abi.Texture, "MtsbShape": abi.Shape, "MtsbEmitter": abi.Emitter,
+              "MtsbEnvmap": abi.Envmap, "MtsbSensor": abi.Sensor, "MtsbIntegrator": abi.Integrator, "MtsbSampler": abi.Sampler,
+              "MtsbSceneDesc": abi.SceneDesc, "MtsbRenderParams": abi.RenderParams, "MtsbStats": abi.Stats, "MtsbSceneInfo": abi.SceneInfo}
+    for n, t in mirror.items():
+        assert C.sizeof(t) == int(got[n]), (n, C.sizeof(t), got[n])
+    for n, dt in (("MtsbRay", abi.RAY_DTYPE), ("MtsbHit", abi.HIT_DTYPE), ("MtsbBsdfQuery", abi.BSDF_QUERY_DTYPE), ("MtsbBsdfResult", abi.BSDF_RESULT_DTYPE),
+                  ("MtsbDirectQuery", abi.DIRECT_QUERY_DTYPE), ("MtsbDirectResult", abi.DIRECT_RESULT_DTYPE)):
+        assert dt.itemsize == int(got[n]), (n, dt.itemsize, got[n])
+    for f in ("n_passes", "closest_launches", "ms_reduce", "closest_rays_bounce", "shadow_rays_bounce"):
+        assert getattr(abi.Stats, f).offset == int(got["MtsbStats." + f]), f
+    assert abi.Material.tex_alpha.offset == int(got["MtsbMaterial.tex_alpha"])
