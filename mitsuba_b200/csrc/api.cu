@@ -129,7 +129,7 @@ void dcache_release() {
 // arrays of a 10 M-triangle scene are ~300 MB, and mtsb_scene_create is inside the end-to-end step, so large arrays are
 // staged here: two pinned 32 MiB buffers per device, filled by a few host threads while the previous chunk is on the bus.
 namespace {
-struct Stager { bool ready = false; cudaStream_t st = nullptr; void *pin[2] = {nullptr, nullptr}; cudaEvent_t ev[2] = {nullptr, nullptr}; };
+struct Stager { std::mutex m; bool ready = false; cudaStream_t st = nullptr; void *pin[2] = {nullptr, nullptr}; cudaEvent_t ev[2] = {nullptr, nullptr}; };
 std::mutex g_stager_mutex;
 std::map<int, Stager> g_stagers;
 const size_t kStageChunk = (size_t) 32 << 20;
@@ -151,8 +151,10 @@ void stage_copy(void *dst, const void *src, size_t bytes) {
 int staged_h2d(void *dst, const void *src, size_t bytes) {
     if (bytes < ((size_t) 1 << 20)) { MTSB_CUDA(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice)); return MTSB_OK; }
     int dev = 0; MTSB_CUDA(cudaGetDevice(&dev));
-    std::lock_guard<std::mutex> g(g_stager_mutex);
-    Stager &sg = g_stagers[dev];
+    Stager *sgp;
+    { std::lock_guard<std::mutex> g(g_stager_mutex); sgp = &g_stagers[dev]; }        // map nodes are stable; the copy itself is locked per device,
+    Stager &sg = *sgp;                                                              // so the per-GPU threads of mtsb_multi_create upload side by side
+    std::lock_guard<std::mutex> gd(sg.m);
     if (!sg.ready) {
         MTSB_CUDA(cudaStreamCreateWithFlags(&sg.st, cudaStreamNonBlocking));
         for (int i = 0; i < 2; ++i) { MTSB_CUDA(cudaHostAlloc(&sg.pin[i], kStageChunk, cudaHostAllocDefault)); MTSB_CUDA(cudaEventCreateWithFlags(&sg.ev[i], cudaEventDisableTiming)); }

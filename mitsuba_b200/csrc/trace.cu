@@ -85,6 +85,7 @@ extern "C" int mtsb_trace_device(mtsb_scene_t scene, const void *d_rays, size_t 
 
 namespace {
 struct TracePipe {
+    std::mutex m;
     bool ready = false;
     cudaStream_t s_in = nullptr, s_out = nullptr;
     MtsbRay *pin_rays[2] = {nullptr, nullptr}; MtsbHit *pin_hits[2] = {nullptr, nullptr};
@@ -133,8 +134,10 @@ extern "C" int mtsb_trace(mtsb_scene_t scene, const MtsbRay *rays, size_t n, int
     if (!s || (n && (!rays || !hits)) || (mode != MTSB_TRACE_CLOSEST && mode != MTSB_TRACE_ANY)) { set_error("mtsb_trace: bad argument"); return MTSB_ERR_INVALID; }
     if (n == 0) return MTSB_OK;
     MTSB_CUDA(cudaSetDevice(s->device));
-    std::lock_guard<std::mutex> g(g_pipe_mutex);             // one host-buffer query per process at a time: the staging buffers are shared
-    TracePipe &p = g_pipes[s->device];
+    TracePipe *pp;
+    { std::lock_guard<std::mutex> g(g_pipe_mutex); pp = &g_pipes[s->device]; }      // map nodes are stable
+    TracePipe &p = *pp;
+    std::lock_guard<std::mutex> gd(p.m);                     // one host-buffer query per DEVICE at a time: its staging buffers are shared
     int rc = pipe_init(p);
     if (rc) return rc;
     const size_t chunk = std::min<size_t>(n, MTSB_TRACE_CHUNK);
