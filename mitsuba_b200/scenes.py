@@ -163,8 +163,12 @@ def parametric_object(nu, nv, kind, rng, radius=1.0):
     i0 = (np.arange(nu)[:, None] * (nv + 1) + np.arange(nv)[None, :])
     i1 = (((np.arange(nu) + 1) % nu)[:, None] * (nv + 1) + np.arange(nv)[None, :])
     a, b_, c, d = i0, i1, i1 + 1, i0 + 1
-    # winding chosen so that the face normal points outward for both families
-    tris = np.concatenate([np.stack([a, c, b_], -1).reshape(-1, 3), np.stack([a, d, c], -1).reshape(-1, 3)])
+    # winding chosen so that the face normal points outward for both families (the two parametrisations have opposite
+    # handedness: the sphere's polar angle runs against the torus' tube angle)
+    if kind == 0:
+        tris = np.concatenate([np.stack([a, b_, c], -1).reshape(-1, 3), np.stack([a, c, d], -1).reshape(-1, 3)])
+    else:
+        tris = np.concatenate([np.stack([a, c, b_], -1).reshape(-1, 3), np.stack([a, d, c], -1).reshape(-1, 3)])
     # area-weighted vertex normals
     p = pos
     fn = np.cross(p[tris[:, 1]] - p[tris[:, 0]], p[tris[:, 2]] - p[tris[:, 0]])

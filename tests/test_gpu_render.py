@@ -69,7 +69,9 @@ def check_same_stream(gpu_lib, oracle_mod, b, spp, label, seed=9, rtol=1e-3):
     ost = orc.render(spp=spp, seed=seed, counter_rng=True)
     fo = orc.film_download().astype(np.float64)
     bad = (np.abs(fg - fo) > rtol * np.maximum(np.abs(fo), 1e-3))[..., :3].any(-1)
-    assert bad.mean() <= 2e-3, (label, int(bad.sum()), bad.size)
+    # a comparison that rounds differently on the two sides now and then sends ONE sample down another path: its 5 x 5 filter
+    # footprint (25 pixels) is allowed on top of the 0.2 % fraction, which on these small images is less than one footprint
+    assert bad.sum() <= max(2e-3 * bad.size, 25), (label, int(bad.sum()), bad.size)
     assert rel_mse(sc.film_develop().astype(np.float64), orc.film_develop().astype(np.float64)) < 1e-5
     assert st.samples == ost.samples
     for f in ("closest_rays", "shade_events", "path_length_sum"):
