@@ -85,6 +85,9 @@ struct TraceArgs {
 #ifndef MTSB_TQ_FLUSH
 #define MTSB_TQ_FLUSH 24           /* run a triangle phase when this many tests are queued (<= 32; 24 measured best)                                */
 #endif
+#ifndef MTSB_TQ_FLUSH_ANY
+#define MTSB_TQ_FLUSH_ANY MTSB_TQ_FLUSH   /* the same threshold for any-hit queries (8 / 16 measured: no better)                    */
+#endif
 #define MTSB_TQ_OWNER_SHIFT 27     /* entry = owner lane << 27 | triangle record index (2^27 records = 134 M triangles)           */
 
 struct WarpShared {
@@ -192,7 +195,7 @@ __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_MIN_CTAS) k_trace
             }
             // (c) triangle phase: when a full warp of tests is queued, or when nothing else can make progress
             const bool other_work = __any_sync(0xFFFFFFFFu, active && (tr.tw != 0 || tr.wants_node()));
-            while (qtail - qhead >= (uint32_t) MTSB_TQ_FLUSH || (qtail != qhead && !other_work)) {
+            while (qtail - qhead >= (uint32_t) (ANY ? MTSB_TQ_FLUSH_ANY : MTSB_TQ_FLUSH) || (qtail != qhead && !other_work)) {
                 __syncwarp();
                 const uint32_t nq = min(32u, qtail - qhead);
                 if (lane < nq) {
