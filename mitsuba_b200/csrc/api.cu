@@ -12,6 +12,7 @@
 #include <cmath>
 #include <cstring>
 #include <thread>
+#include <chrono>
 #include <algorithm>
 
 namespace mtsb {
@@ -197,9 +198,15 @@ extern "C" int mtsb_abi_version(void) { return MTSB_ABI_VERSION; }
 extern "C" const char *mtsb_last_error(void) { return g_error.c_str(); }
 
 extern "C" int mtsb_device_count(void) {
-    int n = 0;
-    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
-    return n;
+    // a process that starts while another one is still tearing its context down has been seen to get a transient
+    // failure here; ask a few times before reporting "no device"
+    for (int attempt = 0; attempt < 4; ++attempt) {
+        int n = 0;
+        if (cudaGetDeviceCount(&n) == cudaSuccess && n > 0) return n;
+        cudaGetLastError();
+        if (attempt < 3) std::this_thread::sleep_for(std::chrono::milliseconds(250));
+    }
+    return 0;
 }
 
 extern "C" int mtsb_init(int device) {
